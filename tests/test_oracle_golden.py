@@ -1,0 +1,108 @@
+"""The CPU oracle (oracle/az_oracle.py) against outputs of the unmodified reference
+(tests/golden/*, made by oracle/gen_golden.py).  CPU only."""
+import numpy as np
+import pytest
+
+import az_oracle as orc
+from golden_util import load_json, spec_of, board_from_words, position_after, fhex, GOLDEN
+
+
+@pytest.mark.parametrize("name,g", [("rules_tictactoe.json", orc.TICTACTOE),
+                                    ("rules_connect4.json", orc.CONNECT4),
+                                    ("rules_gomoku7.json", orc.GOMOKU),
+                                    ("rules_gomoku15.json", orc.gomoku_spec(15))])
+def test_rules_playouts(name, g):
+    n = 0
+    for plies in load_json(name):
+        board = orc.new_board(g)
+        for rec in plies:
+            ref = board_from_words(g, rec["p0"], rec["p1"])
+            assert np.array_equal(ref[:2], board[:2])
+            legal = orc.valid_moves(g, board)
+            assert [r * g.cols + c for r, c in legal] == rec["legal"]
+            mv = tuple(rec["move"])
+            before = board.copy()
+            nxt = orc.make_move(g, board, rec["player"], mv)
+            assert nxt == 1 - rec["player"]
+            assert orc.check_winner(g, board, rec["player"], mv) == rec["winner"]
+            probe = board.copy()
+            orc.undo_move(g, probe, nxt, mv)              # make/undo round trip
+            assert np.array_equal(probe[:2], before[:2])
+            n += 1
+    assert n > 50
+
+
+def test_gomoku_set_order_matches_real_set():
+    rng = np.random.default_rng(5)
+    for g in (orc.GOMOKU, orc.gomoku_spec(15), orc.gomoku_spec(9)):
+        cells = g.rows * g.cols
+        for r in range(g.rows):
+            for c in range(g.cols):
+                assert orc.cpython_tuple2_hash(r, c) == hash((r, c)) & orc.MASK64
+        for _ in range(300):
+            b = orc.new_board(g)
+            k = int(rng.integers(0, cells))
+            for i, cell in enumerate(rng.permutation(cells)[:k]):
+                b[i % 2, cell // g.cols, cell % g.cols] = 1
+            assert orc.valid_moves(g, b) == orc.valid_moves_pyset(g, b)
+
+
+def test_puct_bits():
+    for case in load_json("puct.json"):
+        parent = orc.Node(None, None, 0, 0)
+        parent.visit = case["parent_visit"]
+        for j, ch in enumerate(case["children"]):
+            p = fhex(ch["prior"])
+            prior = np.float64(p) if case["prior_is_f64"] else np.float32(p)
+            nd = orc.Node(parent, (0, j), 1, 1, prior)
+            nd.visit = ch["visit"]
+            nd.value = fhex(ch["value"]) if ch["visit"] else 0
+            parent.children.append(nd)
+        sel = orc.select_child(parent)
+        assert parent.children.index(sel) == case["selected"]
+        for nd, u, is32 in zip(parent.children, case["ucb"], case["ucb_is_f32"]):
+            assert float(nd.ucb) == fhex(u)
+            assert isinstance(nd.ucb, np.float32) == is32
+
+
+def test_search_cases():
+    cases = load_json("search.json")
+    assert len(cases) > 100
+    for case in cases:
+        g = spec_of(case)
+        board, player, mc = position_after(g, case["opening"])
+        before = board.copy()
+        root = orc.Node(None, None, player, mc)
+        noise = None if case["noise"] is None else np.asarray(case["noise"], dtype=np.float64)
+        orc.mcts(g, orc.HashEvaluator(g, case["seed"], case["qbits"]), board, root, case["iters"], noise=noise)
+        assert np.array_equal(board, before)
+        got, ref = orc.root_summary(g, root), case["result"]
+        assert got["actions"] == ref["actions"]
+        assert got["visits"] == ref["visits"]
+        assert got["values"] == [fhex(v) for v in ref["values"]]
+        assert got["priors"] == [fhex(v) for v in ref["priors"]]
+        assert got["root_visit"] == ref["root_visit"] == case["iters"]
+        assert got["root_value"] == fhex(ref["root_value"])
+
+
+def test_selfplay_and_buffer_transform():
+    recs = load_json("selfplay.json")
+    arrs = np.load(f"{GOLDEN}/selfplay.npz")
+    for i, rec in enumerate(recs):
+        g = spec_of(rec)
+        np.random.seed(rec["np_seed"])
+        ev = orc.HashEvaluator(g, rec["seed"], rec["qbits"])
+        boards, actions, policies, qs, winner = orc.self_play(
+            g, ev, rec["iters"], noise_fn=lambda A: np.random.dirichlet([0.03] * A), rng=np.random)
+        assert winner == rec["winner"] and len(boards) == rec["plies"]
+        assert np.array_equal(np.stack(boards), arrs[f"t{i}_boards"])
+        assert np.array_equal(np.stack(policies), arrs[f"t{i}_policies"])
+        if f"t{i}_actions" in arrs:
+            assert np.array_equal(np.asarray(actions, dtype=np.int64), arrs[f"t{i}_actions"])
+            assert np.array_equal(np.asarray(qs), arrs[f"t{i}_qs"])
+        if f"t{i}_buf_states" in arrs:
+            reward = 0 if winner == -1 else 1
+            samples = orc.trajectory_to_samples(g, boards, policies, winner, reward)
+            assert np.array_equal(np.stack([s[0] for s in samples]), arrs[f"t{i}_buf_states"])
+            assert np.array_equal(np.stack([s[1] for s in samples]), arrs[f"t{i}_buf_policies"])
+            assert np.array_equal(np.asarray([s[2] for s in samples], dtype=np.float64), arrs[f"t{i}_buf_z"])
