@@ -1,0 +1,925 @@
+// Forest kernels: PUCT select, expand, backup for thousands of concurrent trees (sm_100a).
+//
+// Replaces the per-node Python of the reference's simulation loop:
+//   MCTS.mcts                         ai/mcts.py:11-60
+//   Node.select / expand / backup     ai/node.py:42-74
+//   calcUcbOfChildrenFromParent       utils.py:29-44  ('network' branch, c_puct = 1)
+//   add_dirichlet_noise (mixing only) utils.py:24-25
+// One thread GROUP (8 or 32 lanes) owns one tree.  One launch of az_advance_kernel
+//   A. consumes the evaluator's answers for the tree's pending leaves: generate legal moves
+//      in reference order, write the child block (coalesced), back the value up the path;
+//   B. runs new descents until `vl` leaves wait for evaluation (terminal leaves are backed
+//      up on the spot and cost a simulation each, exactly like `continue` in mcts.py:28-32).
+// Compiled with -fmad=false: every score is the reference's rounding sequence.
+#include <cstdio>
+#include "az_forest.h"
+#include "az_rules.cuh"
+
+namespace {
+
+template <int G>
+__device__ __forceinline__ unsigned az_group_mask() {
+    if constexpr (G == 32) return 0xffffffffu;
+    else return ((1u << (G & 31)) - 1u) << (((threadIdx.x & 31) / G) * G);
+}
+
+// fp32 PUCT of the reference under NumPy >= 2 promotion:
+//   s = (float)sqrt((double)Np); t = P*s; u = t/(float)(n+1); q = (float)(W/n); ucb = q+u
+__device__ __forceinline__ float az_puct32(double W, float P, int n, float s) {
+    const float u = __fdiv_rn(__fmul_rn(P, s), (float)(n + 1));
+    if (n == 0) return u;                                     // utils.py:32-35
+    const float q = __double2float_rn(__ddiv_rn(W, (double)n));
+    return __fadd_rn(q, u);                                   // utils.py:40
+}
+
+// f64 variant: root children when Dirichlet noise made their priors np.float64.
+__device__ __forceinline__ double az_puct64(double W, double P, int n, double s) {
+    const double u = __ddiv_rn(__dmul_rn(P, s), (double)(n + 1));
+    if (n == 0) return u;
+    return __dadd_rn(__ddiv_rn(W, (double)n), u);
+}
+
+template <int G, typename T>
+__device__ __forceinline__ void az_group_argmax(unsigned gmask, T& best, int& idx) {
+#pragma unroll
+    for (int off = G / 2; off > 0; off >>= 1) {
+        const T o = __shfl_xor_sync(gmask, best, off, G);
+        const int oi = __shfl_xor_sync(gmask, idx, off, G);
+        if (o > best || (o == best && oi < idx)) {           // first maximum in child order
+            best = o;
+            idx = oi;
+        }
+    }
+}
+
+template <int NW, int G>
+__global__ void __launch_bounds__(128) az_advance_kernel(AzForestDev f, int smem_per_group) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x % G;
+    const int grp = threadIdx.x / G;
+    const int tree = blockIdx.x * (blockDim.x / G) + grp;
+    const unsigned gmask = az_group_mask<G>();
+    if (tree >= f.n_trees) return;
+    if (!f.active[tree] || f.done_flag[tree]) return;
+
+    const AzGame& g = f.g;
+    unsigned char* sm = smem_raw + (size_t)grp * smem_per_group;
+    uint32_t* s_path = reinterpret_cast<uint32_t*>(sm);
+    uint8_t* s_moves = sm + 4 * f.max_depth;
+    uint8_t* s_tab_a = s_moves + ((g.max_children + 15) & ~15);
+    uint8_t* s_tab_b = s_tab_a + g.set_slots;
+
+    AzHot* hot = f.hot + (size_t)tree * f.cap;
+    AzMeta* meta = f.meta + (size_t)tree * f.cap;
+    uint8_t* vlc = f.vlc + (size_t)tree * f.cap;
+    const bool use_vl = f.vl > 1;
+    const int A = g.action_dim;
+
+    unsigned st_sims = 0, st_term = 0, st_exp = 0, st_child = 0, st_sel = 0, st_reads = 0, st_coll = 0;
+    int n_nodes = f.n_nodes[tree];
+    int sims = f.sims_done[tree];
+
+    // ---------------- phase A: expand + backup the evaluated leaves -----------------------
+    const int npend = f.n_pending[tree];
+    for (int j = 0; j < npend; ++j) {
+        const size_t pj = (size_t)tree * f.vl + j;
+        const int slot = f.leaf_slot[pj];
+        const int len = f.path_len[pj];
+        const uint32_t* gpath = f.path + pj * f.max_depth;
+        const uint32_t leaf = gpath[len - 1];
+        AzBoard<NW> b;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) {
+            b.w[0][w] = f.pend_words[pj * 2 * NW + w];
+            b.w[1][w] = f.pend_words[pj * 2 * NW + NW + w];
+        }
+        int nc = 0;
+        if (lane == 0) nc = az_legal_moves<NW>(g, b, f.cell_hash, s_tab_a, s_tab_b, s_moves);
+        nc = __shfl_sync(gmask, nc, 0, G);
+        __syncwarp(gmask);                                    // s_moves visible to the group
+        const uint32_t base = (uint32_t)n_nodes;
+        n_nodes += nc;
+        const float* pri = f.priors + (size_t)slot * A;
+        const bool noisy_root = (leaf == 0) && f.use_noise;
+        for (int c = lane; c < nc; c += G) {
+            const int cell = s_moves[c];
+            const int ai = az_action_index(g, cell);
+            float p = pri[ai];                               // node.py:57 gather, unmasked softmax
+            if (noisy_root) {                                // utils.py:24: f32*0.75 + f64 noise*0.25
+                const double p64 = __dadd_rn((double)__fmul_rn(0.75f, p),
+                                             __dmul_rn(0.25, f.root_noise[(size_t)tree * A + ai]));
+                f.root_prior64[(size_t)tree * g.max_children + c] = p64;
+                p = __double2float_rn(p64);                  // kept for reporting only
+            }
+            AzHot h;
+            h.W = 0.0;
+            h.P = p;
+            h.N = 0;
+            hot[base + c] = h;
+            AzMeta m;
+            m.child_base = 0;
+            m.action = (uint16_t)cell;
+            m.nchild = 0;
+            m.status = AZ_ST_LEAF;
+            meta[base + c] = m;
+            if (use_vl) vlc[base + c] = 0;
+        }
+        if (lane == 0) {
+            AzMeta m = meta[leaf];
+            m.child_base = base;
+            m.nchild = (uint8_t)nc;
+            m.status = AZ_ST_EXPANDED;
+            meta[leaf] = m;
+        }
+        const double result = -(double)f.values[slot];        // mcts.py:56
+        for (int i = lane; i < len; i += G) {                 // node.py:69-72
+            const uint32_t nd = gpath[i];
+            AzHot h = hot[nd];
+            h.N += 1;
+            h.W = __dadd_rn(h.W, ((len - 1 - i) & 1) ? -result : result);
+            hot[nd] = h;
+            if (use_vl) vlc[nd] -= 1;
+        }
+        __syncwarp(gmask);
+        ++st_exp;
+        st_child += nc;
+        ++st_sims;
+        ++sims;
+    }
+
+    // ---------------- phase B: descend until `vl` leaves are pending -----------------------
+    AzBoard<NW> rootb;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+        rootb.w[0][w] = f.root_words[(size_t)tree * 2 * NW + w];
+        rootb.w[1][w] = f.root_words[(size_t)tree * 2 * NW + NW + w];
+    }
+    const int root_player = f.root_player[tree];
+    const int root_mc = f.root_mc[tree];
+    int started = sims;
+    int np = 0;
+    while (started < f.iters && np < f.vl) {
+        AzBoard<NW> b = rootb;
+        int player = root_player, mc = root_mc, len = 1;
+        uint32_t node = 0;
+        if (lane == 0) s_path[0] = 0;
+        AzMeta m = meta[0];
+        while (m.status == AZ_ST_EXPANDED) {                  // mcts.py:20-23
+            const int nc = m.nchild;
+            const uint32_t cb = m.child_base;
+            int pn = hot[node].N;
+            if (use_vl) pn += vlc[node];
+            int bi = 0x7fffffff;
+            if (node == 0 && f.use_noise) {
+                const double s = __dsqrt_rn((double)pn);
+                double best = -1.0 / 0.0;
+                for (int c = lane; c < nc; c += G) {
+                    AzHot h = hot[cb + c];
+                    int n = h.N;
+                    double W = h.W;
+                    if (use_vl) { const int v = vlc[cb + c]; n += v; W -= (double)v; }
+                    const double sc = az_puct64(W, f.root_prior64[(size_t)tree * g.max_children + c], n, s);
+                    if (sc > best) { best = sc; bi = c; }
+                }
+                az_group_argmax<G, double>(gmask, best, bi);
+            } else {
+                const float s = __double2float_rn(__dsqrt_rn((double)pn));
+                float best = -1.0f / 0.0f;
+                for (int c = lane; c < nc; c += G) {
+                    AzHot h = hot[cb + c];
+                    int n = h.N;
+                    double W = h.W;
+                    if (use_vl) { const int v = vlc[cb + c]; n += v; W -= (double)v; }
+                    const float sc = az_puct32(W, h.P, n, s);
+                    if (sc > best) { best = sc; bi = c; }
+                }
+                az_group_argmax<G, float>(gmask, best, bi);
+            }
+            if (bi == 0x7fffffff) bi = 0;                     // all-NaN guard: max() keeps the first
+            st_reads += nc;
+            ++st_sel;
+            node = cb + bi;
+            if (lane == 0) s_path[len] = node;
+            ++len;
+            m = meta[node];
+            b.put(player, m.action);                          // Game.make_move (mcts.py:23)
+            player ^= 1;
+            ++mc;
+        }
+        if (m.status == AZ_ST_PENDING) {                      // leaf already waiting: close the batch
+            ++st_coll;
+            break;
+        }
+        __syncwarp(gmask);                                    // s_path visible to all lanes
+        int status = m.status;
+        if (node != 0 && status == AZ_ST_LEAF) {              // mcts.py:25-32, cached in the node
+            if (az_is_win<NW>(g, b, player ^ 1, m.action)) status = AZ_ST_WIN;
+            else if (mc == g.state_dim) status = AZ_ST_DRAW;
+            if (status != AZ_ST_LEAF && lane == 0) {
+                m.status = (uint8_t)status;
+                meta[node] = m;
+            }
+        }
+        if (status == AZ_ST_WIN || status == AZ_ST_DRAW) {
+            const double v = status == AZ_ST_WIN ? 1.0 : 0.0;
+            for (int i = lane; i < len; i += G) {
+                const uint32_t nd = s_path[i];
+                AzHot h = hot[nd];
+                h.N += 1;
+                h.W = __dadd_rn(h.W, ((len - 1 - i) & 1) ? -v : v);
+                hot[nd] = h;
+            }
+            __syncwarp(gmask);
+            ++st_term;
+            ++st_sims;
+            ++started;
+            ++sims;
+            continue;
+        }
+        // leaf needs the evaluator
+        int slot = 0;
+        if (lane == 0) slot = atomicAdd(f.n_leaves, 1);
+        slot = __shfl_sync(gmask, slot, 0, G);
+        const size_t pj = (size_t)tree * f.vl + np;
+        uint32_t* gpath = f.path + pj * f.max_depth;
+        for (int i = lane; i < len; i += G) {
+            const uint32_t nd = s_path[i];
+            gpath[i] = nd;
+            if (use_vl) vlc[nd] += 1;
+        }
+        if (lane == 0) {
+            f.path_len[pj] = (uint16_t)len;
+            f.leaf_slot[pj] = slot;
+            f.pend_player[pj] = (uint8_t)player;
+            f.pend_mc[pj] = (uint16_t)mc;
+            f.leaf_player[slot] = (uint8_t)player;
+            f.leaf_tree[slot] = tree;
+            if (use_vl) {
+                m.status = AZ_ST_PENDING;
+                meta[node] = m;
+            }
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                f.pend_words[pj * 2 * NW + w] = b.w[0][w];
+                f.pend_words[pj * 2 * NW + NW + w] = b.w[1][w];
+                f.leaf_words[(size_t)slot * 2 * NW + w] = b.w[player][w];           // canonical: mine
+                f.leaf_words[(size_t)slot * 2 * NW + NW + w] = b.w[player ^ 1][w];  // theirs
+            }
+        }
+        __syncwarp(gmask);
+        ++np;
+        ++started;
+    }
+
+    if (lane == 0) {
+        f.n_nodes[tree] = n_nodes;
+        f.sims_done[tree] = sims;
+        f.n_pending[tree] = (uint8_t)np;
+        if (np == 0 && sims >= f.iters) {
+            f.done_flag[tree] = 1;
+            atomicAdd(f.n_done, 1);
+        }
+    }
+    if (f.stats && lane < 7) {
+        const unsigned vals[7] = {st_sims, st_term, st_exp, st_child, st_sel, st_reads, st_coll};
+        unsigned v = 0;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) if (lane == k) v = vals[k];
+        if (v) f.stats[(size_t)tree * AZ_STAT_COUNT + lane] += v;
+    }
+}
+
+}  // namespace
+
+// ======================================================================================
+// Auxiliary kernels
+// ======================================================================================
+namespace {
+
+__global__ void az_begin_move_kernel(AzForestDev f) {
+    const int tree = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tree >= f.n_trees) return;
+    AzHot h;
+    h.W = 0.0;
+    h.P = 0.f;
+    h.N = 0;
+    f.hot[(size_t)tree * f.cap] = h;
+    AzMeta m;
+    m.child_base = 0;
+    m.action = 0;
+    m.nchild = 0;
+    m.status = AZ_ST_LEAF;
+    f.meta[(size_t)tree * f.cap] = m;
+    f.vlc[(size_t)tree * f.cap] = 0;
+    f.n_nodes[tree] = 1;
+    f.sims_done[tree] = 0;
+    f.n_pending[tree] = 0;
+    const bool live = f.active[tree] != 0;
+    f.done_flag[tree] = live ? 0 : 1;
+    if (!live) atomicAdd(f.n_done, 1);                       // counters are zeroed by the host before
+}
+
+// splitmix64 finaliser; the build-defined hash evaluator (oracle/az_oracle.py: hash_eval_*).
+__device__ __forceinline__ uint64_t az_sm64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    uint64_t z = x;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+// One thread per (leaf, action): priors exact in fp32 (integer * power of two), sum <= 1.
+__global__ void az_eval_hash_kernel(AzForestDev f, uint64_t seed, int qbits, float scale) {
+    const int n = *f.n_leaves;
+    const int A = f.g.action_dim;
+    const int nw = f.g.nw;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < (long long)n * (A + 1);
+         t += (long long)gridDim.x * blockDim.x) {
+        const int slot = (int)(t / (A + 1));
+        const int a = (int)(t - (long long)slot * (A + 1));
+        const uint64_t* w = f.leaf_words + (size_t)slot * 2 * nw;
+        uint64_t h = az_sm64(seed);
+        for (int i = 0; i < nw; ++i) h = az_sm64(h ^ w[i]);
+        h = az_sm64(h ^ 0xA5A5A5A5A5A5A5A5ull);
+        for (int i = 0; i < nw; ++i) h = az_sm64(h ^ w[nw + i]);
+        if (f.g.planes == 3) h = az_sm64(h ^ (uint64_t)f.leaf_player[slot]);
+        if (a < A) {
+            const uint64_t x = az_sm64(h + (uint64_t)a + 1);
+            const uint32_t q = (uint32_t)((x >> 40) & ((1ull << qbits) - 1)) + 1;
+            f.priors[(size_t)slot * A + a] = __fmul_rn((float)q, scale);
+        } else {
+            const uint64_t x = az_sm64(h + 0xFFFFull);
+            const int q = (int)((x >> 40) & 0xFFFF) - 32768;
+            f.values[slot] = __fmul_rn((float)q, 1.0f / 32768.0f);
+        }
+    }
+}
+
+// f32 planes [n][C][H][W] (the reference's board format) -> side bitboards.
+__global__ void az_planes_to_words_kernel(const float* __restrict__ planes, int n, AzGame g, uint64_t* words) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n * 2 * g.nw) return;
+    const int tree = t / (2 * g.nw), r = t % (2 * g.nw), side = r / g.nw, wi = r % g.nw;
+    const float* p = planes + ((size_t)tree * g.planes + side) * g.state_dim;
+    uint64_t v = 0;
+    for (int i = 0; i < 64; ++i) {
+        const int cell = wi * 64 + i;
+        if (cell < g.state_dim && p[cell] == 1.0f) v |= 1ull << i;
+    }
+    words[t] = v;
+}
+
+// Evaluation batch -> f32 canonical planes [B][C][H][W] for an external (PyTorch) evaluator:
+// plane 0 = side to move, plane 1 = opponent (gomoku.py:34-40), plane 2 = side-to-move id.
+__global__ void az_leaves_to_planes_kernel(AzForestDev f, float* out, int max_b) {
+    const int n = min(*f.n_leaves, max_b);
+    const int cells = f.g.state_dim, C = f.g.planes, nw = f.g.nw;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < (long long)n * C * cells;
+         t += (long long)gridDim.x * blockDim.x) {
+        const int slot = (int)(t / (C * cells));
+        const int r = (int)(t - (long long)slot * C * cells);
+        const int pl = r / cells, cell = r - pl * cells;
+        float v;
+        if (pl < 2) v = (float)((f.leaf_words[(size_t)slot * 2 * nw + pl * nw + (cell >> 6)] >> (cell & 63)) & 1ull);
+        else v = (float)f.leaf_player[slot];
+        out[t] = v;
+    }
+}
+
+// logits [B][A], values [B] from an external evaluator -> priors exactly as ai/mcts.py:49:
+// exp(l)/sum(exp(l)) in fp32 (max-subtracted for range safety; same value up to rounding).
+__global__ void az_logits_to_priors_kernel(AzForestDev f, const float* __restrict__ logits,
+                                           const float* __restrict__ values, int max_b) {
+    const int n = min(*f.n_leaves, max_b);
+    const int A = f.g.action_dim;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= n) return;
+    const float* l = logits + (size_t)warp * A;
+    float mx = -1.0f / 0.0f;
+    for (int a = lane; a < A; a += 32) mx = fmaxf(mx, l[a]);
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float s = 0.f;
+    for (int a = lane; a < A; a += 32) s += expf(l[a] - mx);
+    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    for (int a = lane; a < A; a += 32) f.priors[(size_t)warp * A + a] = expf(l[a] - mx) / s;
+    if (lane == 0) f.values[warp] = values[warp];
+}
+
+// Visit counts of the root children scattered to action order (utils.py:46-55) + root Q.
+__global__ void az_root_visits_kernel(AzForestDev f, int* visits, double* q) {
+    const int tree = blockIdx.x;
+    const int A = f.g.action_dim;
+    for (int a = threadIdx.x; a < A; a += blockDim.x) visits[(size_t)tree * A + a] = 0;
+    __syncthreads();
+    const AzMeta m = f.meta[(size_t)tree * f.cap];
+    const AzHot* hot = f.hot + (size_t)tree * f.cap;
+    const AzMeta* meta = f.meta + (size_t)tree * f.cap;
+    if (m.status == AZ_ST_EXPANDED)
+        for (int c = threadIdx.x; c < m.nchild; c += blockDim.x)
+            visits[(size_t)tree * A + az_action_index(f.g, meta[m.child_base + c].action)] = hot[m.child_base + c].N;
+    if (threadIdx.x == 0 && q) q[tree] = hot[0].N ? hot[0].W / (double)hot[0].N : 0.0;   // gomoku.py:141
+}
+
+}  // namespace
+
+// ======================================================================================
+// Host side: handle + C ABI (include/az_b200.h)
+// ======================================================================================
+#include <string>
+#include <vector>
+#include "az_host.h"
+#include "../../include/az_b200.h"
+
+thread_local std::string g_az_error;
+
+extern "C" const char* az_last_error(void) { return g_az_error.c_str(); }
+extern "C" const char* az_version(void) { return "az_b200 0.1 (sm_100a)"; }
+
+int az_fail(int code, const std::string& msg) {
+    g_az_error = msg;
+    return code;
+}
+
+int az_make_game(int game, int rows, int cols, AzGame* out) {
+    AzGame g{};
+    g.gid = game;
+    g.rows = rows;
+    g.cols = cols;
+    if (game == AZ_GAME_TICTACTOE) {
+        if (rows != 3 || cols != 3) return az_fail(AZ_EINVAL, "tictactoe is 3x3");
+        g.k = 3; g.action_dim = 9; g.planes = 3; g.max_children = 9;
+    } else if (game == AZ_GAME_CONNECT4) {
+        if (rows != 6 || cols != 7) return az_fail(AZ_EINVAL, "connect4 is 6x7");
+        g.k = 4; g.action_dim = 7; g.planes = 3; g.max_children = 7;
+    } else if (game == AZ_GAME_GOMOKU) {
+        if (rows != cols || rows < 5 || rows > 15) return az_fail(AZ_EINVAL, "gomoku is n x n, 5 <= n <= 15");
+        g.k = 5; g.action_dim = rows * cols; g.planes = 2; g.max_children = rows * cols;
+    } else {
+        return az_fail(AZ_EINVAL, "unknown game id");
+    }
+    g.state_dim = rows * cols;
+    g.nw = (g.state_dim + 63) / 64;
+    g.set_slots = 0;
+    if (game == AZ_GAME_GOMOKU) {                 // largest table a CPython set of <= cells items reaches
+        int size = 8;
+        for (int fill = 1; fill <= g.state_dim; ++fill)
+            if (fill * 5 >= (size - 1) * 3) {
+                size = 8;
+                while (size <= fill * 4) size <<= 1;
+            }
+        g.set_slots = size;
+    }
+    *out = g;
+    return AZ_OK;
+}
+
+// CPython 3.8+ tuple hash of (r, c), Objects/tupleobject.c (xxHash-derived).
+uint64_t az_tuple2_hash(uint64_t r, uint64_t c) {
+    const uint64_t P1 = 11400714785074694791ull, P2 = 14029467366897019727ull, P5 = 2870177450012600261ull;
+    uint64_t acc = P5;
+    const uint64_t lanes[2] = {r, c};
+    for (int i = 0; i < 2; ++i) {
+        acc += lanes[i] * P2;
+        acc = (acc << 31) | (acc >> 33);
+        acc *= P1;
+    }
+    acc += 2ull ^ (P5 ^ 3527539ull);
+    if (acc == ~0ull) acc = 1546275796ull;
+    return acc;
+}
+
+struct az_forest {
+    AzForestDev d{};
+    int max_iters = 0;
+    int G = 32;
+    int block = 128;
+    int smem_per_group = 0;
+    std::vector<void*> allocs;
+    double* noise_dev = nullptr;
+    int* h_counts = nullptr;      // pinned: n_leaves, n_done
+    void* h_stage = nullptr;      // pinned staging for roots
+    size_t h_stage_bytes = 0;
+    float* planes_stage_dev = nullptr;
+    int32_t* i32_stage_dev = nullptr;
+};
+
+namespace {
+
+template <typename T>
+int az_dev_alloc(az_forest* f, T** p, size_t n) {
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, n * sizeof(T) + 16);
+    if (e != cudaSuccess) return az_fail(AZ_ENOMEM, std::string("cudaMalloc: ") + cudaGetErrorString(e));
+    f->allocs.push_back(q);
+    *p = reinterpret_cast<T*>(q);
+    return AZ_OK;
+}
+
+__global__ void az_roots_from_i32_kernel(AzForestDev f, const int32_t* players, const int32_t* mcs) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= f.n_trees) return;
+    f.root_player[t] = (uint8_t)players[t];
+    f.root_mc[t] = (uint16_t)mcs[t];
+}
+
+template <int NW>
+__global__ void az_rules_legal_kernel(AzGame g, int n, const uint64_t* words, const uint64_t* cell_hash,
+                                      int32_t* counts, uint8_t* cells, uint8_t* scratch) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    AzBoard<NW> b;
+    for (int w = 0; w < NW; ++w) {
+        b.w[0][w] = words[(size_t)t * 2 * NW + w];
+        b.w[1][w] = words[(size_t)t * 2 * NW + NW + w];
+    }
+    uint8_t* ta = scratch + (size_t)t * 2 * (g.set_slots + 1);
+    counts[t] = az_legal_moves<NW>(g, b, cell_hash, ta, ta + g.set_slots, cells + (size_t)t * g.state_dim);
+}
+
+template <int NW>
+__global__ void az_rules_winner_kernel(AzGame g, int n, const uint64_t* words, const int32_t* players,
+                                       const int32_t* cells, int32_t* out) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    AzBoard<NW> b;
+    for (int w = 0; w < NW; ++w) {
+        b.w[0][w] = words[(size_t)t * 2 * NW + w];
+        b.w[1][w] = words[(size_t)t * 2 * NW + NW + w];
+    }
+    out[t] = az_is_win<NW>(g, b, players[t], cells[t]) ? players[t] : -1;
+}
+
+template <int NW, int G>
+int az_launch_advance(az_forest* f, cudaStream_t s) {
+    const int gpb = f->block / G;
+    const int grid = (f->d.n_trees + gpb - 1) / gpb;
+    const size_t smem = (size_t)gpb * f->smem_per_group;
+    az_advance_kernel<NW, G><<<grid, f->block, smem, s>>>(f->d, f->smem_per_group);
+    return AZ_OK;
+}
+
+}  // namespace
+
+#define AZ_CUDA_OK(expr)                                                                       \
+    do {                                                                                       \
+        cudaError_t e__ = (expr);                                                              \
+        if (e__ != cudaSuccess) return az_fail(AZ_ECUDA, std::string(#expr ": ") + cudaGetErrorString(e__)); \
+    } while (0)
+
+extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int max_iters, int vl_batch,
+                                az_forest** out) {
+    if (!out || n_trees <= 0 || max_iters <= 0 || vl_batch <= 0 || vl_batch > 64)
+        return az_fail(AZ_EINVAL, "az_forest_create: bad arguments");
+    AzGame g;
+    int rc = az_make_game(game, rows, cols, &g);
+    if (rc) return rc;
+    az_forest* f = new az_forest();
+    AzForestDev& d = f->d;
+    d.g = g;
+    d.n_trees = n_trees;
+    d.iters = max_iters;
+    d.vl = vl_batch;
+    d.cap = 1 + max_iters * g.max_children;
+    d.max_depth = g.state_dim + 2;
+    d.max_leaves = n_trees * vl_batch;
+    d.use_noise = 0;
+    f->max_iters = max_iters;
+    f->G = (g.max_children <= 9) ? 8 : 32;
+    size_t per_group = 4 * (size_t)d.max_depth + ((g.max_children + 15) & ~15) + 2 * (size_t)g.set_slots;
+    f->smem_per_group = (int)((per_group + 15) & ~(size_t)15);
+    const size_t nodes = (size_t)n_trees * d.cap;
+    const int nw = g.nw;
+#define AZ_ALLOC(ptr, count)                                  \
+    if ((rc = az_dev_alloc(f, &(ptr), (count))) != AZ_OK) {   \
+        az_forest_destroy(f);                                 \
+        return rc;                                            \
+    }
+    AZ_ALLOC(d.hot, nodes);
+    AZ_ALLOC(d.meta, nodes);
+    AZ_ALLOC(d.vlc, nodes);
+    AZ_ALLOC(d.root_words, (size_t)n_trees * 2 * nw);
+    AZ_ALLOC(d.root_player, (size_t)n_trees);
+    AZ_ALLOC(d.root_mc, (size_t)n_trees);
+    AZ_ALLOC(d.active, (size_t)n_trees);
+    AZ_ALLOC(d.n_nodes, (size_t)n_trees);
+    AZ_ALLOC(d.sims_done, (size_t)n_trees);
+    AZ_ALLOC(d.n_pending, (size_t)n_trees);
+    AZ_ALLOC(d.done_flag, (size_t)n_trees);
+    AZ_ALLOC(d.path, (size_t)d.max_leaves * d.max_depth);
+    AZ_ALLOC(d.path_len, (size_t)d.max_leaves);
+    AZ_ALLOC(d.leaf_slot, (size_t)d.max_leaves);
+    AZ_ALLOC(d.pend_words, (size_t)d.max_leaves * 2 * nw);
+    AZ_ALLOC(d.pend_player, (size_t)d.max_leaves);
+    AZ_ALLOC(d.pend_mc, (size_t)d.max_leaves);
+    AZ_ALLOC(d.n_leaves, 4);
+    d.n_done = d.n_leaves + 1;
+    AZ_ALLOC(d.leaf_words, (size_t)d.max_leaves * 2 * nw);
+    AZ_ALLOC(d.leaf_player, (size_t)d.max_leaves);
+    AZ_ALLOC(d.leaf_tree, (size_t)d.max_leaves);
+    AZ_ALLOC(d.priors, (size_t)d.max_leaves * g.action_dim);
+    AZ_ALLOC(d.values, (size_t)d.max_leaves);
+    AZ_ALLOC(d.root_prior64, (size_t)n_trees * g.max_children);
+    AZ_ALLOC(d.stats, (size_t)n_trees * AZ_STAT_COUNT);
+    AZ_ALLOC(f->noise_dev, (size_t)n_trees * g.action_dim);
+    AZ_ALLOC(f->planes_stage_dev, (size_t)n_trees * g.planes * g.state_dim);
+    AZ_ALLOC(f->i32_stage_dev, (size_t)n_trees * 2);
+    uint64_t* hash_dev = nullptr;
+    AZ_ALLOC(hash_dev, (size_t)g.state_dim);
+#undef AZ_ALLOC
+    std::vector<uint64_t> hashes(g.state_dim);
+    for (int i = 0; i < g.state_dim; ++i) hashes[i] = az_tuple2_hash(i / g.cols, i % g.cols);
+    cudaMemcpy(hash_dev, hashes.data(), hashes.size() * 8, cudaMemcpyHostToDevice);
+    d.cell_hash = hash_dev;
+    d.root_noise = nullptr;
+    cudaMemset(d.active, 1, n_trees);
+    cudaMemset(d.stats, 0, (size_t)n_trees * AZ_STAT_COUNT * 8);
+    cudaMemset(d.done_flag, 1, n_trees);
+    cudaMemset(d.n_leaves, 0, 16);
+    cudaMemset(d.root_words, 0, (size_t)n_trees * 2 * nw * 8);
+    cudaMemset(d.root_player, 0, n_trees);
+    cudaMemset(d.root_mc, 0, (size_t)n_trees * 2);
+    f->h_stage_bytes = (size_t)n_trees * (size_t)std::max<size_t>((size_t)g.planes * g.state_dim * 4, (size_t)g.action_dim * 8) + 64;
+    if (cudaMallocHost(&f->h_counts, 64) != cudaSuccess || cudaMallocHost(&f->h_stage, f->h_stage_bytes) != cudaSuccess) {
+        az_forest_destroy(f);
+        return az_fail(AZ_ENOMEM, "cudaMallocHost failed");
+    }
+    const size_t smem = (size_t)(f->block / f->G) * f->smem_per_group;
+    if (smem > 48 * 1024) {
+        cudaError_t e;
+        if (nw == 1) e = f->G == 8 ? cudaFuncSetAttribute(az_advance_kernel<1, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                                   : cudaFuncSetAttribute(az_advance_kernel<1, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        else e = cudaFuncSetAttribute(az_advance_kernel<4, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) { az_forest_destroy(f); return az_fail(AZ_ECUDA, "smem attribute"); }
+    }
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        az_forest_destroy(f);
+        return az_fail(AZ_ECUDA, std::string("az_forest_create: ") + cudaGetErrorString(e));
+    }
+    *out = f;
+    return AZ_OK;
+}
+
+extern "C" void az_forest_destroy(az_forest* f) {
+    if (!f) return;
+    for (void* p : f->allocs) cudaFree(p);
+    if (f->h_counts) cudaFreeHost(f->h_counts);
+    if (f->h_stage) cudaFreeHost(f->h_stage);
+    delete f;
+}
+
+AzForestDev* az_forest_dev(az_forest* f) { return &f->d; }
+
+static int az_set_players(az_forest* f, const int32_t* players, const int32_t* mcs, cudaStream_t s) {
+    const int n = f->d.n_trees;
+    AZ_CUDA_OK(cudaMemcpyAsync(f->i32_stage_dev, players, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    AZ_CUDA_OK(cudaMemcpyAsync(f->i32_stage_dev + n, mcs, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    az_roots_from_i32_kernel<<<(n + 255) / 256, 256, 0, s>>>(f->d, f->i32_stage_dev, f->i32_stage_dev + n);
+    AZ_CUDA_OK(cudaGetLastError());
+    return AZ_OK;
+}
+
+extern "C" int az_forest_set_roots_planes(az_forest* f, const float* planes_host, const int32_t* players_host,
+                                          const int32_t* move_counts_host, void* stream) {
+    if (!f || !planes_host || !players_host || !move_counts_host) return az_fail(AZ_EINVAL, "set_roots_planes: null");
+    cudaStream_t s = (cudaStream_t)stream;
+    const AzGame& g = f->d.g;
+    const size_t bytes = (size_t)f->d.n_trees * g.planes * g.state_dim * 4;
+    AZ_CUDA_OK(cudaMemcpyAsync(f->planes_stage_dev, planes_host, bytes, cudaMemcpyHostToDevice, s));
+    const int n = f->d.n_trees * 2 * g.nw;
+    az_planes_to_words_kernel<<<(n + 127) / 128, 128, 0, s>>>(f->planes_stage_dev, f->d.n_trees, g, f->d.root_words);
+    AZ_CUDA_OK(cudaGetLastError());
+    return az_set_players(f, players_host, move_counts_host, s);
+}
+
+extern "C" int az_forest_set_roots_words(az_forest* f, const uint64_t* words_host, const int32_t* players_host,
+                                         const int32_t* move_counts_host, void* stream) {
+    if (!f || !words_host || !players_host || !move_counts_host) return az_fail(AZ_EINVAL, "set_roots_words: null");
+    cudaStream_t s = (cudaStream_t)stream;
+    AZ_CUDA_OK(cudaMemcpyAsync(f->d.root_words, words_host, (size_t)f->d.n_trees * 2 * f->d.g.nw * 8,
+                               cudaMemcpyHostToDevice, s));
+    return az_set_players(f, players_host, move_counts_host, s);
+}
+
+extern "C" int az_forest_set_active(az_forest* f, const uint8_t* active_host, void* stream) {
+    if (!f) return az_fail(AZ_EINVAL, "set_active: null");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!active_host) AZ_CUDA_OK(cudaMemsetAsync(f->d.active, 1, f->d.n_trees, s));
+    else AZ_CUDA_OK(cudaMemcpyAsync(f->d.active, active_host, f->d.n_trees, cudaMemcpyHostToDevice, s));
+    return AZ_OK;
+}
+
+extern "C" int az_forest_set_noise(az_forest* f, const double* noise_host, void* stream) {
+    if (!f) return az_fail(AZ_EINVAL, "set_noise: null");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!noise_host) {
+        f->d.use_noise = 0;
+        f->d.root_noise = nullptr;
+        return AZ_OK;
+    }
+    AZ_CUDA_OK(cudaMemcpyAsync(f->noise_dev, noise_host, (size_t)f->d.n_trees * f->d.g.action_dim * 8,
+                               cudaMemcpyHostToDevice, s));
+    f->d.use_noise = 1;
+    f->d.root_noise = f->noise_dev;
+    return AZ_OK;
+}
+
+extern "C" int az_forest_begin_move(az_forest* f, int iters, void* stream) {
+    if (!f || iters < 0 || iters > f->max_iters) return az_fail(AZ_EINVAL, "begin_move: iters out of range");
+    f->d.iters = iters;
+    AZ_CUDA_OK(cudaMemsetAsync(f->d.n_leaves, 0, 2 * sizeof(int), (cudaStream_t)stream));
+    az_begin_move_kernel<<<(f->d.n_trees + 255) / 256, 256, 0, (cudaStream_t)stream>>>(f->d);
+    AZ_CUDA_OK(cudaGetLastError());
+    return AZ_OK;
+}
+
+extern "C" int az_forest_advance(az_forest* f, void* stream) {
+    if (!f) return az_fail(AZ_EINVAL, "advance: null");
+    cudaStream_t s = (cudaStream_t)stream;
+    AZ_CUDA_OK(cudaMemsetAsync(f->d.n_leaves, 0, sizeof(int), s));
+    if (f->d.g.nw == 1) {
+        if (f->G == 8) az_launch_advance<1, 8>(f, s);
+        else az_launch_advance<1, 32>(f, s);
+    } else {
+        az_launch_advance<4, 32>(f, s);
+    }
+    AZ_CUDA_OK(cudaGetLastError());
+    return AZ_OK;
+}
+
+extern "C" int az_forest_counts(az_forest* f, int* n_leaves, int* n_done, void* stream) {
+    if (!f) return az_fail(AZ_EINVAL, "counts: null");
+    cudaStream_t s = (cudaStream_t)stream;
+    AZ_CUDA_OK(cudaMemcpyAsync(f->h_counts, f->d.n_leaves, 2 * sizeof(int), cudaMemcpyDeviceToHost, s));
+    AZ_CUDA_OK(cudaStreamSynchronize(s));
+    if (n_leaves) *n_leaves = f->h_counts[0];
+    if (n_done) *n_done = f->h_counts[1];
+    return AZ_OK;
+}
+
+extern "C" int az_eval_hash(az_forest* f, uint64_t seed, int qbits, void* stream) {
+    if (!f || qbits < 1 || qbits > 16) return az_fail(AZ_EINVAL, "eval_hash: qbits in 1..16");
+    int lg = 0;
+    while ((1 << lg) < f->d.g.action_dim) ++lg;
+    const float scale = ldexpf(1.0f, -(qbits + lg));
+    const long long work = (long long)f->d.max_leaves * (f->d.g.action_dim + 1);
+    const int grid = (int)std::min<long long>((work + 255) / 256, 148 * 16);
+    az_eval_hash_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(f->d, seed, qbits, scale);
+    AZ_CUDA_OK(cudaGetLastError());
+    return AZ_OK;
+}
+
+extern "C" int az_leaves_to_planes(az_forest* f, float* planes_dev, int max_b, void* stream) {
+    if (!f || !planes_dev) return az_fail(AZ_EINVAL, "leaves_to_planes: null");
+    az_leaves_to_planes_kernel<<<148 * 4, 256, 0, (cudaStream_t)stream>>>(f->d, planes_dev, max_b);
+    AZ_CUDA_OK(cudaGetLastError());
+    return AZ_OK;
+}
+
+extern "C" int az_leaves_set_logits(az_forest* f, const float* logits_dev, const float* values_dev, int max_b,
+                                    void* stream) {
+    if (!f || !logits_dev || !values_dev) return az_fail(AZ_EINVAL, "leaves_set_logits: null");
+    const int nb = std::min(max_b, f->d.max_leaves);
+    az_logits_to_priors_kernel<<<(nb * 32 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(f->d, logits_dev, values_dev, max_b);
+    AZ_CUDA_OK(cudaGetLastError());
+    return AZ_OK;
+}
+
+extern "C" int az_forest_search_hash(az_forest* f, int iters, uint64_t seed, int qbits, void* stream) {
+    int rc = az_forest_begin_move(f, iters, stream);
+    if (rc) return rc;
+    // vl == 1: every advance retires one simulation per live tree, so iters + 1 advances
+    // finish the search (the last one only applies results); vl > 1 polls the done counter.
+    int done = 0, steps = 0;
+    for (;;) {
+        const int burst = steps == 0 ? (f->d.vl == 1 ? iters + 1 : std::max(8, iters / f->d.vl)) : 4;
+        for (int i = 0; i < burst; ++i) {
+            if ((rc = az_forest_advance(f, stream))) return rc;
+            if ((rc = az_eval_hash(f, seed, qbits, stream))) return rc;
+            ++steps;
+        }
+        if ((rc = az_forest_counts(f, nullptr, &done, stream))) return rc;
+        if (done >= f->d.n_trees) break;
+        if (steps > 2 * iters + 16) return az_fail(AZ_ESTATE, "search_hash: did not converge");
+    }
+    return AZ_OK;
+}
+
+extern "C" int az_forest_root_visits(az_forest* f, int32_t* visits_host, double* q_host, void* stream) {
+    if (!f || !visits_host) return az_fail(AZ_EINVAL, "root_visits: null");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int n = f->d.n_trees, A = f->d.g.action_dim;
+    int* vis_dev = nullptr;
+    double* q_dev = nullptr;
+    AZ_CUDA_OK(cudaMallocAsync(&vis_dev, (size_t)n * A * 4, s));
+    AZ_CUDA_OK(cudaMallocAsync(&q_dev, (size_t)n * 8, s));
+    az_root_visits_kernel<<<n, 64, 0, s>>>(f->d, vis_dev, q_dev);
+    AZ_CUDA_OK(cudaMemcpyAsync(visits_host, vis_dev, (size_t)n * A * 4, cudaMemcpyDeviceToHost, s));
+    if (q_host) AZ_CUDA_OK(cudaMemcpyAsync(q_host, q_dev, (size_t)n * 8, cudaMemcpyDeviceToHost, s));
+    AZ_CUDA_OK(cudaFreeAsync(vis_dev, s));
+    AZ_CUDA_OK(cudaFreeAsync(q_dev, s));
+    AZ_CUDA_OK(cudaStreamSynchronize(s));
+    return AZ_OK;
+}
+
+extern "C" int az_forest_root_children(az_forest* f, int tree, int max_children, int32_t* cells_host,
+                                       int32_t* visits_host, double* values_host, double* priors_host,
+                                       int32_t* root_visit, double* root_value, void* stream) {
+    if (!f || tree < 0 || tree >= f->d.n_trees) return az_fail(AZ_EINVAL, "root_children: bad tree");
+    cudaStream_t s = (cudaStream_t)stream;
+    AZ_CUDA_OK(cudaStreamSynchronize(s));
+    AzMeta m;
+    AzHot h;
+    AZ_CUDA_OK(cudaMemcpy(&m, f->d.meta + (size_t)tree * f->d.cap, sizeof(m), cudaMemcpyDeviceToHost));
+    AZ_CUDA_OK(cudaMemcpy(&h, f->d.hot + (size_t)tree * f->d.cap, sizeof(h), cudaMemcpyDeviceToHost));
+    if (root_visit) *root_visit = h.N;
+    if (root_value) *root_value = h.W;
+    if (m.status != AZ_ST_EXPANDED) return 0;
+    const int nc = std::min<int>(m.nchild, max_children);
+    std::vector<AzHot> hh(nc);
+    std::vector<AzMeta> mm(nc);
+    std::vector<double> p64(nc);
+    AZ_CUDA_OK(cudaMemcpy(hh.data(), f->d.hot + (size_t)tree * f->d.cap + m.child_base, nc * sizeof(AzHot), cudaMemcpyDeviceToHost));
+    AZ_CUDA_OK(cudaMemcpy(mm.data(), f->d.meta + (size_t)tree * f->d.cap + m.child_base, nc * sizeof(AzMeta), cudaMemcpyDeviceToHost));
+    if (f->d.use_noise)
+        AZ_CUDA_OK(cudaMemcpy(p64.data(), f->d.root_prior64 + (size_t)tree * f->d.g.max_children, nc * 8, cudaMemcpyDeviceToHost));
+    for (int c = 0; c < nc; ++c) {
+        if (cells_host) cells_host[c] = mm[c].action;
+        if (visits_host) visits_host[c] = hh[c].N;
+        if (values_host) values_host[c] = hh[c].W;
+        if (priors_host) priors_host[c] = f->d.use_noise ? p64[c] : (double)hh[c].P;
+    }
+    return m.nchild;
+}
+
+extern "C" int az_forest_stats(az_forest* f, uint64_t* out8_host, int reset, void* stream) {
+    if (!f || !out8_host) return az_fail(AZ_EINVAL, "stats: null");
+    cudaStream_t s = (cudaStream_t)stream;
+    AZ_CUDA_OK(cudaStreamSynchronize(s));
+    std::vector<unsigned long long> all((size_t)f->d.n_trees * AZ_STAT_COUNT);
+    AZ_CUDA_OK(cudaMemcpy(all.data(), f->d.stats, all.size() * 8, cudaMemcpyDeviceToHost));
+    for (int k = 0; k < AZ_STAT_COUNT; ++k) out8_host[k] = 0;
+    for (size_t t = 0; t < (size_t)f->d.n_trees; ++t)
+        for (int k = 0; k < AZ_STAT_COUNT; ++k) out8_host[k] += all[t * AZ_STAT_COUNT + k];
+    if (reset) AZ_CUDA_OK(cudaMemset(f->d.stats, 0, all.size() * 8));
+    return AZ_OK;
+}
+
+extern "C" int az_forest_info(az_forest* f, int* n_trees, int* action_dim, int* planes, int* nw, int* cap) {
+    if (!f) return az_fail(AZ_EINVAL, "info: null");
+    if (n_trees) *n_trees = f->d.n_trees;
+    if (action_dim) *action_dim = f->d.g.action_dim;
+    if (planes) *planes = f->d.g.planes;
+    if (nw) *nw = f->d.g.nw;
+    if (cap) *cap = f->d.cap;
+    return AZ_OK;
+}
+
+// ---- batched rules (differential tests) ----------------------------------------------------
+extern "C" int az_rules_legal(int game, int rows, int cols, int n, const uint64_t* words_host,
+                              int32_t* out_counts_host, uint8_t* out_cells_host) {
+    AzGame g;
+    int rc = az_make_game(game, rows, cols, &g);
+    if (rc) return rc;
+    uint64_t *w = nullptr, *hd = nullptr;
+    int32_t* cnt = nullptr;
+    uint8_t *cells = nullptr, *scratch = nullptr;
+    std::vector<uint64_t> hashes(g.state_dim);
+    for (int i = 0; i < g.state_dim; ++i) hashes[i] = az_tuple2_hash(i / g.cols, i % g.cols);
+    AZ_CUDA_OK(cudaMalloc(&w, (size_t)n * 2 * g.nw * 8));
+    AZ_CUDA_OK(cudaMalloc(&hd, (size_t)g.state_dim * 8));
+    AZ_CUDA_OK(cudaMalloc(&cnt, (size_t)n * 4));
+    AZ_CUDA_OK(cudaMalloc(&cells, (size_t)n * g.state_dim));
+    AZ_CUDA_OK(cudaMalloc(&scratch, (size_t)n * 2 * (g.set_slots + 1)));
+    AZ_CUDA_OK(cudaMemcpy(w, words_host, (size_t)n * 2 * g.nw * 8, cudaMemcpyHostToDevice));
+    AZ_CUDA_OK(cudaMemcpy(hd, hashes.data(), (size_t)g.state_dim * 8, cudaMemcpyHostToDevice));
+    if (g.nw == 1) az_rules_legal_kernel<1><<<(n + 63) / 64, 64>>>(g, n, w, hd, cnt, cells, scratch);
+    else az_rules_legal_kernel<4><<<(n + 63) / 64, 64>>>(g, n, w, hd, cnt, cells, scratch);
+    AZ_CUDA_OK(cudaGetLastError());
+    AZ_CUDA_OK(cudaMemcpy(out_counts_host, cnt, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    AZ_CUDA_OK(cudaMemcpy(out_cells_host, cells, (size_t)n * g.state_dim, cudaMemcpyDeviceToHost));
+    cudaFree(w); cudaFree(hd); cudaFree(cnt); cudaFree(cells); cudaFree(scratch);
+    return AZ_OK;
+}
+
+extern "C" int az_rules_winner(int game, int rows, int cols, int n, const uint64_t* words_host,
+                               const int32_t* players_host, const int32_t* cells_host, int32_t* out_winner_host) {
+    AzGame g;
+    int rc = az_make_game(game, rows, cols, &g);
+    if (rc) return rc;
+    uint64_t* w = nullptr;
+    int32_t *pl = nullptr, *ce = nullptr, *out = nullptr;
+    AZ_CUDA_OK(cudaMalloc(&w, (size_t)n * 2 * g.nw * 8));
+    AZ_CUDA_OK(cudaMalloc(&pl, (size_t)n * 4));
+    AZ_CUDA_OK(cudaMalloc(&ce, (size_t)n * 4));
+    AZ_CUDA_OK(cudaMalloc(&out, (size_t)n * 4));
+    AZ_CUDA_OK(cudaMemcpy(w, words_host, (size_t)n * 2 * g.nw * 8, cudaMemcpyHostToDevice));
+    AZ_CUDA_OK(cudaMemcpy(pl, players_host, (size_t)n * 4, cudaMemcpyHostToDevice));
+    AZ_CUDA_OK(cudaMemcpy(ce, cells_host, (size_t)n * 4, cudaMemcpyHostToDevice));
+    if (g.nw == 1) az_rules_winner_kernel<1><<<(n + 127) / 128, 128>>>(g, n, w, pl, ce, out);
+    else az_rules_winner_kernel<4><<<(n + 127) / 128, 128>>>(g, n, w, pl, ce, out);
+    AZ_CUDA_OK(cudaGetLastError());
+    AZ_CUDA_OK(cudaMemcpy(out_winner_host, out, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    cudaFree(w); cudaFree(pl); cudaFree(ce); cudaFree(out);
+    return AZ_OK;
+}

@@ -1,0 +1,70 @@
+// Device-side view of a forest of concurrent search trees (one per game) in HBM.
+//
+// Layout (SoA across node fields, grouped by access pattern):
+//   hot [tree*cap + i]   AzHot  {W f64, P f32, N i32}  -- 16 B, one vector load per child in PUCT
+//   meta[tree*cap + i]   AzMeta {child_base, action, nchild, status} -- 8 B, selected child only
+//   vlc [tree*cap + i]   u8 virtual-loss count (only touched when vl > 1)
+// Children of a node are contiguous (bump allocator per tree), in the reference's child
+// order (= order of Game.get_valid_moves, ai/node.py:55-59).  Node 0 is the root.
+#pragma once
+#include <cuda_runtime.h>
+#include "az_types.h"
+
+// counters in AzForestDev::stats
+#define AZ_STAT_SIMS 0        // completed simulations (iterations of ai/mcts.py:16)
+#define AZ_STAT_TERMINAL 1    // ... of which ended on a terminal node
+#define AZ_STAT_EXPAND 2      // expansions (= evaluations consumed)
+#define AZ_STAT_CHILDREN 3    // children created
+#define AZ_STAT_SELECT 4      // select steps (edges walked)
+#define AZ_STAT_CHILD_READS 5 // children scored in select
+#define AZ_STAT_COLLIDE 6     // virtual-loss batches cut short by a pending leaf
+#define AZ_STAT_COUNT 8
+
+struct AzForestDev {
+    AzGame g;
+    int n_trees;
+    int cap;          // nodes per tree
+    int iters;        // simulations per move (mcts_iterations)
+    int vl;           // leaves per tree per step (1 = the reference's sequential search)
+    int max_depth;    // path entries per leaf
+    int max_leaves;   // n_trees * vl
+    int use_noise;    // Dirichlet noise mixed into the root priors (utils.py:12-27)
+
+    AzHot* hot;
+    AzMeta* meta;
+    uint8_t* vlc;
+
+    // per tree
+    uint64_t* root_words;    // [n_trees][2*nw]  side-0 words then side-1 words
+    uint8_t* root_player;    // side to move at the root
+    uint16_t* root_mc;       // moves played so far
+    uint8_t* active;         // tree takes part in the search
+    int* n_nodes;            // bump allocator
+    int* sims_done;
+    uint8_t* n_pending;
+    uint8_t* done_flag;
+
+    // pending leaves [n_trees][vl]
+    uint32_t* path;          // [n_trees][vl][max_depth]
+    uint16_t* path_len;
+    int* leaf_slot;
+    uint64_t* pend_words;    // [n_trees][vl][2*nw]  leaf position (side 0, side 1)
+    uint8_t* pend_player;
+    uint16_t* pend_mc;
+
+    // evaluation batch (compacted)
+    int* n_leaves;           // device counter, zeroed before every advance
+    int* n_done;             // trees that finished all their simulations
+    uint64_t* leaf_words;    // [max_leaves][2*nw]  canonical: mine, theirs
+    uint8_t* leaf_player;    // side to move (plane 2 of the 3-plane games)
+    int* leaf_tree;
+    float* priors;           // [max_leaves][A]  exp(l)/sum(exp(l)), unmasked (ai/mcts.py:49)
+    float* values;           // [max_leaves]
+
+    // root noise
+    const double* root_noise;  // [n_trees][A] or nullptr
+    double* root_prior64;      // [n_trees][max_children]  f64 priors of root children
+
+    const uint64_t* cell_hash; // CPython hash((r,c)) per cell (Gomoku child order)
+    unsigned long long* stats; // AZ_STAT_*
+};

@@ -1,0 +1,154 @@
+// Bitboard rules of TicTacToe / Connect4 / Gomoku for sm_100a device code.
+//
+// Restates, on side bitboards (bit r*cols+c), what the reference computes on float planes:
+//   make_move / undo_move   games/tictactoe.py:36-51  connect4.py:55-70  gomoku.py:50-63
+//   check_winner            games/tictactoe.py:53-79  connect4.py:72-98  gomoku.py:65-91
+//   get_valid_moves (ORDER) games/tictactoe.py:81-83  connect4.py:43-53  gomoku.py:93-106
+// The Gomoku legal list is `list(set)` in the reference, i.e. CPython set slot order; the
+// emulation below follows CPython 3.12 Objects/setobject.c (set_add_entry,
+// set_table_resize, set_insert_clean) with the tuple hashes supplied by the host.
+#pragma once
+#include "az_types.h"
+
+#ifdef __CUDA_ARCH__
+#define AZ_CTZ64(x) (__ffsll((long long)(x)) - 1)
+#else
+#define AZ_CTZ64(x) __builtin_ctzll(x)
+#endif
+
+template <int NW>
+struct AzBoard {
+    uint64_t w[2][NW];   // w[player][word]
+
+    __host__ __device__ __forceinline__ bool has(int p, int cell) const {
+        return (w[p][NW == 1 ? 0 : (cell >> 6)] >> (cell & 63)) & 1ull;
+    }
+    __host__ __device__ __forceinline__ bool empty(int cell) const {
+        const int i = NW == 1 ? 0 : (cell >> 6);
+        return !(((w[0][i] | w[1][i]) >> (cell & 63)) & 1ull);
+    }
+    __host__ __device__ __forceinline__ void put(int p, int cell) {
+        w[p][NW == 1 ? 0 : (cell >> 6)] |= 1ull << (cell & 63);
+    }
+    __host__ __device__ __forceinline__ void clear(int p, int cell) {
+        w[p][NW == 1 ? 0 : (cell >> 6)] &= ~(1ull << (cell & 63));
+    }
+};
+
+// Run of `p` stones through `cell` along +-(dr,dc), `cell` counted as 1.
+template <int NW>
+__host__ __device__ __forceinline__ int az_run_length(const AzGame& g, const AzBoard<NW>& b, int p,
+                                                      int r0, int c0, int dr, int dc) {
+    int n = 1;
+#pragma unroll
+    for (int s = 1; s >= -1; s -= 2) {
+        int r = r0 + s * dr, c = c0 + s * dc;
+        while (r >= 0 && r < g.rows && c >= 0 && c < g.cols && b.has(p, r * g.cols + c)) {
+            ++n;
+            r += s * dr;
+            c += s * dc;
+        }
+    }
+    return n;
+}
+
+// true iff player p, who just played `cell`, has a run >= k through it (overlines count).
+template <int NW>
+__host__ __device__ __forceinline__ bool az_is_win(const AzGame& g, const AzBoard<NW>& b, int p, int cell) {
+    const int r = cell / g.cols, c = cell - r * g.cols;
+    return az_run_length(g, b, p, r, c, 0, 1) >= g.k || az_run_length(g, b, p, r, c, 1, 0) >= g.k ||
+           az_run_length(g, b, p, r, c, 1, 1) >= g.k || az_run_length(g, b, p, r, c, 1, -1) >= g.k;
+}
+
+// Index into the policy vector of a move stored as a cell: games/*: get_action_idx.
+__host__ __device__ __forceinline__ int az_action_index(const AzGame& g, int cell) {
+    return g.gid == AZ_GAME_CONNECT4 ? cell % g.cols : cell;
+}
+
+// ---- CPython set emulation -------------------------------------------------------------
+// One probe sequence of set_add_entry / set_insert_clean: home slot, up to 9 linear probes
+// when they fit below the mask, then i = 5i + 1 + (perturb >>= 5).
+__host__ __device__ __forceinline__ bool az_set_insert(uint8_t* tab, uint32_t mask, uint8_t x, uint64_t h,
+                                                       bool check_dup) {
+    uint64_t perturb = h;
+    uint64_t i = h & mask;
+    for (;;) {
+        const int lim = (i + 9 <= mask) ? 9 : 0;
+        for (int j = 0; j <= lim; ++j) {
+            const uint8_t e = tab[i + j];
+            if (e == 0xFF) {
+                tab[i + j] = x;
+                return true;
+            }
+            if (check_dup && e == x) return false;
+        }
+        perturb >>= 5;
+        i = (i * 5 + 1 + perturb) & mask;
+    }
+}
+
+// Legal moves (as cells) in the reference's child order, computed by ONE thread.
+// tab_a / tab_b: scratch of g.set_slots bytes each (Gomoku only).  Returns the count.
+template <int NW>
+__host__ __device__ inline int az_legal_moves(const AzGame& g, const AzBoard<NW>& b,
+                                              const uint64_t* __restrict__ cell_hash, uint8_t* tab_a,
+                                              uint8_t* tab_b, uint8_t* out) {
+    int n = 0;
+    if (g.gid == AZ_GAME_TICTACTOE) {
+        for (int cell = 0; cell < g.state_dim; ++cell)
+            if (b.empty(cell)) out[n++] = (uint8_t)cell;
+        return n;
+    }
+    if (g.gid == AZ_GAME_CONNECT4) {
+        for (int c = 0; c < g.cols; ++c) {
+            if (!b.empty(c)) continue;                      // top cell taken: column full
+            int r = g.rows - 1;
+            while (!b.empty(r * g.cols + c)) --r;           // lowest empty row (row 0 = top)
+            out[n++] = (uint8_t)(r * g.cols + c);
+        }
+        return n;
+    }
+    // Gomoku: empty 8-neighbours of every stone, inserted in the reference's scan order.
+    uint8_t* tab = tab_a;
+    uint8_t* spare = tab_b;
+    uint32_t mask = 7;
+    int fill = 0;
+    for (int i = 0; i < 8; ++i) tab[i] = 0xFF;
+    const int ddr[4] = {0, 1, 1, 1}, ddc[4] = {1, 0, 1, -1};
+    for (int wi = 0; wi < NW; ++wi) {
+        uint64_t occ = b.w[0][wi] | b.w[1][wi];
+        while (occ) {
+            const int cell = wi * 64 + AZ_CTZ64(occ);
+            occ &= occ - 1;
+            const int r = cell / g.cols, c = cell - r * g.cols;
+            for (int d = 0; d < 4; ++d) {
+                for (int s = 1; s >= -1; s -= 2) {
+                    const int rr = r + s * ddr[d], cc = c + s * ddc[d];
+                    if (rr < 0 || rr >= g.rows || cc < 0 || cc >= g.cols) continue;
+                    const int x = rr * g.cols + cc;
+                    if (!b.empty(x)) continue;
+                    if (!az_set_insert(tab, mask, (uint8_t)x, cell_hash[x], true)) continue;
+                    ++fill;
+                    if ((uint32_t)fill * 5 >= mask * 3) {   // grow: smallest 2^k > 4*used
+                        uint32_t newsize = 8;
+                        while (newsize <= (uint32_t)fill * 4) newsize <<= 1;
+                        for (uint32_t i = 0; i < newsize; ++i) spare[i] = 0xFF;
+                        for (uint32_t i = 0; i <= mask; ++i)
+                            if (tab[i] != 0xFF) az_set_insert(spare, newsize - 1, tab[i], cell_hash[tab[i]], false);
+                        uint8_t* t = tab;
+                        tab = spare;
+                        spare = t;
+                        mask = newsize - 1;
+                    }
+                }
+            }
+        }
+    }
+    if (fill == 0) {                                        // empty board: centre (gomoku.py:104-105)
+        out[0] = (uint8_t)((g.rows / 2) * g.cols + g.cols / 2);
+        return 1;
+    }
+    for (uint32_t i = 0; i <= mask; ++i)
+        if (tab[i] != 0xFF) out[n++] = tab[i];
+    return n;
+}

@@ -1,0 +1,77 @@
+"""ctypes binding of libaz_b200.so -- the C ABI declared in include/az_b200.h.
+
+Fails loudly when the CUDA library is missing or a call fails; there is no CPU path.
+"""
+import ctypes as C
+import os
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(PKG, "libaz_b200.so")
+
+AZ_OK = 0
+GAME_IDS = {"tictactoe": 0, "connect4": 1, "gomoku": 2}
+
+vp, i32, u64 = C.c_void_p, C.c_int, C.c_uint64
+_SIGS = {
+    "az_version": (C.c_char_p, []),
+    "az_last_error": (C.c_char_p, []),
+    "az_forest_create": (i32, [i32, i32, i32, i32, i32, i32, C.POINTER(vp)]),
+    "az_forest_destroy": (None, [vp]),
+    "az_forest_set_roots_planes": (i32, [vp, vp, vp, vp, vp]),
+    "az_forest_set_roots_words": (i32, [vp, vp, vp, vp, vp]),
+    "az_forest_set_active": (i32, [vp, vp, vp]),
+    "az_forest_set_noise": (i32, [vp, vp, vp]),
+    "az_forest_begin_move": (i32, [vp, i32, vp]),
+    "az_forest_advance": (i32, [vp, vp]),
+    "az_forest_counts": (i32, [vp, C.POINTER(i32), C.POINTER(i32), vp]),
+    "az_eval_hash": (i32, [vp, u64, i32, vp]),
+    "az_leaves_to_planes": (i32, [vp, vp, i32, vp]),
+    "az_leaves_set_logits": (i32, [vp, vp, vp, i32, vp]),
+    "az_forest_search_hash": (i32, [vp, i32, u64, i32, vp]),
+    "az_forest_root_visits": (i32, [vp, vp, vp, vp]),
+    "az_forest_root_children": (i32, [vp, i32, i32, vp, vp, vp, vp, C.POINTER(i32), C.POINTER(C.c_double), vp]),
+    "az_forest_stats": (i32, [vp, vp, i32, vp]),
+    "az_forest_info": (i32, [vp] + [C.POINTER(i32)] * 5),
+    "az_rules_legal": (i32, [i32, i32, i32, i32, vp, vp, vp]),
+    "az_rules_winner": (i32, [i32, i32, i32, i32, vp, vp, vp, vp]),
+}
+# entry points added by later translation units; bound when present in the header
+_OPTIONAL = {}
+
+_lib = None
+
+
+class AzError(RuntimeError):
+    pass
+
+
+def declared_symbols():
+    """Every function name include/az_b200.h declares (used by the CPU export test)."""
+    import re
+    hdr = os.path.join(os.path.dirname(PKG), "include", "az_b200.h")
+    text = open(hdr).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(az_[a-z0-9_]+)\s*\(", text)))
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise AzError(f"{SO_PATH} is missing: run `python __graft_entry__.py build` "
+                      "(nvcc, sm_100a). There is no CPU fallback.")
+    L = C.CDLL(SO_PATH)
+    for table in (_SIGS, _OPTIONAL):
+        for name, (res, args) in table.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+    _lib = L
+    return L
+
+
+def check(rc, what=""):
+    if rc < 0:
+        raise AzError(f"{what} failed ({rc}): {load().az_last_error().decode()}")
+    return rc
