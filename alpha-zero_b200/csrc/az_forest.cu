@@ -458,7 +458,7 @@ int az_make_game(int game, int rows, int cols, AzGame* out) {
         return az_fail(AZ_EINVAL, "unknown game id");
     }
     g.state_dim = rows * cols;
-    g.nw = (g.state_dim + 63) / 64;
+    g.nw = g.state_dim <= 64 ? 1 : AZ_MAX_WORDS;   // kernels are instantiated for 1 and 4 words
     g.set_slots = 0;
     if (game == AZ_GAME_GOMOKU) {                 // largest table a CPython set of <= cells items reaches
         int size = 8;

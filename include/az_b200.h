@@ -17,6 +17,8 @@
 extern "C" {
 #endif
 
+#define AZ_API __attribute__((visibility("default")))
+
 #define AZ_OK 0
 #define AZ_EINVAL (-1)
 #define AZ_ECUDA (-2)
@@ -30,68 +32,69 @@ extern "C" {
 typedef struct az_forest az_forest;
 typedef struct az_net az_net;
 
-const char* az_version(void);
-const char* az_last_error(void);
+AZ_API const char* az_version(void);
+AZ_API const char* az_last_error(void);
 
 /* ---- forest of search trees: replaces ai/node.py:20-40 (Node objects) ----------------- */
 /* rows/cols: 3x3, 6x7, or n x n Gomoku (n <= 15; the reference's class attrs, gomoku.py:10).
  * max_iters bounds mcts_iterations of later searches (node pool = 1 + max_iters*max_children
  * per tree); vl_batch = leaves per tree per step (1 = the reference's sequential search). */
-int az_forest_create(int game, int rows, int cols, int n_trees, int max_iters, int vl_batch, az_forest** out);
-void az_forest_destroy(az_forest* f);
+AZ_API int az_forest_create(int game, int rows, int cols, int n_trees, int max_iters, int vl_batch, az_forest** out);
+AZ_API void az_forest_destroy(az_forest* f);
 
 /* Root positions.  planes_host: float32 [n_trees][C][rows][cols] exactly as the reference
  * holds boards (Game().board, games/gomoku.py:16-17); players / move_counts as int32. */
-int az_forest_set_roots_planes(az_forest* f, const float* planes_host, const int32_t* players_host,
+AZ_API int az_forest_set_roots_planes(az_forest* f, const float* planes_host, const int32_t* players_host,
                                const int32_t* move_counts_host, void* stream);
-/* Same from side bitboards: words_host uint64 [n_trees][2][nw], bit r*cols+c. */
-int az_forest_set_roots_words(az_forest* f, const uint64_t* words_host, const int32_t* players_host,
+/* Same from side bitboards: words_host uint64 [n_trees][2][nw], bit (r*cols+c)%64 of word
+ * (r*cols+c)/64; nw = 1 for boards of <= 64 cells, else 4 (az_forest_info reports it). */
+AZ_API int az_forest_set_roots_words(az_forest* f, const uint64_t* words_host, const int32_t* players_host,
                               const int32_t* move_counts_host, void* stream);
 /* active_host: uint8 [n_trees] (NULL = all active). */
-int az_forest_set_active(az_forest* f, const uint8_t* active_host, void* stream);
+AZ_API int az_forest_set_active(az_forest* f, const uint8_t* active_host, void* stream);
 /* Dirichlet noise for the root priors, float64 [n_trees][A] playing the role of
  * np.random.dirichlet in utils.py:21; NULL turns noise off (dirichlet=False, mcts.py:11). */
-int az_forest_set_noise(az_forest* f, const double* noise_host, void* stream);
+AZ_API int az_forest_set_noise(az_forest* f, const double* noise_host, void* stream);
 
 /* ---- one search: replaces MCTS.mcts, ai/mcts.py:11-60 ------------------------------------ */
 /* Fresh roots (no subtree reuse, gomoku.py:134) and `iters` simulations per tree. */
-int az_forest_begin_move(az_forest* f, int iters, void* stream);
+AZ_API int az_forest_begin_move(az_forest* f, int iters, void* stream);
 /* Apply the evaluator's answers (expand + backup, node.py:50-74) and select the next
  * leaves (node.py:42-47, utils.py:29-44).  Fills the evaluation batch. */
-int az_forest_advance(az_forest* f, void* stream);
+AZ_API int az_forest_advance(az_forest* f, void* stream);
 /* Synchronises `stream`; returns the size of the evaluation batch and finished trees. */
-int az_forest_counts(az_forest* f, int* n_leaves, int* n_done, void* stream);
+AZ_API int az_forest_counts(az_forest* f, int* n_leaves, int* n_done, void* stream);
 
 /* Evaluators (the `model(...)` call + softmax glue of ai/mcts.py:46-49): */
 /* (a) build-defined exact hash evaluator shared with the oracle (parity runs); */
-int az_eval_hash(az_forest* f, uint64_t seed, int qbits, void* stream);
+AZ_API int az_eval_hash(az_forest* f, uint64_t seed, int qbits, void* stream);
 /* (b) external evaluator: canonical leaves as float32 planes [max_b][C][rows][cols] ... */
-int az_leaves_to_planes(az_forest* f, float* planes_dev, int max_b, void* stream);
+AZ_API int az_leaves_to_planes(az_forest* f, float* planes_dev, int max_b, void* stream);
 /* ... and its logits [max_b][A], values [max_b] back (softmax as mcts.py:49); */
-int az_leaves_set_logits(az_forest* f, const float* logits_dev, const float* values_dev, int max_b, void* stream);
+AZ_API int az_leaves_set_logits(az_forest* f, const float* logits_dev, const float* values_dev, int max_b, void* stream);
 /* (c) the built-in policy/value net, az_net_* below. */
 
 /* Whole search with the hash evaluator, host loop inside the library. */
-int az_forest_search_hash(az_forest* f, int iters, uint64_t seed, int qbits, void* stream);
+AZ_API int az_forest_search_hash(az_forest* f, int iters, uint64_t seed, int qbits, void* stream);
 
 /* ---- results: replaces utils.get_probablity_distribution_of_children (utils.py:46-55),
  *      root.value/root.visit (gomoku.py:141) and reads of root.children (test.py:44-46) ---- */
-int az_forest_root_visits(az_forest* f, int32_t* visits_host /*[n_trees][A]*/, double* q_host /*[n_trees]*/,
+AZ_API int az_forest_root_visits(az_forest* f, int32_t* visits_host /*[n_trees][A]*/, double* q_host /*[n_trees]*/,
                           void* stream);
 /* Children of one root in child order: cell = r*cols+c of prevAction. Returns the count. */
-int az_forest_root_children(az_forest* f, int tree, int max_children, int32_t* cells_host, int32_t* visits_host,
+AZ_API int az_forest_root_children(az_forest* f, int tree, int max_children, int32_t* cells_host, int32_t* visits_host,
                             double* values_host, double* priors_host, int32_t* root_visit, double* root_value,
                             void* stream);
 /* counters: [sims, terminal sims, expansions, children, selects, children scored, collisions, -] */
-int az_forest_stats(az_forest* f, uint64_t* out8_host, int reset, void* stream);
-int az_forest_info(az_forest* f, int* n_trees, int* action_dim, int* planes, int* nw, int* cap);
+AZ_API int az_forest_stats(az_forest* f, uint64_t* out8_host, int reset, void* stream);
+AZ_API int az_forest_info(az_forest* f, int* n_trees, int* action_dim, int* planes, int* nw, int* cap);
 
 /* ---- batched rules for differential tests: games/*.py get_valid_moves / check_winner ---- */
 /* words_host uint64 [n][2][nw]; out_counts int32 [n]; out_cells uint8 [n][rows*cols]. */
-int az_rules_legal(int game, int rows, int cols, int n, const uint64_t* words_host, int32_t* out_counts_host,
+AZ_API int az_rules_legal(int game, int rows, int cols, int n, const uint64_t* words_host, int32_t* out_counts_host,
                    uint8_t* out_cells_host);
 /* After `player` played `cell`: winner id or -1 (check_winner). */
-int az_rules_winner(int game, int rows, int cols, int n, const uint64_t* words_host, const int32_t* players_host,
+AZ_API int az_rules_winner(int game, int rows, int cols, int n, const uint64_t* words_host, const int32_t* players_host,
                     const int32_t* cells_host, int32_t* out_winner_host);
 
 #ifdef __cplusplus
