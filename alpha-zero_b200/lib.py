@@ -34,6 +34,7 @@ _SIGS = {
     "az_forest_info": (i32, [vp] + [C.POINTER(i32)] * 5),
     "az_rules_legal": (i32, [i32, i32, i32, i32, vp, vp, vp]),
     "az_rules_winner": (i32, [i32, i32, i32, i32, vp, vp, vp, vp]),
+    "az_gemm_bf16": (i32, [vp, i32, vp, vp, vp, i32, vp, i32, i32, i32, i32, i32, vp]),
 }
 # entry points added by later translation units; bound when present in the header
 _OPTIONAL = {}

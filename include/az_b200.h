@@ -97,6 +97,13 @@ AZ_API int az_rules_legal(int game, int rows, int cols, int n, const uint64_t* w
 AZ_API int az_rules_winner(int game, int rows, int cols, int n, const uint64_t* words_host, const int32_t* players_host,
                     const int32_t* cells_host, int32_t* out_winner_host);
 
+/* ---- policy/value network: replaces Net.forward (ai/nn.py:63-84) + softmax (ai/mcts.py:49) ---- */
+/* Tensor-core GEMM building block, exposed for parity tests: out[M][N] (bf16, row stride ldo)
+ * = epi(A[M][K] (bf16, row stride lda) * W[N][K]^T + bias[N] (fp32)); epi 0 = none, 1 = exact
+ * GELU, 2 = + resid[M][ldr].  All pointers are device memory; N, K multiples of 64. */
+AZ_API int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const float* bias_dev, const void* resid_dev,
+                        int ldr, void* out_dev, int ldo, int M, int N, int K, int epi, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
