@@ -852,6 +852,26 @@ extern "C" int az_forest_root_children(az_forest* f, int tree, int max_children,
     return m.nchild;
 }
 
+extern "C" int az_forest_read_leaves(az_forest* f, int max_n, uint64_t* words_host, uint8_t* players_host,
+                                     int32_t* trees_host, float* priors_host, float* values_host, void* stream) {
+    if (!f) return az_fail(AZ_EINVAL, "read_leaves: null");
+    cudaStream_t s = (cudaStream_t)stream;
+    int n = 0;
+    int rc = az_forest_counts(f, &n, nullptr, stream);
+    if (rc) return rc;
+    n = std::min(n, max_n);
+    const int nw = f->d.g.nw, A = f->d.g.action_dim;
+    if (n > 0) {
+        if (words_host) AZ_CUDA_OK(cudaMemcpyAsync(words_host, f->d.leaf_words, (size_t)n * 2 * nw * 8, cudaMemcpyDeviceToHost, s));
+        if (players_host) AZ_CUDA_OK(cudaMemcpyAsync(players_host, f->d.leaf_player, (size_t)n, cudaMemcpyDeviceToHost, s));
+        if (trees_host) AZ_CUDA_OK(cudaMemcpyAsync(trees_host, f->d.leaf_tree, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+        if (priors_host) AZ_CUDA_OK(cudaMemcpyAsync(priors_host, f->d.priors, (size_t)n * A * 4, cudaMemcpyDeviceToHost, s));
+        if (values_host) AZ_CUDA_OK(cudaMemcpyAsync(values_host, f->d.values, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+        AZ_CUDA_OK(cudaStreamSynchronize(s));
+    }
+    return n;
+}
+
 extern "C" int az_forest_stats(az_forest* f, uint64_t* out8_host, int reset, void* stream) {
     if (!f || !out8_host) return az_fail(AZ_EINVAL, "stats: null");
     cudaStream_t s = (cudaStream_t)stream;

@@ -123,3 +123,430 @@ extern "C" int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const
     a.m_count = nullptr;
     return az_launch_gemm(ta, tb, a, epi, M, (cudaStream_t)stream);
 }
+
+// ======================================================================================
+// The network object
+// ======================================================================================
+#include "az_net_kernels.cuh"
+
+struct AzBlockW {
+    float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
+    bf16 *w_in = nullptr, *w_out = nullptr, *w1 = nullptr, *w2 = nullptr;
+    float *b_in = nullptr, *b_out = nullptr, *b1 = nullptr, *b2 = nullptr;
+    CUtensorMap tm_in, tm_q, tm_kv, tm_out, tm_w1, tm_w2;
+};
+
+struct az_net {
+    int rows = 0, cols = 0, C = 0, patch = 0, D = 0, H = 0, L = 0, A = 0, T = 0;
+    int chunk = 0;                       // boards per pass through the activation buffers
+    bool finalized = false;
+    std::vector<void*> allocs;
+    std::map<std::string, std::vector<float>> host;   // raw fp32 parameters until finalize
+    // embedding
+    bf16* wt_embed = nullptr;
+    float* posb = nullptr;
+    std::vector<AzBlockW> blk;
+    float *lnf_g = nullptr, *lnf_b = nullptr, *w_pol = nullptr, *b_pol = nullptr, *w_val = nullptr, *b_val = nullptr;
+    // activations (one chunk)
+    bf16 *x = nullptr, *xn = nullptr, *qkv = nullptr, *ao = nullptr, *hbuf = nullptr;
+    bf16 *qc = nullptr, *oc = nullptr, *xc = nullptr, *xcn = nullptr, *hc = nullptr, *xc2 = nullptr;
+    CUtensorMap tm_xn, tm_ao, tm_hbuf, tm_xn_cls, tm_oc, tm_xcn, tm_hc;
+    // scratch for the stand-alone forward (planes in, logits out)
+    uint64_t* in_words = nullptr;
+    uint8_t* in_player = nullptr;
+    float *out_priors = nullptr, *out_values = nullptr, *out_logits = nullptr;
+    unsigned long long launches = 0;     // kernels launched by forward passes
+};
+
+template <typename T>
+static int az_net_alloc(az_net* n, T** p, size_t count) {
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, count * sizeof(T) + 256);
+    if (e != cudaSuccess) return az_fail(AZ_ENOMEM, std::string("net cudaMalloc: ") + cudaGetErrorString(e));
+    n->allocs.push_back(q);
+    *p = reinterpret_cast<T*>(q);
+    return AZ_OK;
+}
+
+static int az_upload_f32(az_net* n, float** dst, const std::vector<float>& v) {
+    int rc = az_net_alloc(n, dst, v.size());
+    if (rc) return rc;
+    AZ_CUDA_OK(cudaMemcpy(*dst, v.data(), v.size() * 4, cudaMemcpyHostToDevice));
+    return AZ_OK;
+}
+
+static int az_upload_bf16(az_net* n, bf16** dst, const float* v, size_t count) {
+    std::vector<bf16> tmp(count);
+    for (size_t i = 0; i < count; ++i) tmp[i] = __float2bfloat16(v[i]);
+    int rc = az_net_alloc(n, dst, count);
+    if (rc) return rc;
+    AZ_CUDA_OK(cudaMemcpy(*dst, tmp.data(), count * 2, cudaMemcpyHostToDevice));
+    return AZ_OK;
+}
+
+extern "C" int az_net_create(int rows, int cols, int planes, int patch, int embed_dim, int num_heads, int depth,
+                             int action_dim, int max_batch, az_net** out) {
+    if (!out || rows <= 0 || cols <= 0 || planes < 2 || planes > 3 || patch <= 0 || !(patch & 1) || depth < 1 ||
+        action_dim <= 0 || max_batch <= 0)
+        return az_fail(AZ_EINVAL, "az_net_create: bad arguments");
+    if (embed_dim % 64 || embed_dim > 1024) return az_fail(AZ_EINVAL, "az_net_create: embed_dim must be a multiple of 64, <= 1024");
+    if (num_heads <= 0 || embed_dim % num_heads || embed_dim / num_heads > 128)
+        return az_fail(AZ_EINVAL, "az_net_create: head dim must divide embed_dim and be <= 128");
+    if (rows * cols + 1 > 256) return az_fail(AZ_EINVAL, "az_net_create: at most 255 board cells");
+    az_net* n = new az_net();
+    n->rows = rows; n->cols = cols; n->C = planes; n->patch = patch; n->D = embed_dim; n->H = num_heads;
+    n->L = depth; n->A = action_dim; n->T = rows * cols + 1;
+    n->chunk = max_batch < 4096 ? max_batch : 4096;
+    n->blk.resize(depth);
+    *out = n;
+    return AZ_OK;
+}
+
+extern "C" int az_net_invalidate_graphs(az_net* n);
+extern "C" void az_net_destroy(az_net* n) {
+    if (!n) return;
+    az_net_invalidate_graphs(n);
+    for (void* p : n->allocs) cudaFree(p);
+    delete n;
+}
+
+// Parameters arrive under their state_dict names (ai/nn.py module tree), fp32, host memory.
+extern "C" int az_net_set_param(az_net* n, const char* name, const float* data_host, long long numel) {
+    if (!n || !name || !data_host || numel <= 0) return az_fail(AZ_EINVAL, "az_net_set_param: bad arguments");
+    n->host[name] = std::vector<float>(data_host, data_host + numel);
+    n->finalized = false;
+    return AZ_OK;
+}
+
+static const std::vector<float>* az_param(az_net* n, const std::string& name, size_t numel, std::string* err) {
+    auto it = n->host.find(name);
+    if (it == n->host.end()) { *err = "missing parameter " + name; return nullptr; }
+    if (it->second.size() != numel) { *err = "parameter " + name + " has wrong size"; return nullptr; }
+    return &it->second;
+}
+
+// Converts the fp32 state_dict into device layouts, allocates one chunk of activations and
+// encodes the TMA descriptors.  Call again after az_net_set_param to refresh the weights.
+extern "C" int az_net_finalize(az_net* n) {
+    if (!n) return az_fail(AZ_EINVAL, "az_net_finalize: null");
+    az_net_invalidate_graphs(n);
+    for (void* p : n->allocs) cudaFree(p);
+    n->allocs.clear();
+    const int D = n->D, T = n->T, C = n->C, P = n->patch, A = n->A, cells = n->rows * n->cols;
+    std::string err;
+    int rc;
+#define AZ_P(var, name, numel)                                      \
+    const std::vector<float>* var = az_param(n, name, numel, &err); \
+    if (!var) return az_fail(AZ_EINVAL, "az_net_finalize: " + err);
+    // ---- embedding: conv weight [D][C][P][P] -> channel-last [C*P*P][D]; pos/bias tables
+    AZ_P(cw, "embedding.patch_embed.patch_embed.weight", (size_t)D * C * P * P)
+    AZ_P(cb, "embedding.patch_embed.patch_embed.bias", (size_t)D)
+    AZ_P(cls, "embedding.cls_token", (size_t)D)
+    AZ_P(pos, "embedding.pos_embedding", (size_t)T * D)
+    {
+        std::vector<float> wt((size_t)C * P * P * D);
+        for (int d = 0; d < D; ++d)
+            for (int k = 0; k < C * P * P; ++k) wt[(size_t)k * D + d] = (*cw)[(size_t)d * C * P * P + k];
+        if ((rc = az_upload_bf16(n, &n->wt_embed, wt.data(), wt.size()))) return rc;
+        // the kernel sums bf16-rounded weights: build the tables from the same rounded values
+        std::vector<float> posb((size_t)2 * T * D);
+        for (int stm = 0; stm < 2; ++stm)
+            for (int t = 0; t < T; ++t)
+                for (int d = 0; d < D; ++d) {
+                    float v = (*pos)[(size_t)t * D + d];
+                    if (t == 0) v += (*cls)[d];
+                    else {
+                        v += (*cb)[d];
+                        if (stm == 1 && C == 3) {          // plane 2 is all ones: every in-bounds tap contributes
+                            const int r = (t - 1) / n->cols, c = (t - 1) % n->cols;
+                            for (int kr = 0; kr < P; ++kr)
+                                for (int kc = 0; kc < P; ++kc) {
+                                    const int rr = r + kr - P / 2, cc = c + kc - P / 2;
+                                    if (rr < 0 || rr >= n->rows || cc < 0 || cc >= n->cols) continue;
+                                    v += __bfloat162float(__float2bfloat16(wt[(size_t)((2 * P + kr) * P + kc) * D + d]));
+                                }
+                        }
+                    }
+                    posb[((size_t)stm * T + t) * D + d] = v;
+                }
+        if ((rc = az_upload_f32(n, &n->posb, posb))) return rc;
+    }
+    // ---- blocks
+    for (int l = 0; l < n->L; ++l) {
+        AzBlockW& w = n->blk[l];
+        const std::string p = "blocks." + std::to_string(l) + ".";
+        AZ_P(g1, p + "norm1.weight", (size_t)D) AZ_P(be1, p + "norm1.bias", (size_t)D)
+        AZ_P(g2, p + "norm2.weight", (size_t)D) AZ_P(be2, p + "norm2.bias", (size_t)D)
+        AZ_P(wi, p + "attn.in_proj_weight", (size_t)3 * D * D) AZ_P(bi, p + "attn.in_proj_bias", (size_t)3 * D)
+        AZ_P(wo, p + "attn.out_proj.weight", (size_t)D * D) AZ_P(bo, p + "attn.out_proj.bias", (size_t)D)
+        AZ_P(w1, p + "mlp.0.weight", (size_t)4 * D * D) AZ_P(bb1, p + "mlp.0.bias", (size_t)4 * D)
+        AZ_P(w2, p + "mlp.3.weight", (size_t)4 * D * D) AZ_P(bb2, p + "mlp.3.bias", (size_t)D)
+        if ((rc = az_upload_f32(n, &w.ln1_g, *g1)) || (rc = az_upload_f32(n, &w.ln1_b, *be1)) ||
+            (rc = az_upload_f32(n, &w.ln2_g, *g2)) || (rc = az_upload_f32(n, &w.ln2_b, *be2)) ||
+            (rc = az_upload_f32(n, &w.b_in, *bi)) || (rc = az_upload_f32(n, &w.b_out, *bo)) ||
+            (rc = az_upload_f32(n, &w.b1, *bb1)) || (rc = az_upload_f32(n, &w.b2, *bb2)) ||
+            (rc = az_upload_bf16(n, &w.w_in, wi->data(), wi->size())) || (rc = az_upload_bf16(n, &w.w_out, wo->data(), wo->size())) ||
+            (rc = az_upload_bf16(n, &w.w1, w1->data(), w1->size())) || (rc = az_upload_bf16(n, &w.w2, w2->data(), w2->size())))
+            return rc;
+        if ((rc = az_make_tmap(&w.tm_in, w.w_in, 3 * D, D, D, az_pick_bn(3 * D))) ||
+            (rc = az_make_tmap(&w.tm_q, w.w_in, D, D, D, az_pick_bn(D))) ||
+            (rc = az_make_tmap(&w.tm_kv, w.w_in + (size_t)D * D, 2 * D, D, D, az_pick_bn(2 * D))) ||
+            (rc = az_make_tmap(&w.tm_out, w.w_out, D, D, D, az_pick_bn(D))) ||
+            (rc = az_make_tmap(&w.tm_w1, w.w1, 4 * D, D, D, az_pick_bn(4 * D))) ||
+            (rc = az_make_tmap(&w.tm_w2, w.w2, D, 4 * D, 4 * D, az_pick_bn(D))))
+            return rc;
+    }
+    // ---- heads
+    AZ_P(gf, "norm.weight", (size_t)D) AZ_P(bf, "norm.bias", (size_t)D)
+    AZ_P(wp, "policy_head.weight", (size_t)A * D) AZ_P(bp, "policy_head.bias", (size_t)A)
+    AZ_P(wv, "value_head.weight", (size_t)D) AZ_P(bv, "value_head.bias", (size_t)1)
+#undef AZ_P
+    if ((rc = az_upload_f32(n, &n->lnf_g, *gf)) || (rc = az_upload_f32(n, &n->lnf_b, *bf)) ||
+        (rc = az_upload_f32(n, &n->w_pol, *wp)) || (rc = az_upload_f32(n, &n->b_pol, *bp)) ||
+        (rc = az_upload_f32(n, &n->w_val, *wv)) || (rc = az_upload_f32(n, &n->b_val, *bv)))
+        return rc;
+    // ---- activations for one chunk of boards
+    const size_t B = (size_t)n->chunk, M = B * T;
+    const bool deep = n->L > 1;
+    if ((rc = az_net_alloc(n, &n->x, M * D)) || (rc = az_net_alloc(n, &n->xn, M * D)) ||
+        (rc = az_net_alloc(n, &n->qkv, M * (deep ? 3 : 2) * D)) ||
+        (rc = az_net_alloc(n, &n->qc, B * D)) || (rc = az_net_alloc(n, &n->oc, B * D)) ||
+        (rc = az_net_alloc(n, &n->xc, B * D)) || (rc = az_net_alloc(n, &n->xcn, B * D)) ||
+        (rc = az_net_alloc(n, &n->hc, B * 4 * D)) || (rc = az_net_alloc(n, &n->xc2, B * D)))
+        return rc;
+    if (deep && ((rc = az_net_alloc(n, &n->ao, M * D)) || (rc = az_net_alloc(n, &n->hbuf, M * 4 * D)))) return rc;
+    const int nw = cells <= 64 ? 1 : AZ_MAX_WORDS;
+    if ((rc = az_net_alloc(n, &n->in_words, B * 2 * nw)) || (rc = az_net_alloc(n, &n->in_player, B)) ||
+        (rc = az_net_alloc(n, &n->out_priors, B * A)) || (rc = az_net_alloc(n, &n->out_values, B)) ||
+        (rc = az_net_alloc(n, &n->out_logits, B * A)))
+        return rc;
+    AZ_CUDA_OK(cudaMemset(n->x, 0, M * D * 2));
+    AZ_CUDA_OK(cudaMemset(n->xn, 0, M * D * 2));
+    if ((rc = az_make_tmap(&n->tm_xn, n->xn, M, D, D, 128)) ||
+        (rc = az_make_tmap(&n->tm_xn_cls, n->xn, B, D, (uint64_t)T * D, 128)) ||
+        (rc = az_make_tmap(&n->tm_oc, n->oc, B, D, D, 128)) || (rc = az_make_tmap(&n->tm_xcn, n->xcn, B, D, D, 128)) ||
+        (rc = az_make_tmap(&n->tm_hc, n->hc, B, 4 * D, 4 * D, 128)))
+        return rc;
+    if (deep && ((rc = az_make_tmap(&n->tm_ao, n->ao, M, D, D, 128)) || (rc = az_make_tmap(&n->tm_hbuf, n->hbuf, M, 4 * D, 4 * D, 128))))
+        return rc;
+    AZ_CUDA_OK(cudaDeviceSynchronize());
+    n->finalized = true;
+    return AZ_OK;
+}
+
+// ---- forward pass over one chunk of boards ------------------------------------------------
+static AzGemmArgs az_gargs(const AzBatch& b, int rows_per_item, const float* bias, const bf16* resid, int ldr, bf16* out,
+                           int ldo, int N, int K) {
+    AzGemmArgs a{};
+    a.bias = bias; a.resid = resid; a.ldr = ldr; a.out = out; a.ldo = ldo; a.N = N; a.K = K;
+    a.m_fixed = b.fixed; a.m_count = b.count; a.m_item_offset = b.offset; a.m_item_cap = b.cap;
+    a.m_rows_per_item = rows_per_item;
+    if (!b.count) {                                         // host-known batch: rows directly
+        int items = b.fixed - b.offset;
+        items = items < 0 ? 0 : (items > b.cap ? b.cap : items);
+        a.m_fixed = items * rows_per_item;
+    }
+    return a;
+}
+
+template <typename F>
+static void az_ln_dispatch(int D, F&& f) {
+    if (D <= 256) f(std::integral_constant<int, 1>());
+    else if (D <= 512) f(std::integral_constant<int, 2>());
+    else f(std::integral_constant<int, 4>());
+}
+
+static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words, const uint8_t* players, int nw,
+                                float* priors, float* values, float* logits, cudaStream_t s) {
+    const int D = n->D, T = n->T, H = n->H, L = n->L, A = n->A;
+    const int cap = batch.cap;                               // grid bound (items)
+    const long long max_rows = (long long)cap * T;
+    int rc;
+    // 1. boards -> tokens -> LN1 of block 0
+    AzEmbedArgs ea{};
+    ea.batch = batch; ea.leaf_words = words; ea.leaf_player = players; ea.nw = nw;
+    ea.rows = n->rows; ea.cols = n->cols; ea.planes = n->C; ea.patch = n->patch; ea.D = D; ea.T = T;
+    ea.wt = n->wt_embed; ea.posb = n->posb; ea.ln_g = n->blk[0].ln1_g; ea.ln_b = n->blk[0].ln1_b;
+    ea.x = n->x; ea.xn = n->xn; ea.write_all_x = L > 1;
+    {
+        const int grid = (int)((max_rows + 7) / 8);
+        az_ln_dispatch(D, [&](auto nv) { az_embed_ln_kernel<decltype(nv)::value><<<grid, 256, 0, s>>>(ea); });
+        AZ_CUDA_OK(cudaGetLastError());
+        ++n->launches;
+    }
+    auto layernorm = [&](int rows_per_item, const bf16* in, int ld_in, bf16* out, int ld_out, const float* g, const float* b) {
+        const long long rows = (long long)cap * rows_per_item;
+        const int grid = (int)((rows + 7) / 8);
+        az_ln_dispatch(D, [&](auto nv) {
+            az_layernorm_kernel<decltype(nv)::value><<<grid, 256, 0, s>>>(batch, rows_per_item, in, ld_in, out, ld_out, D, g, b);
+        });
+        ++n->launches;
+    };
+    for (int l = 0; l < L - 1; ++l) {                        // full blocks (ai/nn.py:52-61)
+        AzBlockW& w = n->blk[l];
+        if (l > 0) layernorm(T, n->x, D, n->xn, D, w.ln1_g, w.ln1_b);
+        if ((rc = az_launch_gemm(n->tm_xn, w.tm_in, az_gargs(batch, T, w.b_in, nullptr, 0, n->qkv, 3 * D, 3 * D, D), AZ_EPI_BIAS, (int)max_rows, s))) return rc;
+        const int hd = D / H;
+        const size_t smem = ((size_t)2 * T * (hd + 1) + 4 * T) * sizeof(float);
+        if (smem > 48 * 1024) AZ_CUDA_OK(cudaFuncSetAttribute(az_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        az_attention_kernel<<<cap * H, 128, smem, s>>>(batch, n->qkv, n->ao, T, D, H);
+        AZ_CUDA_OK(cudaGetLastError());
+        if ((rc = az_launch_gemm(n->tm_ao, w.tm_out, az_gargs(batch, T, w.b_out, n->x, D, n->x, D, D, D), AZ_EPI_RESID, (int)max_rows, s))) return rc;
+        layernorm(T, n->x, D, n->xn, D, w.ln2_g, w.ln2_b);
+        if ((rc = az_launch_gemm(n->tm_xn, w.tm_w1, az_gargs(batch, T, w.b1, nullptr, 0, n->hbuf, 4 * D, 4 * D, D), AZ_EPI_GELU, (int)max_rows, s))) return rc;
+        if ((rc = az_launch_gemm(n->tm_hbuf, w.tm_w2, az_gargs(batch, T, w.b2, n->x, D, n->x, D, D, 4 * D), AZ_EPI_RESID, (int)max_rows, s))) return rc;
+        n->launches += 5;
+    }
+    {                                                        // last block, cls-pruned
+        AzBlockW& w = n->blk[L - 1];
+        if (L > 1) layernorm(T, n->x, D, n->xn, D, w.ln1_g, w.ln1_b);
+        // K,V of every token; Q of the cls token only (rows of xn with stride T*D)
+        if ((rc = az_launch_gemm(n->tm_xn, w.tm_kv, az_gargs(batch, T, w.b_in + D, nullptr, 0, n->qkv, 2 * D, 2 * D, D), AZ_EPI_BIAS, (int)max_rows, s))) return rc;
+        if ((rc = az_launch_gemm(n->tm_xn_cls, w.tm_q, az_gargs(batch, 1, w.b_in, nullptr, 0, n->qc, D, D, D), AZ_EPI_BIAS, cap, s))) return rc;
+        az_cls_attention_kernel<<<(cap * H + 3) / 4, 128, 0, s>>>(batch, n->qc, n->qkv, n->oc, T, D, H);
+        AZ_CUDA_OK(cudaGetLastError());
+        if ((rc = az_launch_gemm(n->tm_oc, w.tm_out, az_gargs(batch, 1, w.b_out, n->x, T * D, n->xc, D, D, D), AZ_EPI_RESID, cap, s))) return rc;
+        layernorm(1, n->xc, D, n->xcn, D, w.ln2_g, w.ln2_b);
+        if ((rc = az_launch_gemm(n->tm_xcn, w.tm_w1, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap, s))) return rc;
+        if ((rc = az_launch_gemm(n->tm_hc, w.tm_w2, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap, s))) return rc;
+        n->launches += 6;
+    }
+    AzHeadArgs ha{};
+    ha.batch = batch; ha.xc = n->xc2; ha.D = D; ha.A = A; ha.ln_g = n->lnf_g; ha.ln_b = n->lnf_b;
+    ha.w_pol = n->w_pol; ha.b_pol = n->b_pol; ha.w_val = n->w_val; ha.b_val = n->b_val;
+    ha.priors = priors; ha.values = values; ha.logits = logits;
+    az_head_kernel<<<cap, 128, (size_t)(D + A + 8) * sizeof(float), s>>>(ha);
+    AZ_CUDA_OK(cudaGetLastError());
+    ++n->launches;
+    return AZ_OK;
+}
+
+// Evaluate the forest's pending leaves (the `model(...)` call of ai/mcts.py:46 for the whole
+// batch): priors/values land in the forest's evaluation buffers.  Asynchronous, capturable.
+extern "C" int az_net_eval_leaves(az_net* n, az_forest* f, void* stream) {
+    if (!n || !f) return az_fail(AZ_EINVAL, "az_net_eval_leaves: null");
+    if (!n->finalized) return az_fail(AZ_ESTATE, "az_net_eval_leaves: call az_net_finalize first");
+    AzForestDev* d = az_forest_dev(f);
+    if (d->g.rows != n->rows || d->g.cols != n->cols || d->g.planes != n->C || d->g.action_dim != n->A)
+        return az_fail(AZ_EINVAL, "az_net_eval_leaves: net and forest disagree on the game");
+    for (int off = 0; off < d->max_leaves; off += n->chunk) {
+        AzBatch b{d->n_leaves, 0, off, std::min(n->chunk, d->max_leaves - off)};
+        int rc = az_net_forward_chunk(n, b, d->leaf_words, d->leaf_player, d->g.nw, d->priors, d->values, nullptr, (cudaStream_t)stream);
+        if (rc) return rc;
+    }
+    return AZ_OK;
+}
+
+__global__ void az_planes_to_leaves_kernel(const float* __restrict__ planes, int n, int C, int cells, int nw,
+                                           uint64_t* words, uint8_t* players) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n * 2 * nw) return;
+    const int b = t / (2 * nw), r = t % (2 * nw), side = r / nw, wi = r % nw;
+    const float* p = planes + ((size_t)b * C + side) * cells;
+    uint64_t v = 0;
+    for (int i = 0; i < 64; ++i) {
+        const int cell = wi * 64 + i;
+        if (cell < cells && p[cell] == 1.0f) v |= 1ull << i;
+    }
+    words[t] = v;
+    if (r == 0) players[b] = (C == 3 && planes[((size_t)b * C + 2) * cells] == 1.0f) ? 1 : 0;
+}
+
+// Net.forward on host planes (ai/nn.py:74-84): float32 [B][C][rows][cols] canonical boards in,
+// logits [B][A], values [B] and softmax priors [B][A] out (host).  Synchronous.
+extern "C" int az_net_forward_planes(az_net* n, const float* planes_host, int B, float* logits_host, float* values_host,
+                                     float* priors_host, void* stream) {
+    if (!n || !planes_host || B <= 0) return az_fail(AZ_EINVAL, "az_net_forward_planes: bad arguments");
+    if (!n->finalized) return az_fail(AZ_ESTATE, "az_net_forward_planes: call az_net_finalize first");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int cells = n->rows * n->cols, nw = cells <= 64 ? 1 : AZ_MAX_WORDS;
+    float* pl_dev = nullptr;
+    AZ_CUDA_OK(cudaMalloc(&pl_dev, (size_t)n->chunk * n->C * cells * 4));
+    for (int off = 0; off < B; off += n->chunk) {
+        const int nb = std::min(n->chunk, B - off);
+        AZ_CUDA_OK(cudaMemcpyAsync(pl_dev, planes_host + (size_t)off * n->C * cells, (size_t)nb * n->C * cells * 4, cudaMemcpyHostToDevice, s));
+        az_planes_to_leaves_kernel<<<(nb * 2 * nw + 127) / 128, 128, 0, s>>>(pl_dev, nb, n->C, cells, nw, n->in_words, n->in_player);
+        AzBatch b{nullptr, nb, 0, nb};
+        int rc = az_net_forward_chunk(n, b, n->in_words, n->in_player, nw, n->out_priors, n->out_values, n->out_logits, s);
+        if (rc) { cudaFree(pl_dev); return rc; }
+        if (logits_host) AZ_CUDA_OK(cudaMemcpyAsync(logits_host + (size_t)off * n->A, n->out_logits, (size_t)nb * n->A * 4, cudaMemcpyDeviceToHost, s));
+        if (priors_host) AZ_CUDA_OK(cudaMemcpyAsync(priors_host + (size_t)off * n->A, n->out_priors, (size_t)nb * n->A * 4, cudaMemcpyDeviceToHost, s));
+        if (values_host) AZ_CUDA_OK(cudaMemcpyAsync(values_host + off, n->out_values, (size_t)nb * 4, cudaMemcpyDeviceToHost, s));
+        AZ_CUDA_OK(cudaStreamSynchronize(s));
+    }
+    cudaFree(pl_dev);
+    return AZ_OK;
+}
+
+extern "C" long long az_net_launch_count(az_net* n) { return n ? (long long)n->launches : 0; }
+
+// ======================================================================================
+// Whole search with the built-in net: the loop of ai/mcts.py:16 for every tree at once.
+// One step = az_forest_advance (apply answers + select) followed by the net on the new
+// leaves; the step is captured once into a CUDA graph and replayed (no per-node host work).
+// ======================================================================================
+struct AzStepGraph {
+    az_forest* f = nullptr;
+    int iters = -1, use_noise = -1;
+    cudaGraphExec_t exec = nullptr;
+};
+static std::map<az_net*, AzStepGraph> g_graphs;
+static cudaStream_t g_own_stream = nullptr;
+
+static int az_step_eager(az_net* n, az_forest* f, cudaStream_t s) {
+    int rc = az_forest_advance(f, s);
+    if (rc) return rc;
+    return az_net_eval_leaves(n, f, s);
+}
+
+extern "C" int az_forest_search_net(az_forest* f, az_net* n, int iters, void* stream) {
+    if (!f || !n) return az_fail(AZ_EINVAL, "az_forest_search_net: null");
+    if (!n->finalized) return az_fail(AZ_ESTATE, "az_forest_search_net: call az_net_finalize first");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!s) {                                               // graphs cannot be captured on the legacy stream
+        if (!g_own_stream) AZ_CUDA_OK(cudaStreamCreateWithFlags(&g_own_stream, cudaStreamNonBlocking));
+        AZ_CUDA_OK(cudaStreamSynchronize(0));
+        s = g_own_stream;
+    }
+    int rc = az_forest_begin_move(f, iters, s);
+    if (rc) return rc;
+    AzForestDev* d = az_forest_dev(f);
+    AzStepGraph& g = g_graphs[n];
+    int steps = 0;
+    if (g.f != f || g.iters != iters || g.use_noise != d->use_noise || !g.exec) {
+        if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
+        if ((rc = az_step_eager(n, f, s))) return rc;      // warm-up outside capture (sets func attributes)
+        ++steps;
+        cudaGraph_t graph = nullptr;
+        AZ_CUDA_OK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+        rc = az_step_eager(n, f, s);
+        cudaError_t ce = cudaStreamEndCapture(s, &graph);
+        if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+        if (ce != cudaSuccess) return az_fail(AZ_ECUDA, std::string("graph capture: ") + cudaGetErrorString(ce));
+        ce = cudaGraphInstantiate(&g.exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ce != cudaSuccess) return az_fail(AZ_ECUDA, std::string("graph instantiate: ") + cudaGetErrorString(ce));
+        g.f = f; g.iters = iters; g.use_noise = d->use_noise;
+    }
+    int done = 0;
+    for (;;) {
+        const int burst = steps <= 1 ? (d->vl == 1 ? iters + 1 - steps : std::max(8, iters / d->vl)) : 4;
+        for (int i = 0; i < burst; ++i) {
+            AZ_CUDA_OK(cudaGraphLaunch(g.exec, s));
+            ++steps;
+        }
+        if ((rc = az_forest_counts(f, nullptr, &done, s))) return rc;
+        if (done >= d->n_trees) break;
+        if (steps > 2 * iters + 16) return az_fail(AZ_ESTATE, "az_forest_search_net: did not converge");
+    }
+    return AZ_OK;
+}
+
+extern "C" int az_net_invalidate_graphs(az_net* n) {
+    auto it = g_graphs.find(n);
+    if (it != g_graphs.end()) {
+        if (it->second.exec) cudaGraphExecDestroy(it->second.exec);
+        g_graphs.erase(it);
+    }
+    return AZ_OK;
+}

@@ -1,0 +1,392 @@
+// CUDA-core kernels of the policy/value net (everything that is not a dense projection):
+// board -> token embedding (+LayerNorm), LayerNorm, multi-head attention, cls-query
+// attention of the pruned last block, final LayerNorm + heads + softmax.
+// Reference: ai/nn.py:5-36 (embedding), :38-61 (block), :74-84 (heads); ai/mcts.py:49 (softmax).
+#pragma once
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+typedef __nv_bfloat16 bf16;
+
+// Items (boards) this launch handles: the evaluation batch size lives on the device.
+struct AzBatch {
+    const int* count;   // device counter (forest n_leaves) or nullptr
+    int fixed;          // used when count == nullptr
+    int offset, cap;    // this launch covers items [offset, offset + cap)
+};
+__device__ __forceinline__ int az_batch_items(const AzBatch& b) {
+    int n = (b.count ? *b.count : b.fixed) - b.offset;
+    return n < 0 ? 0 : (n > b.cap ? b.cap : n);
+}
+
+__device__ __forceinline__ float az_warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float az_warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__device__ __forceinline__ void az_unpack8(const uint4& u, float (&f)[8]) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float2 t = __bfloat1622float2(h[i]);
+        f[2 * i] = t.x;
+        f[2 * i + 1] = t.y;
+    }
+}
+__device__ __forceinline__ uint4 az_pack8(const float (&f)[8]) {
+    uint4 u;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    return u;
+}
+
+// LayerNorm of a row held as NV x 8 channels per lane (channel = (v*32+lane)*8 + e), eps 1e-5,
+// biased variance (torch.nn.LayerNorm).  Lanes whose vector lies beyond D hold zeros.
+template <int NV>
+__device__ __forceinline__ void az_row_layernorm(float (&x)[NV][8], int D, int lane, const float* __restrict__ gamma,
+                                                 const float* __restrict__ beta) {
+    float s = 0.f;
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s += x[v][e];
+    const float mean = az_warp_sum(s) / (float)D;
+    float q = 0.f;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        const bool on = (v * 32 + lane) * 8 < D;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const float d = on ? x[v][e] - mean : 0.f;
+            q += d * d;
+        }
+    }
+    const float rstd = rsqrtf(az_warp_sum(q) / (float)D + 1e-5f);
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        const int d0 = (v * 32 + lane) * 8;
+        if (d0 < D) {
+            const float4 g0 = *reinterpret_cast<const float4*>(gamma + d0), g1 = *reinterpret_cast<const float4*>(gamma + d0 + 4);
+            const float4 b0 = *reinterpret_cast<const float4*>(beta + d0), b1 = *reinterpret_cast<const float4*>(beta + d0 + 4);
+            const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) x[v][e] = (x[v][e] - mean) * rstd * gg[e] + bb[e];
+        }
+    }
+}
+
+struct AzEmbedArgs {
+    AzBatch batch;
+    const uint64_t* leaf_words;   // [items][2][nw] canonical: mine, theirs
+    const uint8_t* leaf_player;   // side to move (plane 2 of the 3-plane games)
+    int nw, rows, cols, planes, patch, D, T;
+    const bf16* wt;               // [planes*patch*patch][D] conv weight, channel-last
+    const float* posb;            // [2][T][D]: pos-emb + conv bias (+ plane-2 sum when stm=1); row 0 = cls + pos[0]
+    const float* ln_g;            // LayerNorm 1 of block 0
+    const float* ln_b;
+    bf16* x;                      // [items*T][D] residual stream
+    bf16* xn;                     // [items*T][D] LN1(x)
+    int write_all_x;              // 0: only the cls rows of x are needed (depth == 1)
+};
+
+// One warp per token: conv patch embedding of binary planes as a sum of weight rows
+// (ai/nn.py:9-18), + cls/pos (ai/nn.py:33-35), then LayerNorm 1 of the first block (:54).
+template <int NV>
+__global__ void __launch_bounds__(256) az_embed_ln_kernel(AzEmbedArgs a) {
+    const int items = az_batch_items(a.batch);
+    const int lane = threadIdx.x & 31;
+    const long long token = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (token >= (long long)items * a.T) return;
+    const int b = (int)(token / a.T), t = (int)(token - (long long)b * a.T);
+    const int item = a.batch.offset + b;
+    const int stm = a.planes == 3 ? a.leaf_player[item] : 0;
+    float x[NV][8];
+    const float* pb = a.posb + ((size_t)stm * a.T + t) * a.D;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        const int d0 = (v * 32 + lane) * 8;
+        if (d0 < a.D) {
+            const float4 p0 = *reinterpret_cast<const float4*>(pb + d0), p1 = *reinterpret_cast<const float4*>(pb + d0 + 4);
+            x[v][0] = p0.x; x[v][1] = p0.y; x[v][2] = p0.z; x[v][3] = p0.w;
+            x[v][4] = p1.x; x[v][5] = p1.y; x[v][6] = p1.z; x[v][7] = p1.w;
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) x[v][e] = 0.f;
+        }
+    }
+    if (t > 0) {
+        const int cell = t - 1, r = cell / a.cols, c = cell - r * a.cols, half = a.patch >> 1;
+        const uint64_t* w = a.leaf_words + (size_t)item * 2 * a.nw;
+        for (int kr = 0; kr < a.patch; ++kr) {
+            const int rr = r + kr - half;
+            if (rr < 0 || rr >= a.rows) continue;
+            for (int kc = 0; kc < a.patch; ++kc) {
+                const int cc = c + kc - half;
+                if (cc < 0 || cc >= a.cols) continue;
+                const int s = rr * a.cols + cc;
+                const uint64_t bit = 1ull << (s & 63);
+                int ch = -1;
+                if (w[s >> 6] & bit) ch = 0;
+                else if (w[a.nw + (s >> 6)] & bit) ch = 1;
+                if (ch < 0) continue;
+                const bf16* wr = a.wt + (size_t)((ch * a.patch + kr) * a.patch + kc) * a.D;
+#pragma unroll
+                for (int v = 0; v < NV; ++v) {
+                    const int d0 = (v * 32 + lane) * 8;
+                    if (d0 < a.D) {
+                        float f[8];
+                        az_unpack8(*reinterpret_cast<const uint4*>(wr + d0), f);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) x[v][e] += f[e];
+                    }
+                }
+            }
+        }
+    }
+    const size_t row = (size_t)b * a.T + t;
+    if (a.write_all_x || t == 0) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            const int d0 = (v * 32 + lane) * 8;
+            if (d0 < a.D) *reinterpret_cast<uint4*>(a.x + row * a.D + d0) = az_pack8(x[v]);
+        }
+    }
+    az_row_layernorm<NV>(x, a.D, lane, a.ln_g, a.ln_b);
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        const int d0 = (v * 32 + lane) * 8;
+        if (d0 < a.D) *reinterpret_cast<uint4*>(a.xn + row * a.D + d0) = az_pack8(x[v]);
+    }
+}
+
+// LayerNorm of bf16 rows: in[row*ld_in .. +D) -> out[row*ld_out .. +D).  One warp per row.
+template <int NV>
+__global__ void __launch_bounds__(256) az_layernorm_kernel(AzBatch batch, int rows_per_item, const bf16* in, int ld_in,
+                                                           bf16* out, int ld_out, int D, const float* g, const float* bt) {
+    const long long rows = (long long)az_batch_items(batch) * rows_per_item;
+    const int lane = threadIdx.x & 31;
+    const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    float x[NV][8];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        const int d0 = (v * 32 + lane) * 8;
+        if (d0 < D) az_unpack8(*reinterpret_cast<const uint4*>(in + (size_t)row * ld_in + d0), x[v]);
+        else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) x[v][e] = 0.f;
+        }
+    }
+    az_row_layernorm<NV>(x, D, lane, g, bt);
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        const int d0 = (v * 32 + lane) * 8;
+        if (d0 < D) *reinterpret_cast<uint4*>(out + (size_t)row * ld_out + d0) = az_pack8(x[v]);
+    }
+}
+
+// Full multi-head self-attention of one (board, head) per block (nn.MultiheadAttention,
+// ai/nn.py:42,55; eval mode, no masks): softmax(q k^T / sqrt(hd)) v.  qkv rows hold
+// [q | k | v] (3D wide).  Used by every block except the last (which is cls-pruned).
+// smem: K and V of the head as fp32 [T][hd+1] each + one probability row per warp.
+__global__ void __launch_bounds__(128) az_attention_kernel(AzBatch batch, const bf16* __restrict__ qkv, bf16* __restrict__ out,
+                                                           int T, int D, int H) {
+    extern __shared__ float sm_att[];
+    const int items = az_batch_items(batch);
+    const int b = blockIdx.x / H, h = blockIdx.x - b * H;
+    if (b >= items) return;
+    const int hd = D / H, ldk = hd + 1;
+    float* sk = sm_att;
+    float* sv = sk + (size_t)T * ldk;
+    float* sp = sv + (size_t)T * ldk;                       // [4 warps][T]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bf16* base = qkv + (size_t)b * T * 3 * D;
+    for (int i = threadIdx.x; i < T * hd; i += blockDim.x) {
+        const int t = i / hd, d = i - t * hd;
+        sk[t * ldk + d] = __bfloat162float(base[(size_t)t * 3 * D + D + h * hd + d]);
+        sv[t * ldk + d] = __bfloat162float(base[(size_t)t * 3 * D + 2 * D + h * hd + d]);
+    }
+    __syncthreads();
+    const float scale = rsqrtf((float)hd);
+    float* p = sp + warp * T;
+    for (int tq = warp; tq < T; tq += 4) {
+        const bf16* qp = base + (size_t)tq * 3 * D + h * hd;
+        float mx = -1e30f;
+        for (int tk = lane; tk < T; tk += 32) {
+            float s = 0.f;
+            for (int d = 0; d < hd; ++d) s += __bfloat162float(qp[d]) * sk[tk * ldk + d];
+            s *= scale;
+            p[tk] = s;
+            mx = fmaxf(mx, s);
+        }
+        mx = az_warp_max(mx);
+        float sum = 0.f;
+        for (int tk = lane; tk < T; tk += 32) {
+            const float e = __expf(p[tk] - mx);
+            p[tk] = e;
+            sum += e;
+        }
+        sum = az_warp_sum(sum);
+        __syncwarp();
+        const float inv = 1.0f / sum;
+        for (int d = lane; d < hd; d += 32) {
+            float o = 0.f;
+            for (int tk = 0; tk < T; ++tk) o += p[tk] * sv[tk * ldk + d];
+            out[((size_t)b * T + tq) * D + h * hd + d] = __float2bfloat16(o * inv);
+        }
+        __syncwarp();
+    }
+}
+
+// Attention of the LAST block restricted to the cls query (only x[:,0] feeds the heads,
+// ai/nn.py:81).  One warp per (board, head); kv rows hold [k | v] (2D wide), qc holds the cls
+// query rows [items][D].  hd <= 128, T <= 256.
+__global__ void __launch_bounds__(128) az_cls_attention_kernel(AzBatch batch, const bf16* __restrict__ qc,
+                                                               const bf16* __restrict__ kv, bf16* __restrict__ oc, int T,
+                                                               int D, int H) {
+    const int items = az_batch_items(batch);
+    const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    const int b = w / H, h = w - b * H;
+    if (b >= items) return;
+    const int hd = D / H;
+    float q[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int d = lane + 32 * j;
+        q[j] = d < hd ? __bfloat162float(qc[(size_t)b * D + h * hd + d]) : 0.f;
+    }
+    const bf16* kb = kv + (size_t)b * T * 2 * D + h * hd;
+    const float scale = rsqrtf((float)hd);
+    float s[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] = -1e30f;
+    for (int t = 0; t < T; ++t) {
+        float part = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int d = lane + 32 * j;
+            if (d < hd) part += q[j] * __bfloat162float(kb[(size_t)t * 2 * D + d]);
+        }
+        part = az_warp_sum(part) * scale;
+        if ((t & 31) == lane) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (j == (t >> 5)) s[j] = part;
+        }
+    }
+    float mx = -1e30f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) mx = fmaxf(mx, s[j]);
+    mx = az_warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        s[j] = (j * 32 + lane < T) ? __expf(s[j] - mx) : 0.f;
+        sum += s[j];
+    }
+    sum = az_warp_sum(sum);
+    float o[4] = {0.f, 0.f, 0.f, 0.f};
+    const bf16* vb = kb + D;
+    for (int t = 0; t < T; ++t) {
+        float pt = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (j == (t >> 5)) pt = s[j];
+        pt = __shfl_sync(0xffffffffu, pt, t & 31);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int d = lane + 32 * j;
+            if (d < hd) o[j] += pt * __bfloat162float(vb[(size_t)t * 2 * D + d]);
+        }
+    }
+    const float inv = 1.0f / sum;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int d = lane + 32 * j;
+        if (d < hd) oc[(size_t)b * D + h * hd + d] = __float2bfloat16(o[j] * inv);
+    }
+}
+
+struct AzHeadArgs {
+    AzBatch batch;
+    const bf16* xc;       // [items][D] cls rows after the last block
+    int D, A;
+    const float *ln_g, *ln_b;     // Net.norm
+    const float *w_pol, *b_pol;   // [A][D], [A]
+    const float *w_val, *b_val;   // [D], [1]
+    float* priors;        // [.. + offset][A]
+    float* values;
+    float* logits;        // optional raw logits [.. + offset][A] (parity tests), may be null
+};
+
+// Final LayerNorm (ai/nn.py:78) + policy/value heads (:82-83) + the softmax of ai/mcts.py:49
+// (max-subtracted for range safety; mathematically the same exp(l)/sum(exp(l))).
+// One block of 128 threads per board; smem: D + A + 8 floats.
+__global__ void __launch_bounds__(128) az_head_kernel(AzHeadArgs a) {
+    extern __shared__ float sm_head[];
+    const int items = az_batch_items(a.batch);
+    const int b = blockIdx.x;
+    if (b >= items) return;
+    float* xs = sm_head;
+    float* lg = xs + a.D;
+    float* red = lg + a.A;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float s = 0.f;
+    for (int d = threadIdx.x; d < a.D; d += blockDim.x) {
+        const float v = __bfloat162float(a.xc[(size_t)b * a.D + d]);
+        xs[d] = v;
+        s += v;
+    }
+    s = az_warp_sum(s);
+    if (lane == 0) red[warp] = s;
+    __syncthreads();
+    const float mean = (red[0] + red[1] + red[2] + red[3]) / (float)a.D;
+    __syncthreads();
+    float q = 0.f;
+    for (int d = threadIdx.x; d < a.D; d += blockDim.x) {
+        const float dv = xs[d] - mean;
+        q += dv * dv;
+    }
+    q = az_warp_sum(q);
+    if (lane == 0) red[warp] = q;
+    __syncthreads();
+    const float rstd = rsqrtf((red[0] + red[1] + red[2] + red[3]) / (float)a.D + 1e-5f);
+    for (int d = threadIdx.x; d < a.D; d += blockDim.x) xs[d] = (xs[d] - mean) * rstd * a.ln_g[d] + a.ln_b[d];
+    __syncthreads();
+    for (int o = warp; o <= a.A; o += 4) {                   // o == A is the value head
+        const float* wr = o < a.A ? a.w_pol + (size_t)o * a.D : a.w_val;
+        float acc = 0.f;
+        for (int d = lane; d < a.D; d += 32) acc += wr[d] * xs[d];
+        acc = az_warp_sum(acc);
+        if (lane == 0) {
+            if (o < a.A) lg[o] = acc + a.b_pol[o];
+            else a.values[a.batch.offset + b] = tanhf(acc + a.b_val[0]);
+        }
+    }
+    __syncthreads();
+    float mx = -1e30f;
+    for (int i = threadIdx.x; i < a.A; i += blockDim.x) mx = fmaxf(mx, lg[i]);
+    mx = az_warp_max(mx);
+    if (lane == 0) red[4 + warp] = mx;
+    __syncthreads();
+    mx = fmaxf(fmaxf(red[4], red[5]), fmaxf(red[6], red[7]));
+    float sum = 0.f;
+    for (int i = threadIdx.x; i < a.A; i += blockDim.x) sum += expf(lg[i] - mx);
+    sum = az_warp_sum(sum);
+    __syncthreads();
+    if (lane == 0) red[warp] = sum;
+    __syncthreads();
+    sum = red[0] + red[1] + red[2] + red[3];
+    const size_t ob = (size_t)(a.batch.offset + b) * a.A;
+    for (int i = threadIdx.x; i < a.A; i += blockDim.x) {
+        a.priors[ob + i] = expf(lg[i] - mx) / sum;
+        if (a.logits) a.logits[ob + i] = lg[i];
+    }
+}

@@ -135,10 +135,21 @@ class Forest:
         _lib.check(self._L.az_forest_search_hash(self.h, int(iters), C.c_uint64(seed), int(qbits), self.stream),
                    "search_hash")
 
-    def search_external(self, iters, evaluate, max_b=None):
-        """Search with an arbitrary evaluator `evaluate(planes_dev_ptr, n) -> (logits_ptr, values_ptr)`
-        working on device memory (used for `model` callables; see ai/mcts.py)."""
-        raise NotImplementedError("use alpha_zero_b200.ai.MCTS")
+    def search_net(self, net, iters):
+        """Whole search with the built-in net (ai.nn.B200Net): CUDA-graph replay per step."""
+        _lib.check(self._L.az_forest_search_net(self.h, net.h, int(iters), self.stream), "search_net")
+
+    def read_leaves(self):
+        """Current evaluation batch and the evaluator's answers (host copies)."""
+        m = self.n_trees * self.vl
+        words = np.zeros((m, 2, self.g.nw), np.uint64)
+        players = np.zeros(m, np.uint8)
+        trees = np.zeros(m, np.int32)
+        priors = np.zeros((m, self.g.action_dim), np.float32)
+        values = np.zeros(m, np.float32)
+        n = _lib.check(self._L.az_forest_read_leaves(self.h, m, _ptr(words), _ptr(players), _ptr(trees), _ptr(priors),
+                                                     _ptr(values), self.stream), "read_leaves")
+        return dict(n=n, words=words[:n], players=players[:n], trees=trees[:n], priors=priors[:n], values=values[:n])
 
     # ---- results --------------------------------------------------------------------------
     def root_visits(self):

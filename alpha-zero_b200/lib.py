@@ -34,6 +34,16 @@ _SIGS = {
     "az_forest_info": (i32, [vp] + [C.POINTER(i32)] * 5),
     "az_rules_legal": (i32, [i32, i32, i32, i32, vp, vp, vp]),
     "az_rules_winner": (i32, [i32, i32, i32, i32, vp, vp, vp, vp]),
+    "az_net_create": (i32, [i32] * 9 + [C.POINTER(vp)]),
+    "az_net_destroy": (None, [vp]),
+    "az_net_set_param": (i32, [vp, C.c_char_p, vp, C.c_longlong]),
+    "az_net_finalize": (i32, [vp]),
+    "az_net_eval_leaves": (i32, [vp, vp, vp]),
+    "az_net_forward_planes": (i32, [vp, vp, i32, vp, vp, vp, vp]),
+    "az_net_launch_count": (C.c_longlong, [vp]),
+    "az_forest_search_net": (i32, [vp, vp, i32, vp]),
+    "az_net_invalidate_graphs": (i32, [vp]),
+    "az_forest_read_leaves": (i32, [vp, i32, vp, vp, vp, vp, vp, vp]),
     "az_gemm_bf16": (i32, [vp, i32, vp, vp, vp, i32, vp, i32, i32, i32, i32, i32, vp]),
 }
 # entry points added by later translation units; bound when present in the header

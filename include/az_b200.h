@@ -85,6 +85,11 @@ AZ_API int az_forest_root_visits(az_forest* f, int32_t* visits_host /*[n_trees][
 AZ_API int az_forest_root_children(az_forest* f, int tree, int max_children, int32_t* cells_host, int32_t* visits_host,
                             double* values_host, double* priors_host, int32_t* root_visit, double* root_value,
                             void* stream);
+/* The current evaluation batch (leaves + the evaluator's answers) copied to the host: canonical
+ * words uint64 [n][2][nw], side to move, owning tree, priors [n][A], values [n].  Returns n.
+ * This is the log that replays a GPU search in the oracle (MCTS.cache preload, mcts.py:40-41). */
+AZ_API int az_forest_read_leaves(az_forest* f, int max_n, uint64_t* words_host, uint8_t* players_host,
+                                 int32_t* trees_host, float* priors_host, float* values_host, void* stream);
 /* counters: [sims, terminal sims, expansions, children, selects, children scored, collisions, -] */
 AZ_API int az_forest_stats(az_forest* f, uint64_t* out8_host, int reset, void* stream);
 AZ_API int az_forest_info(az_forest* f, int* n_trees, int* action_dim, int* planes, int* nw, int* cap);
@@ -103,6 +108,27 @@ AZ_API int az_rules_winner(int game, int rows, int cols, int n, const uint64_t* 
  * GELU, 2 = + resid[M][ldr].  All pointers are device memory; N, K multiples of 64. */
 AZ_API int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const float* bias_dev, const void* resid_dev,
                         int ldr, void* out_dev, int ldo, int M, int N, int K, int epi, void* stream);
+
+/* The reference's Net(img_size, patch_size, embed_dim, action_dim, num_heads, depth, channels)
+ * (ai/nn.py:63-72); rows x cols generalises img_size to non-square boards (Connect4). */
+AZ_API int az_net_create(int rows, int cols, int planes, int patch, int embed_dim, int num_heads, int depth,
+                         int action_dim, int max_batch, az_net** out);
+AZ_API void az_net_destroy(az_net* n);
+/* One call per state_dict entry, under its PyTorch name (utils.load_model checkpoints,
+ * utils.py:63-69): fp32 host data.  az_net_finalize converts them (bf16 weights, TMA maps). */
+AZ_API int az_net_set_param(az_net* n, const char* name, const float* data_host, long long numel);
+AZ_API int az_net_finalize(az_net* n);
+/* Evaluate the forest's pending leaves in place of `model(...)` + softmax (ai/mcts.py:46-49). */
+AZ_API int az_net_eval_leaves(az_net* n, az_forest* f, void* stream);
+/* Net.forward on canonical float32 planes [B][C][rows][cols] (host) -> logits [B][A],
+ * values [B], priors [B][A] (host; any may be NULL).  Synchronous. */
+AZ_API int az_net_forward_planes(az_net* n, const float* planes_host, int B, float* logits_host, float* values_host,
+                                 float* priors_host, void* stream);
+AZ_API long long az_net_launch_count(az_net* n);
+/* MCTS.mcts with the built-in net for every tree of the forest: `iters` simulations per tree,
+ * one CUDA graph per step (advance + net), no per-node host work. */
+AZ_API int az_forest_search_net(az_forest* f, az_net* n, int iters, void* stream);
+AZ_API int az_net_invalidate_graphs(az_net* n);
 
 #ifdef __cplusplus
 }

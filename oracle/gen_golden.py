@@ -252,6 +252,8 @@ def gen_net(R, cfgs, rng):
         net.eval()
         x = (rng.random((c["B"], c["C"], c["img"], c["img"])) < 0.3).astype(np.float32)
         x[:, 1] *= (1 - x[:, 0])                         # no cell owned by both players
+        if c["C"] == 3:                                  # plane 2 is the constant side-to-move plane
+            x[:, 2] = rng.integers(0, 2, c["B"]).astype(np.float32)[:, None, None]
         with torch.no_grad():
             logits, values = net(torch.from_numpy(x))
         out_rec.append(dict(c, keys=sorted(net.state_dict().keys()),

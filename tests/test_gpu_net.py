@@ -1,0 +1,126 @@
+"""The B200 policy/value net (tcgen05 GEMMs + fused kernels) against the reference's Net.
+
+Floating point: operands are bf16 (2^-8 relative rounding) with fp32 accumulation, through at
+most `depth` blocks, so logits are compared with |err| <= 0.05 + 0.02*|ref|, tanh values with
+|err| <= 0.03 and softmax priors with |err| <= 5e-3 (measured: 0.022 / 0.015 / 1e-3).
+Search parity WITH the net is exact: the GPU's own priors/values are replayed in the C oracle
+through the evaluator table (the reference's MCTS.cache preload route, ai/mcts.py:40-41).
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import az_oracle as orc
+import c_oracle as co
+from golden_util import GOLDEN
+from gpu_util import words_from_cells, random_positions, compare_forest_with_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def make_net(rows, cols, C, A, dim, depth, patch, heads=8, seed=5):
+    import torch
+    from alpha_zero_b200.ai.nn import Net
+    from gen_golden import deterministic_state_dict
+    net = Net((rows, cols), patch, dim, A, heads, depth, C, dropout=0.1)
+    net.load_state_dict(deterministic_state_dict(net, seed))
+    net.eval()
+    return net
+
+
+def check_close(l, v, p, rl, rv):
+    assert (np.abs(l - rl) <= 0.05 + 0.02 * np.abs(rl)).all(), np.abs(l - rl).max()
+    assert (np.abs(v - rv) <= 0.03).all(), np.abs(v - rv).max()
+    rp = np.exp(rl) / np.exp(rl).sum(1, keepdims=True)          # ai/mcts.py:49
+    assert (np.abs(p - rp) <= 5e-3).all(), np.abs(p - rp).max()
+    assert np.allclose(p.sum(1), 1.0, atol=1e-5)
+
+
+def test_net_matches_reference_goldens():
+    """Outputs of the unmodified reference Net (tests/golden/net.npz) on weights that are a
+    pure function of (name, shape, seed)."""
+    from alpha_zero_b200.ai.nn import Net, B200Net
+    from gen_golden import deterministic_state_dict
+    recs = json.load(open(os.path.join(GOLDEN, "net.json")))
+    arr = np.load(os.path.join(GOLDEN, "net.npz"))
+    for i, c in enumerate(recs):
+        net = Net(c["img"], c["patch"], c["dim"], c["A"], c["heads"], c["depth"], c["C"], dropout=0.1)
+        assert sorted(net.state_dict().keys()) == c["keys"]
+        net.load_state_dict(deterministic_state_dict(net, c["wseed"]))
+        eng = B200Net(net, max_batch=64)
+        l, v, p = eng.forward_numpy(arr[f"x{i}"])
+        check_close(l, v, p, arr[f"logits{i}"], arr[f"values{i}"])
+        eng.close()
+
+
+@pytest.mark.parametrize("rows,cols,C,A,dim,depth,patch,B", [
+    (6, 7, 3, 7, 512, 1, 5, 5000),        # Connect4, the main.py:134 net shape on a 6x7 board
+    (7, 7, 2, 49, 512, 1, 5, 9000),       # Gomoku, main.py:134
+    (7, 7, 2, 49, 256, 2, 5, 1500),       # main.py:187-188 (depth 2: full block + pruned block)
+    (3, 3, 3, 9, 64, 1, 3, 700),          # TicTacToe small net
+    (15, 15, 2, 225, 128, 2, 3, 300),     # 15x15: T = 226 tokens
+])
+def test_net_matches_torch_fp32(rows, cols, C, A, dim, depth, patch, B):
+    import torch
+    from alpha_zero_b200.ai.nn import B200Net
+    net = make_net(rows, cols, C, A, dim, depth, patch)
+    rng = np.random.default_rng(0)
+    x = (rng.random((B, C, rows, cols)) < 0.3).astype(np.float32)
+    x[:, 1] *= (1 - x[:, 0])
+    if C == 3:
+        x[:, 2] = rng.integers(0, 2, B).astype(np.float32)[:, None, None]
+    x[0] = 0                                                   # empty board
+    eng = B200Net(net, max_batch=4096)
+    l, v, p = eng.forward_numpy(x)
+    with torch.no_grad():
+        rl, rv = net(torch.from_numpy(x[:600]))
+    check_close(l[:600], v[:600], p[:600], rl.numpy(), rv.numpy())
+    l2, v2, p2 = eng.forward_numpy(x[-100:])                     # position in the batch is irrelevant
+    assert np.array_equal(l2, l[-100:]) and np.array_equal(v2, v[-100:])
+    lt, vt = eng(torch.from_numpy(x[:3]))                        # the `model(...)` calling convention
+    assert lt.shape == (3, A) and vt.shape == (3, 1)
+    eng.close()
+
+
+@pytest.mark.parametrize("g,n,iters,vl,dim,depth", [(orc.CONNECT4, 256, 200, 1, 128, 1), (orc.GOMOKU, 128, 160, 1, 64, 2),
+                                                    (orc.GOMOKU, 96, 200, 4, 64, 1), (orc.TICTACTOE, 64, 100, 1, 64, 1)])
+def test_search_with_net_replays_exactly_in_oracle(g, n, iters, vl, dim, depth):
+    import alpha_zero_b200 as az
+    from alpha_zero_b200.ai.nn import B200Net
+    net = make_net(g.rows, g.cols, g.planes, g.action_dim, dim, depth, 3)
+    eng = B200Net(net, max_batch=n * vl)
+    rng = np.random.default_rng(77)
+    cells, players, mcs = random_positions(g, n, rng, 6)
+    spec = az.game_spec(g.name, g.rows)
+    f = az.Forest(spec, n, iters, vl=vl)
+    f.set_roots_words(words_from_cells(g, cells), players, mcs)
+    # step by step, logging every evaluation the GPU net produced
+    f.begin_move(iters)
+    keys, pri, val = [], [], []
+    for _ in range(2 * iters + 8):
+        f.advance()
+        eng.eval_leaves(f)
+        r = f.read_leaves()
+        if r["n"]:
+            k = np.zeros((r["n"], 2 * spec.nw + 1), np.uint64)
+            k[:, :2 * spec.nw] = r["words"].reshape(r["n"], -1)
+            k[:, -1] = r["players"] if g.planes == 3 else 0
+            keys.append(k)
+            pri.append(r["priors"])
+            val.append(r["values"])
+        if f.counts()[1] >= n:
+            break
+    assert f.counts()[1] == n
+    table = co.Table(np.concatenate(keys), np.concatenate(pri), np.concatenate(val))
+    ref = co.search_batch(g, cells, players, mcs, iters, vl, table=table)
+    assert int(ref["stats"][7]) == 0                              # no table misses: same leaves visited
+    compare_forest_with_oracle(f, ref)
+    vis_step, q_step = f.root_visits()
+    # the CUDA-graph path must give the same search
+    f.search_net(eng, iters)
+    vis_graph, q_graph = f.root_visits()
+    assert np.array_equal(vis_step, vis_graph) and np.array_equal(q_step, q_graph)
+    f.close()
+    eng.close()
