@@ -129,6 +129,17 @@ class B200Net:
     def eval_leaves(self, forest, stream=0):
         _lib.check(self._L.az_net_eval_leaves(self.h, forest.h, stream), "az_net_eval_leaves")
 
+    def profile(self, enable=True):
+        _lib.check(self._L.az_net_profile(self.h, int(enable)), "az_net_profile")
+
+    def profile_read(self):
+        """{kernel kind: (total ms, launches)} of the eager passes since profile(True)."""
+        names = (C.c_char_p * 16)()
+        ms = (C.c_double * 16)()
+        cnt = (C.c_longlong * 16)()
+        k = _lib.check(self._L.az_net_profile_read(self.h, 16, names, ms, cnt), "az_net_profile_read")
+        return {names[i].decode(): (ms[i], cnt[i]) for i in range(k)}
+
     def launch_count(self):
         return int(self._L.az_net_launch_count(self.h))
 

@@ -156,6 +156,33 @@ struct az_net {
     uint8_t* in_player = nullptr;
     float *out_priors = nullptr, *out_values = nullptr, *out_logits = nullptr;
     unsigned long long launches = 0;     // kernels launched by forward passes
+    // optional per-kernel timing of eager forward passes (bench.py roofline numbers)
+    bool prof_on = false;
+    struct ProfRec { int kind; cudaEvent_t a, b; };
+    std::vector<ProfRec> prof_pending;
+    double prof_ms[16] = {0};
+    long long prof_n[16] = {0};
+    double prof_units[16] = {0};         // flops (GEMMs) or bytes (others) of the profiled launches
+};
+
+enum { AZ_K_EMBED = 0, AZ_K_GEMM_KV, AZ_K_GEMM_CLS, AZ_K_CLS_ATT, AZ_K_LN, AZ_K_HEAD, AZ_K_GEMM_FULL, AZ_K_ATT_FULL, AZ_K_COUNT };
+static const char* const AZ_K_NAMES[AZ_K_COUNT] = {"embed_ln", "gemm_kv", "gemm_cls_rows", "cls_attention", "layernorm",
+                                                   "head_softmax", "gemm_full_block", "attention_full"};
+
+struct AzProfScope {
+    az_net* n; cudaStream_t s; int idx = -1;
+    AzProfScope(az_net* n_, int kind, cudaStream_t s_) : n(n_), s(s_) {
+        if (!n->prof_on) return;
+        cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+        cudaStreamIsCapturing(s, &st);
+        if (st != cudaStreamCaptureStatusNone) return;
+        az_net::ProfRec r{kind, nullptr, nullptr};
+        cudaEventCreate(&r.a); cudaEventCreate(&r.b);
+        cudaEventRecord(r.a, s);
+        n->prof_pending.push_back(r);
+        idx = (int)n->prof_pending.size() - 1;
+    }
+    ~AzProfScope() { if (idx >= 0) cudaEventRecord(n->prof_pending[idx].b, s); }
 };
 
 template <typename T>
@@ -369,12 +396,14 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
     ea.wt = n->wt_embed; ea.posb = n->posb; ea.ln_g = n->blk[0].ln1_g; ea.ln_b = n->blk[0].ln1_b;
     ea.x = n->x; ea.xn = n->xn; ea.write_all_x = L > 1;
     {
+        AzProfScope ps(n, AZ_K_EMBED, s);
         const int grid = (int)((max_rows + 7) / 8);
         az_ln_dispatch(D, [&](auto nv) { az_embed_ln_kernel<decltype(nv)::value><<<grid, 256, 0, s>>>(ea); });
         AZ_CUDA_OK(cudaGetLastError());
         ++n->launches;
     }
     auto layernorm = [&](int rows_per_item, const bf16* in, int ld_in, bf16* out, int ld_out, const float* g, const float* b) {
+        AzProfScope ps(n, AZ_K_LN, s);
         const long long rows = (long long)cap * rows_per_item;
         const int grid = (int)((rows + 7) / 8);
         az_ln_dispatch(D, [&](auto nv) {
@@ -382,40 +411,53 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         });
         ++n->launches;
     };
+    auto gemm = [&](int kind, const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& ga, int epi, int mr) {
+        AzProfScope ps(n, kind, s);
+        return az_launch_gemm(ta, tb, ga, epi, mr, s);
+    };
     for (int l = 0; l < L - 1; ++l) {                        // full blocks (ai/nn.py:52-61)
         AzBlockW& w = n->blk[l];
         if (l > 0) layernorm(T, n->x, D, n->xn, D, w.ln1_g, w.ln1_b);
-        if ((rc = az_launch_gemm(n->tm_xn, w.tm_in, az_gargs(batch, T, w.b_in, nullptr, 0, n->qkv, 3 * D, 3 * D, D), AZ_EPI_BIAS, (int)max_rows, s))) return rc;
+        if ((rc = gemm(AZ_K_GEMM_FULL, n->tm_xn, w.tm_in, az_gargs(batch, T, w.b_in, nullptr, 0, n->qkv, 3 * D, 3 * D, D), AZ_EPI_BIAS, (int)max_rows))) return rc;
         const int hd = D / H;
         const size_t smem = ((size_t)2 * T * (hd + 1) + 4 * T) * sizeof(float);
         if (smem > 48 * 1024) AZ_CUDA_OK(cudaFuncSetAttribute(az_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        az_attention_kernel<<<cap * H, 128, smem, s>>>(batch, n->qkv, n->ao, T, D, H);
+        {
+            AzProfScope ps(n, AZ_K_ATT_FULL, s);
+            az_attention_kernel<<<cap * H, 128, smem, s>>>(batch, n->qkv, n->ao, T, D, H);
+        }
         AZ_CUDA_OK(cudaGetLastError());
-        if ((rc = az_launch_gemm(n->tm_ao, w.tm_out, az_gargs(batch, T, w.b_out, n->x, D, n->x, D, D, D), AZ_EPI_RESID, (int)max_rows, s))) return rc;
+        if ((rc = gemm(AZ_K_GEMM_FULL, n->tm_ao, w.tm_out, az_gargs(batch, T, w.b_out, n->x, D, n->x, D, D, D), AZ_EPI_RESID, (int)max_rows))) return rc;
         layernorm(T, n->x, D, n->xn, D, w.ln2_g, w.ln2_b);
-        if ((rc = az_launch_gemm(n->tm_xn, w.tm_w1, az_gargs(batch, T, w.b1, nullptr, 0, n->hbuf, 4 * D, 4 * D, D), AZ_EPI_GELU, (int)max_rows, s))) return rc;
-        if ((rc = az_launch_gemm(n->tm_hbuf, w.tm_w2, az_gargs(batch, T, w.b2, n->x, D, n->x, D, D, 4 * D), AZ_EPI_RESID, (int)max_rows, s))) return rc;
+        if ((rc = gemm(AZ_K_GEMM_FULL, n->tm_xn, w.tm_w1, az_gargs(batch, T, w.b1, nullptr, 0, n->hbuf, 4 * D, 4 * D, D), AZ_EPI_GELU, (int)max_rows))) return rc;
+        if ((rc = gemm(AZ_K_GEMM_FULL, n->tm_hbuf, w.tm_w2, az_gargs(batch, T, w.b2, n->x, D, n->x, D, D, 4 * D), AZ_EPI_RESID, (int)max_rows))) return rc;
         n->launches += 5;
     }
     {                                                        // last block, cls-pruned
         AzBlockW& w = n->blk[L - 1];
         if (L > 1) layernorm(T, n->x, D, n->xn, D, w.ln1_g, w.ln1_b);
         // K,V of every token; Q of the cls token only (rows of xn with stride T*D)
-        if ((rc = az_launch_gemm(n->tm_xn, w.tm_kv, az_gargs(batch, T, w.b_in + D, nullptr, 0, n->qkv, 2 * D, 2 * D, D), AZ_EPI_BIAS, (int)max_rows, s))) return rc;
-        if ((rc = az_launch_gemm(n->tm_xn_cls, w.tm_q, az_gargs(batch, 1, w.b_in, nullptr, 0, n->qc, D, D, D), AZ_EPI_BIAS, cap, s))) return rc;
-        az_cls_attention_kernel<<<(cap * H + 3) / 4, 128, 0, s>>>(batch, n->qc, n->qkv, n->oc, T, D, H);
+        if ((rc = gemm(AZ_K_GEMM_KV, n->tm_xn, w.tm_kv, az_gargs(batch, T, w.b_in + D, nullptr, 0, n->qkv, 2 * D, 2 * D, D), AZ_EPI_BIAS, (int)max_rows))) return rc;
+        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_xn_cls, w.tm_q, az_gargs(batch, 1, w.b_in, nullptr, 0, n->qc, D, D, D), AZ_EPI_BIAS, cap))) return rc;
+        {
+            AzProfScope ps(n, AZ_K_CLS_ATT, s);
+            az_cls_attention_kernel<<<(cap * H + 3) / 4, 128, 0, s>>>(batch, n->qc, n->qkv, n->oc, T, D, H);
+        }
         AZ_CUDA_OK(cudaGetLastError());
-        if ((rc = az_launch_gemm(n->tm_oc, w.tm_out, az_gargs(batch, 1, w.b_out, n->x, T * D, n->xc, D, D, D), AZ_EPI_RESID, cap, s))) return rc;
+        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out, az_gargs(batch, 1, w.b_out, n->x, T * D, n->xc, D, D, D), AZ_EPI_RESID, cap))) return rc;
         layernorm(1, n->xc, D, n->xcn, D, w.ln2_g, w.ln2_b);
-        if ((rc = az_launch_gemm(n->tm_xcn, w.tm_w1, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap, s))) return rc;
-        if ((rc = az_launch_gemm(n->tm_hc, w.tm_w2, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap, s))) return rc;
+        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_xcn, w.tm_w1, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap))) return rc;
+        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap))) return rc;
         n->launches += 6;
     }
     AzHeadArgs ha{};
     ha.batch = batch; ha.xc = n->xc2; ha.D = D; ha.A = A; ha.ln_g = n->lnf_g; ha.ln_b = n->lnf_b;
     ha.w_pol = n->w_pol; ha.b_pol = n->b_pol; ha.w_val = n->w_val; ha.b_val = n->b_val;
     ha.priors = priors; ha.values = values; ha.logits = logits;
-    az_head_kernel<<<cap, 128, (size_t)(D + A + 8) * sizeof(float), s>>>(ha);
+    {
+        AzProfScope ps(n, AZ_K_HEAD, s);
+        az_head_kernel<<<cap, 128, (size_t)(D + A + 8) * sizeof(float), s>>>(ha);
+    }
     AZ_CUDA_OK(cudaGetLastError());
     ++n->launches;
     return AZ_OK;
@@ -486,6 +528,7 @@ extern "C" long long az_net_launch_count(az_net* n) { return n ? (long long)n->l
 // leaves; the step is captured once into a CUDA graph and replayed (no per-node host work).
 // ======================================================================================
 struct AzStepGraph {
+    unsigned long long kernels = 0;     // kernels in one captured step
     az_forest* f = nullptr;
     int iters = -1, use_noise = -1;
     cudaGraphExec_t exec = nullptr;
@@ -496,6 +539,7 @@ static cudaStream_t g_own_stream = nullptr;
 static int az_step_eager(az_net* n, az_forest* f, cudaStream_t s) {
     int rc = az_forest_advance(f, s);
     if (rc) return rc;
+    ++n->launches;                                          // the advance kernel
     return az_net_eval_leaves(n, f, s);
 }
 
@@ -519,7 +563,9 @@ extern "C" int az_forest_search_net(az_forest* f, az_net* n, int iters, void* st
         ++steps;
         cudaGraph_t graph = nullptr;
         AZ_CUDA_OK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+        const unsigned long long before = n->launches;
         rc = az_step_eager(n, f, s);
+        g.kernels = n->launches - before;
         cudaError_t ce = cudaStreamEndCapture(s, &graph);
         if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
         if (ce != cudaSuccess) return az_fail(AZ_ECUDA, std::string("graph capture: ") + cudaGetErrorString(ce));
@@ -533,6 +579,7 @@ extern "C" int az_forest_search_net(az_forest* f, az_net* n, int iters, void* st
         const int burst = steps <= 1 ? (d->vl == 1 ? iters + 1 - steps : std::max(8, iters / d->vl)) : 4;
         for (int i = 0; i < burst; ++i) {
             AZ_CUDA_OK(cudaGraphLaunch(g.exec, s));
+            n->launches += g.kernels;
             ++steps;
         }
         if ((rc = az_forest_counts(f, nullptr, &done, s))) return rc;
@@ -549,4 +596,33 @@ extern "C" int az_net_invalidate_graphs(az_net* n) {
         g_graphs.erase(it);
     }
     return AZ_OK;
+}
+
+// ---- per-kernel timing of eager forward passes (CUDA events on the launching stream) -------
+extern "C" int az_net_profile(az_net* n, int enable) {
+    if (!n) return az_fail(AZ_EINVAL, "az_net_profile: null");
+    n->prof_on = enable != 0;
+    if (enable) {
+        for (int k = 0; k < 16; ++k) { n->prof_ms[k] = 0; n->prof_n[k] = 0; }
+    }
+    return AZ_OK;
+}
+
+// Synchronises, folds pending event pairs into totals.  names_out: AZ_K_COUNT C strings.
+extern "C" int az_net_profile_read(az_net* n, int max_kinds, const char** names_out, double* ms_out, long long* count_out) {
+    if (!n) return az_fail(AZ_EINVAL, "az_net_profile_read: null");
+    AZ_CUDA_OK(cudaDeviceSynchronize());
+    for (auto& r : n->prof_pending) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) { n->prof_ms[r.kind] += ms; n->prof_n[r.kind] += 1; }
+        cudaEventDestroy(r.a); cudaEventDestroy(r.b);
+    }
+    n->prof_pending.clear();
+    const int k = max_kinds < AZ_K_COUNT ? max_kinds : AZ_K_COUNT;
+    for (int i = 0; i < k; ++i) {
+        if (names_out) names_out[i] = AZ_K_NAMES[i];
+        if (ms_out) ms_out[i] = n->prof_ms[i];
+        if (count_out) count_out[i] = n->prof_n[i];
+    }
+    return k;
 }

@@ -44,6 +44,8 @@ _SIGS = {
     "az_forest_search_net": (i32, [vp, vp, i32, vp]),
     "az_net_invalidate_graphs": (i32, [vp]),
     "az_forest_read_leaves": (i32, [vp, i32, vp, vp, vp, vp, vp, vp]),
+    "az_net_profile": (i32, [vp, i32]),
+    "az_net_profile_read": (i32, [vp, i32, vp, vp, vp]),
     "az_gemm_bf16": (i32, [vp, i32, vp, vp, vp, i32, vp, i32, i32, i32, i32, i32, vp]),
 }
 # entry points added by later translation units; bound when present in the header

@@ -129,6 +129,9 @@ AZ_API long long az_net_launch_count(az_net* n);
  * one CUDA graph per step (advance + net), no per-node host work. */
 AZ_API int az_forest_search_net(az_forest* f, az_net* n, int iters, void* stream);
 AZ_API int az_net_invalidate_graphs(az_net* n);
+/* Per-kernel CUDA-event timing of eager forward passes (roofline numbers of bench.py). */
+AZ_API int az_net_profile(az_net* n, int enable);
+AZ_API int az_net_profile_read(az_net* n, int max_kinds, const char** names_out, double* ms_out, long long* count_out);
 
 #ifdef __cplusplus
 }
