@@ -1,0 +1,294 @@
+#!/usr/bin/env python
+"""Benchmark of the self-play hot path (BASELINE.json: MCTS simulations/s).
+
+A "step" is one move search for every concurrent game: n_trees x `iters` simulations of the
+reference's loop (ai/mcts.py:16) incl. the policy/value net on every leaf.  Default workload
+= BASELINE.json configs[1]: Connect4 6x7, 4096 concurrent games, 800 sims/move, virtual-loss
+batch 1 (the reference's sequential search), random-init main.py:134 net (D=512, patch 5,
+8 heads, depth 1).  `--workload gomoku` runs configs[2] (Gomoku 7x7, 8192 games, vl=8).
+
+  value  device-timed (CUDA events on the launching stream), root positions already in HBM
+  e2e    wall clock through the C ABI with HOST buffers: pinned float32 root planes in,
+         visit counts + root Q out, every step
+  --impl reference   the reference's CPU implementation of the same path (the oracle port of
+         its single-threaded Python search + batch-1 torch net), one process per host core.
+
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "connect4": dict(game="connect4", rows=6, trees=4096, iters=800, vl=1, max_plies=7,
+                     name="connect4_6x7_4096games_800sims_vl1_net512x1"),
+    "gomoku": dict(game="gomoku", rows=7, trees=8192, iters=800, vl=8, max_plies=12,
+                   name="gomoku_7x7_8192games_800sims_vl8_net512x1"),
+}
+NET = dict(dim=512, depth=1, patch=5, heads=8)          # main.py:134
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="connect4", choices=sorted(WORKLOADS))
+    ap.add_argument("--trees", type=int, default=0)
+    ap.add_argument("--iters", type=int, default=0)
+    ap.add_argument("--vl", type=int, default=0)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--cpu-procs", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ---- CPU baseline (oracle port, subprocess workers; the only place bench.py runs oracle/) ----
+def run_cpu_baseline(wl, seconds, procs):
+    ncpu = os.cpu_count() or 1
+    procs = procs or min(ncpu, 32)
+    cmd = [sys.executable, os.path.join(ROOT, "oracle", "cpu_baseline.py"), "--game", wl["game"], "--rows", str(wl["rows"]),
+           "--dim", str(NET["dim"]), "--depth", str(NET["depth"]), "--patch", str(NET["patch"]), "--heads", str(NET["heads"]),
+           "--iters", str(wl["iters"]), "--seconds", str(seconds)]
+    env = dict(os.environ, OMP_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
+    t0 = time.time()
+    ps = [subprocess.Popen(cmd + ["--seed", str(i)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, env=env, text=True)
+          for i in range(procs)]
+    rate, sims = 0.0, 0
+    for p in ps:
+        out = p.communicate()[0].strip().splitlines()
+        if p.returncode == 0 and out:
+            r = json.loads(out[-1])
+            rate += r["sims"] / r["seconds"]
+            sims += r["sims"]
+    return dict(value=rate, unit="simulations/s", cores=procs, kind="port",
+                sample=f"{procs} single-thread processes x {seconds:.0f}s of the same search (oracle port of ai/mcts.py "
+                       f"+ batch-1 torch Net on CPU, {wl['iters']} sims/move, Dirichlet on); {sims} sims total; "
+                       f"host has {ncpu} logical cores", wall_s=time.time() - t0)
+
+
+# ---- clocks ---------------------------------------------------------------------------------
+class ClockSampler:
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index):
+        self.rows, self.p = [], None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                       "-i", str(gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def summary(self, t0, t1):
+        if self.p:
+            self.p.terminate()
+        rows = [r for t, r in self.rows if t0 <= t <= t1 and len(r) >= 8] or [r for _, r in self.rows if len(r) >= 8]
+        if not rows:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        sm = sorted(int(float(r[1])) for r in rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[4 + i].lower().startswith("active") for r in rows)]
+        return dict(sm_mhz=sm[len(sm) // 2], sm_max_mhz=int(float(rows[0][2])), reasons=reasons, samples=len(rows),
+                    power_w_max=max(float(r[3]) for r in rows))
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return dict(tflops=p["bf16_tflops_sustained"], hbm=p["hbm_gbs"], src="measured (MEASURED_PEAKS.json, sustained bf16)")
+    except Exception:
+        return dict(tflops=1400.0, hbm=6650.0, src="fallback (B200_PROFILING.md: ~1.4 PF sustained, 6.65 TB/s)")
+
+
+def game_class(wl):
+    from alpha_zero_b200 import games
+    G = {"connect4": games.Connect4, "gomoku": games.Gomoku, "tictactoe": games.TicTacToe}[wl["game"]]
+    if wl["game"] == "gomoku":
+        G.rows = G.cols = wl["rows"]
+        G.action_dim = G.state_dim = wl["rows"] ** 2
+    return G
+
+
+def run_b200(args, wl, rank, world):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import alpha_zero_b200 as az
+    from alpha_zero_b200.ai.nn import Net, B200Net
+    from alpha_zero_b200.synth import random_roots
+
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    G = game_class(wl)
+    n, iters, vl = wl["trees"], wl["iters"], wl["vl"]
+    A, T = G.action_dim, G.rows * G.cols + 1
+    torch.manual_seed(0)                                              # identical random-init weights on every rank
+    model = Net((G.rows, G.cols), NET["patch"], NET["dim"], A, NET["heads"], NET["depth"], G.feature_dim, dropout=0.1).eval()
+    stream = torch.cuda.Stream()
+    eng = B200Net(model, max_batch=n * vl)
+    forest = az.Forest(az.game_spec(wl["game"], wl["rows"]), n, iters, vl=vl, stream=stream.cuda_stream)
+    rng = np.random.default_rng(1234 + rank)                          # Philox-free: host NumPy, per-rank stream
+    total = args.warmup + args.steps
+    roots = [random_roots(G, n, wl["max_plies"], rng) for _ in range(total)]
+    noise = [rng.dirichlet([0.03] * A, size=n) for _ in range(total)]
+    pinned = torch.empty((n, G.feature_dim, G.rows, G.cols), dtype=torch.float32).pin_memory()
+    pin_np = pinned.numpy()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def one_step(i, e2e):
+        planes, players, mcs = roots[i]
+        if e2e:
+            np.copyto(pin_np, planes)                                 # the step's inputs start in pinned host memory
+            forest.set_roots_planes(pin_np, players, mcs)             # H2D inside the timed region
+        forest.set_noise(noise[i])
+        forest.search_net(eng, iters)
+        if e2e:
+            return forest.root_visits()                               # D2H of the step's result
+
+    clocks = ClockSampler(local)
+    # ---- value: device time, inputs resident --------------------------------------------------
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches0 = 0
+    for i in range(total):
+        planes, players, mcs = roots[i]
+        forest.set_roots_planes(planes, players, mcs)                 # upload BEFORE the timed region
+        forest.set_noise(noise[i])
+        if i == args.warmup:
+            barrier()
+            t_clock0 = time.time()
+            launches0 = eng.launch_count()
+        torch.cuda.synchronize()
+        if i >= args.warmup:
+            ev[i - args.warmup][0].record(stream)
+        forest.search_net(eng, iters)
+        if i >= args.warmup:
+            ev[i - args.warmup][1].record(stream)
+    barrier()
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    gpu_launches = eng.launch_count() - launches0 + args.steps        # + begin_move kernels
+    stats = forest.stats(reset=True)
+    # ---- e2e: wall clock through the public API with host buffers ------------------------------
+    for i in range(args.warmup):
+        one_step(i, True)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.warmup, total):
+        visits, q = one_step(i, True)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t_clock1 = time.time()
+    assert int(visits.sum()) == n * (iters - 1), "every tree must have completed its simulations"
+    if world > 1:
+        tm = torch.tensor([dev_ms, e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)                      # max over ranks
+        dev_ms, e2e_s = tm.tolist()
+    sims_per_step = n * iters * world
+    out = dict(dev_ms=dev_ms, e2e_s=e2e_s, sims_per_step=sims_per_step, gpu_launches=int(gpu_launches),
+               h2d=int(pinned.numel() * 4 + n * 8 + n * A * 8), d2h=int(n * A * 4 + n * 8), stats=stats)
+    # ---- per-kernel profile (rank 0): eager steps of one search with CUDA events ------------------
+    if rank == 0:
+        planes, players, mcs = roots[-1]
+        forest.set_roots_planes(planes, players, mcs)
+        forest.begin_move(iters)
+        adv = []
+        for s in range(min(iters, 120)):                              # 120 steps into a search
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if s == 60:
+                eng.profile(True)
+            a.record(stream)
+            forest.advance()
+            b.record(stream)
+            eng.eval_leaves(forest, stream.cuda_stream)
+            if s >= 60:
+                adv.append((a, b))
+        prof = eng.profile_read()
+        eng.profile(False)
+        leaves, _ = forest.counts()
+        out["profile"] = {k: dict(ms=v[0] / max(v[1], 1), launches=v[1]) for k, v in prof.items() if v[1]}
+        out["profile"]["forest_advance"] = dict(ms=sum(a.elapsed_time(b) for a, b in adv) / len(adv), launches=len(adv))
+        out["leaves_per_step"] = leaves
+    out["clocks"] = clocks.summary(t_clock0, t_clock1)
+    forest.close()
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return out
+
+
+def main():
+    args = parse()
+    wl = dict(WORKLOADS[args.workload])
+    for k in ("trees", "iters", "vl"):
+        if getattr(args, k):
+            wl[k] = getattr(args, k)
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    config = dict(workload=wl["name"], game=wl["game"], board=f"{wl['rows']}x{7 if wl['game'] == 'connect4' else wl['rows']}",
+                  concurrent_games_per_gpu=wl["trees"], sims_per_move=wl["iters"], vl_batch=wl["vl"],
+                  net="Net(D=512,patch=5,heads=8,depth=1) random-init, ai/nn.py / main.py:134",
+                  l2="inputs larger than L2: forest node pools + activations >> 126 MB, fresh root positions every step",
+                  parallelism=f"dp{world} (games sharded per GPU, no data-path collective)")
+    base = dict(metric="mcts_simulations_per_second", unit="simulations/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
+                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16", data="synthetic", config=config)
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        cb = run_cpu_baseline(wl, args.cpu_seconds, args.cpu_procs or min(os.cpu_count() or 1, 64))
+        line = dict(base, impl="reference", value=cb["value"], ms_per_step=wl["trees"] * wl["iters"] * world / max(cb["value"], 1e-9) * 1e3,
+                    cpu_baseline=cb, e2e=dict(value=cb["value"], unit="simulations/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                    gpu_launches=0)
+        print(json.dumps(line))
+        return
+
+    cb = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cb = run_cpu_baseline(wl, args.cpu_seconds, args.cpu_procs)
+    r = run_b200(args, wl, rank, world)
+    if rank != 0:
+        return
+    pk = peaks()
+    value = r["sims_per_step"] * args.steps / (r["dev_ms"] / 1e3)
+    e2e = r["sims_per_step"] * args.steps / r["e2e_s"]
+    line = dict(base, impl="b200", value=value, ms_per_step=r["dev_ms"] / args.steps, clocks=r["clocks"],
+                e2e=dict(value=e2e, unit="simulations/s", h2d_bytes_per_step=r["h2d"], d2h_bytes_per_step=r["d2h"]),
+                gpu_launches=r["gpu_launches"], search_stats=r["stats"])
+    prof = r.get("profile", {})
+    if "gemm_kv" in prof:
+        G = game_class(wl)
+        T = G.rows * G.cols + 1
+        flops = 2.0 * r["leaves_per_step"] * T * NET["dim"] * 2 * NET["dim"]     # [leaves*T, D] x [D, 2D]
+        ach = flops / (prof["gemm_kv"]["ms"] / 1e3) / 1e12
+        line["roofline"] = dict(kernel="az_gemm_kernel<256,bias> (K/V projection of all tokens, tcgen05)", bound="tensor",
+                                achieved=ach, peak=pk["tflops"], unit="TFLOP/s", frac=ach / pk["tflops"], traffic=None,
+                                peak_source=pk["src"], flops_per_launch=flops, ms_per_launch=prof["gemm_kv"]["ms"])
+        line["kernel_ms"] = {k: round(v["ms"], 4) for k, v in prof.items()}
+    if cb:
+        line["cpu_baseline"] = cb
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()
