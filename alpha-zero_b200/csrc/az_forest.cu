@@ -12,6 +12,7 @@
 //      up on the spot and cost a simulation each, exactly like `continue` in mcts.py:28-32).
 // Compiled with -fmad=false: every score is the reference's rounding sequence.
 #include <cstdio>
+#include <cstdlib>
 #include "az_forest.h"
 #include "az_rules.cuh"
 
@@ -584,7 +585,11 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     d.max_leaves = n_trees * vl_batch;
     d.use_noise = 0;
     f->max_iters = max_iters;
-    f->G = (g.max_children <= 9) ? 8 : 32;
+    // One warp per tree: sub-warp groups (8 lanes for the <= 9-children games) share a warp between
+    // four trees whose descents diverge and serialise; measured 4x slower on Connect4.  AZ_FOREST_GROUP=8
+    // re-enables them for experiments.
+    f->G = 32;
+    if (const char* e = getenv("AZ_FOREST_GROUP")) if (atoi(e) == 8 && g.max_children <= 9) f->G = 8;
     size_t per_group = 4 * (size_t)d.max_depth + ((g.max_children + 15) & ~15) + 2 * (size_t)g.set_slots;
     f->smem_per_group = (int)((per_group + 15) & ~(size_t)15);
     const size_t nodes = (size_t)n_trees * d.cap;

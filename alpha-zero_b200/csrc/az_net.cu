@@ -217,8 +217,8 @@ extern "C" int az_net_create(int rows, int cols, int planes, int patch, int embe
         action_dim <= 0 || max_batch <= 0)
         return az_fail(AZ_EINVAL, "az_net_create: bad arguments");
     if (embed_dim % 64 || embed_dim > 1024) return az_fail(AZ_EINVAL, "az_net_create: embed_dim must be a multiple of 64, <= 1024");
-    if (num_heads <= 0 || embed_dim % num_heads || embed_dim / num_heads > 128)
-        return az_fail(AZ_EINVAL, "az_net_create: head dim must divide embed_dim and be <= 128");
+    if (num_heads <= 0 || embed_dim % num_heads || embed_dim / num_heads > 128 || (embed_dim / num_heads) % 8)
+        return az_fail(AZ_EINVAL, "az_net_create: head dim must divide embed_dim, be a multiple of 8 and <= 128");
     if (rows * cols + 1 > 256) return az_fail(AZ_EINVAL, "az_net_create: at most 255 board cells");
     az_net* n = new az_net();
     n->rows = rows; n->cols = cols; n->C = planes; n->patch = patch; n->D = embed_dim; n->H = num_heads;

@@ -248,43 +248,43 @@ __global__ void __launch_bounds__(128) az_attention_kernel(AzBatch batch, const 
 
 // Attention of the LAST block restricted to the cls query (only x[:,0] feeds the heads,
 // ai/nn.py:81).  One warp per (board, head); kv rows hold [k | v] (2D wide), qc holds the cls
-// query rows [items][D].  hd <= 128, T <= 256.
+// query rows [items][D].  hd <= 128 (multiple of 8), T <= 256.
+//   scores : lane = token; each lane streams its token's K slice (hd bf16, 16-byte loads)
+//   softmax: warp max / sum
+//   output : lane = 2 head dims; V rows are read coalesced (4 bytes per lane), 4 tokens in flight
 __global__ void __launch_bounds__(128) az_cls_attention_kernel(AzBatch batch, const bf16* __restrict__ qc,
                                                                const bf16* __restrict__ kv, bf16* __restrict__ oc, int T,
                                                                int D, int H) {
+    __shared__ float s_q[4][128];
     const int items = az_batch_items(batch);
-    const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int lane = threadIdx.x & 31;
+    const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int w = blockIdx.x * (blockDim.x >> 5) + wib;
     const int b = w / H, h = w - b * H;
     if (b >= items) return;
     const int hd = D / H;
-    float q[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const int d = lane + 32 * j;
-        q[j] = d < hd ? __bfloat162float(qc[(size_t)b * D + h * hd + d]) : 0.f;
-    }
+    for (int d = lane; d < hd; d += 32) s_q[wib][d] = __bfloat162float(qc[(size_t)b * D + h * hd + d]);
+    __syncwarp();
     const bf16* kb = kv + (size_t)b * T * 2 * D + h * hd;
     const float scale = rsqrtf((float)hd);
     float s[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) s[j] = -1e30f;
-    for (int t = 0; t < T; ++t) {
-        float part = 0.f;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int d = lane + 32 * j;
-            if (d < hd) part += q[j] * __bfloat162float(kb[(size_t)t * 2 * D + d]);
-        }
-        part = az_warp_sum(part) * scale;
-        if ((t & 31) == lane) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) if (j == (t >> 5)) s[j] = part;
-        }
-    }
     float mx = -1e30f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) mx = fmaxf(mx, s[j]);
+    for (int j = 0; j < 8; ++j) {
+        const int t = j * 32 + lane;
+        s[j] = -1e30f;
+        if (t < T) {
+            const uint4* kr = reinterpret_cast<const uint4*>(kb + (size_t)t * 2 * D);
+            float acc = 0.f;
+            for (int c = 0; c < hd / 8; ++c) {
+                float f[8];
+                az_unpack8(__ldg(kr + c), f);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc += f[e] * s_q[wib][c * 8 + e];
+            }
+            s[j] = acc * scale;
+            mx = fmaxf(mx, s[j]);
+        }
+    }
     mx = az_warp_max(mx);
     float sum = 0.f;
 #pragma unroll
@@ -292,25 +292,33 @@ __global__ void __launch_bounds__(128) az_cls_attention_kernel(AzBatch batch, co
         s[j] = (j * 32 + lane < T) ? __expf(s[j] - mx) : 0.f;
         sum += s[j];
     }
-    sum = az_warp_sum(sum);
-    float o[4] = {0.f, 0.f, 0.f, 0.f};
+    const float inv = 1.0f / az_warp_sum(sum);
     const bf16* vb = kb + D;
-    for (int t = 0; t < T; ++t) {
-        float pt = 0.f;
+    float o[2][2] = {{0.f, 0.f}, {0.f, 0.f}};                // dims 2*lane(+1) and 64 + 2*lane(+1)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) if (j == (t >> 5)) pt = s[j];
-        pt = __shfl_sync(0xffffffffu, pt, t & 31);
+    for (int j = 0; j < 8; ++j) {
+        if (j * 32 >= T) break;
+        const int tn = min(32, T - j * 32);
+#pragma unroll 4
+        for (int tt = 0; tt < tn; ++tt) {
+            const float pt = __shfl_sync(0xffffffffu, s[j], tt);
+            const bf16* vr = vb + (size_t)(j * 32 + tt) * 2 * D;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int d = lane + 32 * j;
-            if (d < hd) o[j] += pt * __bfloat162float(vb[(size_t)t * 2 * D + d]);
+            for (int u = 0; u < 2; ++u) {
+                const int d = u * 64 + 2 * lane;
+                if (d < hd) {
+                    const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(vr + d));
+                    o[u][0] += pt * v.x;
+                    o[u][1] += pt * v.y;
+                }
+            }
         }
     }
-    const float inv = 1.0f / sum;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const int d = lane + 32 * j;
-        if (d < hd) oc[(size_t)b * D + h * hd + d] = __float2bfloat16(o[j] * inv);
+    for (int u = 0; u < 2; ++u) {
+        const int d = u * 64 + 2 * lane;
+        if (d < hd)
+            *reinterpret_cast<__nv_bfloat162*>(oc + (size_t)b * D + h * hd + d) = __floats2bfloat162_rn(o[u][0] * inv, o[u][1] * inv);
     }
 }
 

@@ -213,15 +213,16 @@ def run_b200(args, wl, rank, world):
         forest.set_roots_planes(planes, players, mcs)
         forest.begin_move(iters)
         adv = []
-        for s in range(min(iters, 120)):                              # 120 steps into a search
+        nprof = min(iters, 120)                                       # up to 120 steps into a search
+        for s in range(nprof):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            if s == 60:
+            if s == nprof // 2:
                 eng.profile(True)
             a.record(stream)
             forest.advance()
             b.record(stream)
             eng.eval_leaves(forest, stream.cuda_stream)
-            if s >= 60:
+            if s >= nprof // 2:
                 adv.append((a, b))
         prof = eng.profile_read()
         eng.profile(False)
