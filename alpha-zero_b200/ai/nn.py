@@ -140,6 +140,9 @@ class B200Net:
         k = _lib.check(self._L.az_net_profile_read(self.h, 16, names, ms, cnt), "az_net_profile_read")
         return {names[i].decode(): (ms[i], cnt[i]) for i in range(k)}
 
+    def proj_width(self):
+        return int(self._L.az_net_proj_width(self.h))
+
     def launch_count(self):
         return int(self._L.az_net_launch_count(self.h))
 

@@ -159,7 +159,12 @@ __global__ void __launch_bounds__(128) az_advance_kernel(AzForestDev f, int smem
     const int root_mc = f.root_mc[tree];
     int started = sims;
     int np = 0;
-    while (started < f.iters && np < f.vl) {
+    // A tree whose best line ends in a terminal node burns simulation after simulation without
+    // ever needing the evaluator; left unbounded, one such tree (up to `iters` descents) sets the
+    // duration of the whole launch.  While nothing is pending the launch may stop after a few of
+    // them -- the next launch resumes the very same sequence, so results do not change.
+    constexpr unsigned kMaxTerminalPerLaunch = 4;
+    while (started < f.iters && np < f.vl && !(np == 0 && st_term >= kMaxTerminalPerLaunch)) {
         AzBoard<NW> b = rootb;
         int player = root_player, mc = root_mc, len = 1;
         uint32_t node = 0;

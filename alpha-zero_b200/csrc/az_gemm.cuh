@@ -31,6 +31,8 @@ struct AzGemmArgs {
     int m_item_offset;          // ... this launch handles items [offset, offset + cap)
     int m_item_cap;
     int m_rows_per_item;        // rows per item (tokens per board, or 1)
+    float* out_f32;             // optional: columns >= f32_col0 are written here as fp32 [M][64] instead
+    int f32_col0;
 };
 
 __device__ __forceinline__ int az_gemm_rows(const AzGemmArgs& a) {
@@ -45,8 +47,9 @@ struct AzGemmCfg {
     static constexpr int BM = 128, BK = 64;
     static constexpr int A_BYTES = BM * BK * 2;              // 16 KB
     static constexpr int B_BYTES = BN * BK * 2;
-    static constexpr int STAGES = BN == 256 ? 4 : 6;
-    static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
+    static constexpr int STAGES = BN >= 192 ? 4 : 6;
+    static constexpr int TMEM_COLS = 2 * BN <= 32 ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
+    static constexpr int ACC_STRIDE = TMEM_COLS / 2;          // TMEM columns between the two accumulator stages
     static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;   // + barriers + align slack
 };
 
@@ -125,7 +128,7 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                     const uint64_t db = azptx::umma_desc_k128(azptx::smem_u32(s_b + stage * Cfg::B_BYTES));
 #pragma unroll
                     for (int k = 0; k < Cfg::BK / 16; ++k)    // +32 bytes (>>4 = 2) per K=16 step
-                        azptx::umma_bf16(tmem_base + as * BN, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                        azptx::umma_bf16(tmem_base + as * Cfg::ACC_STRIDE, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
                     azptx::umma_commit(&empty[stage]);
                     if (kb == kblocks - 1) azptx::umma_commit(&tfull[as]);
                 }
@@ -148,10 +151,19 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
                 uint32_t r[32];
-                azptx::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + c * 32, r);
+                azptx::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * Cfg::ACC_STRIDE + c * 32, r);
                 azptx::tmem_ld_wait();
                 const int col0 = n_blk * BN + c * 32;
-                if (live) {
+                if (live && args.out_f32 && col0 >= args.f32_col0) {      // fp32 side output (attention scores)
+                    const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
+                    float4* op = reinterpret_cast<float4*>(args.out_f32 + (size_t)row * 64 + (col0 - args.f32_col0));
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float4 bb = __ldg(b4 + i);
+                        op[i] = make_float4(__uint_as_float(r[4 * i + 0]) + bb.x, __uint_as_float(r[4 * i + 1]) + bb.y,
+                                            __uint_as_float(r[4 * i + 2]) + bb.z, __uint_as_float(r[4 * i + 3]) + bb.w);
+                    }
+                } else if (live) {
                     const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
                     uint4 rv[4];
                     if (EPI == AZ_EPI_RESID) {

@@ -63,7 +63,7 @@ static int az_make_tmap(CUtensorMap* out, const void* ptr, uint64_t rows, uint64
 
 static int g_num_sms = 0;
 
-static int az_pick_bn(int N) { return N % 256 == 0 ? 256 : (N % 128 == 0 ? 128 : (N % 64 == 0 ? 64 : 0)); }
+static int az_pick_bn(int N) { return N % 256 == 0 ? 256 : (N % 192 == 0 ? 192 : (N % 128 == 0 ? 128 : (N % 64 == 0 ? 64 : 0))); }
 
 template <int BN, int EPI>
 static int az_launch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& a, int max_rows, cudaStream_t s) {
@@ -95,7 +95,7 @@ static int az_launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const Az
         if (epi == AZ_EPI_GELU) return az_launch_gemm_t<BN_, AZ_EPI_GELU>(ta, tb, a, max_rows, s);   \
         return az_launch_gemm_t<BN_, AZ_EPI_RESID>(ta, tb, a, max_rows, s);                    \
     }
-    AZ_G(256) AZ_G(128) AZ_G(64)
+    AZ_G(256) AZ_G(192) AZ_G(128) AZ_G(64)
 #undef AZ_G
     return az_fail(AZ_EINVAL, "gemm: unsupported tile");
 }
@@ -128,6 +128,7 @@ extern "C" int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const
 // The network object
 // ======================================================================================
 #include "az_net_kernels.cuh"
+#include "az_embed_mma.cuh"
 
 struct AzBlockW {
     float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
@@ -142,9 +143,20 @@ struct az_net {
     bool finalized = false;
     std::vector<void*> allocs;
     std::map<std::string, std::vector<float>> host;   // raw fp32 parameters until finalize
+    std::vector<float> host_folded_w_in, host_folded_b_in;   // block 0 in_proj with norm1's affine folded in
     // embedding
     bf16* wt_embed = nullptr;
     float* posb = nullptr;
+    bf16* w_emb_mma = nullptr;           // [D][kpad]: conv taps | pos-emb rows (tensor-core embedding)
+    int emb_kc = 0, emb_kblocks = 0;     // 0 kblocks: shape not supported, CUDA-core embedding is used
+    CUtensorMap tm_emb;
+    float *ones = nullptr, *zeros = nullptr;
+    // depth-1 nets: cls query folded into the projection (V + 64 score columns), see az_cls_attention_folded_kernel
+    bool folded = false;
+    int n2 = 0;
+    bf16* w_vs = nullptr;
+    float *b_vs = nullptr, *sc = nullptr;
+    CUtensorMap tm_vs;
     std::vector<AzBlockW> blk;
     float *lnf_g = nullptr, *lnf_b = nullptr, *w_pol = nullptr, *b_pol = nullptr, *w_val = nullptr, *b_val = nullptr;
     // activations (one chunk)
@@ -297,6 +309,25 @@ extern "C" int az_net_finalize(az_net* n) {
                     posb[((size_t)stm * T + t) * D + d] = v;
                 }
         if ((rc = az_upload_f32(n, &n->posb, posb))) return rc;
+        // tensor-core embedding: A = [taps | one-hot(t)], Wemb = [conv ; pos + bias], K padded to 64/128
+        const int kc = C * P * P;
+        n->emb_kc = kc;
+        n->emb_kblocks = 0;
+        const bool d_ok = (D <= 256 && D % 16 == 0) || D == 512;
+        if (kc + T <= 128 && d_ok && !getenv("AZ_EMBED_SIMT")) {
+            const int kb = (kc + T + 63) / 64, kpad = kb * 64;
+            std::vector<float> we((size_t)D * kpad, 0.f);
+            for (int d = 0; d < D; ++d) {
+                for (int k = 0; k < kc; ++k) we[(size_t)d * kpad + k] = (*cw)[(size_t)d * kc + k];
+                for (int t = 0; t < T; ++t)
+                    we[(size_t)d * kpad + kc + t] = (*pos)[(size_t)t * D + d] + (t == 0 ? (*cls)[d] : (*cb)[d]);
+            }
+            if ((rc = az_upload_bf16(n, &n->w_emb_mma, we.data(), we.size()))) return rc;
+            if ((rc = az_make_tmap(&n->tm_emb, n->w_emb_mma, D, kpad, kpad, D > 256 ? 256 : D))) return rc;
+            n->emb_kblocks = kb;
+        }
+        std::vector<float> one((size_t)D, 1.f), zero((size_t)D, 0.f);
+        if ((rc = az_upload_f32(n, &n->ones, one)) || (rc = az_upload_f32(n, &n->zeros, zero))) return rc;
     }
     // ---- blocks
     for (int l = 0; l < n->L; ++l) {
@@ -308,11 +339,24 @@ extern "C" int az_net_finalize(az_net* n) {
         AZ_P(wo, p + "attn.out_proj.weight", (size_t)D * D) AZ_P(bo, p + "attn.out_proj.bias", (size_t)D)
         AZ_P(w1, p + "mlp.0.weight", (size_t)4 * D * D) AZ_P(bb1, p + "mlp.0.bias", (size_t)4 * D)
         AZ_P(w2, p + "mlp.3.weight", (size_t)4 * D * D) AZ_P(bb2, p + "mlp.3.bias", (size_t)D)
+        std::vector<float> wi_f(*wi), bi_f(*bi);
+        if (l == 0) {        // norm1 of block 0 runs inside the embedding kernel without its affine:
+                             // W' = W diag(gamma), b' = b + W beta  (exact in real arithmetic)
+            for (int r = 0; r < 3 * D; ++r) {
+                double acc = 0.0;
+                for (int k = 0; k < D; ++k) {
+                    acc += (double)(*wi)[(size_t)r * D + k] * (*be1)[k];
+                    wi_f[(size_t)r * D + k] = (*wi)[(size_t)r * D + k] * (*g1)[k];
+                }
+                bi_f[r] = (*bi)[r] + (float)acc;
+            }
+        }
+        if (l == 0) { n->host_folded_w_in = wi_f; n->host_folded_b_in = bi_f; }
         if ((rc = az_upload_f32(n, &w.ln1_g, *g1)) || (rc = az_upload_f32(n, &w.ln1_b, *be1)) ||
             (rc = az_upload_f32(n, &w.ln2_g, *g2)) || (rc = az_upload_f32(n, &w.ln2_b, *be2)) ||
-            (rc = az_upload_f32(n, &w.b_in, *bi)) || (rc = az_upload_f32(n, &w.b_out, *bo)) ||
+            (rc = az_upload_f32(n, &w.b_in, bi_f)) || (rc = az_upload_f32(n, &w.b_out, *bo)) ||
             (rc = az_upload_f32(n, &w.b1, *bb1)) || (rc = az_upload_f32(n, &w.b2, *bb2)) ||
-            (rc = az_upload_bf16(n, &w.w_in, wi->data(), wi->size())) || (rc = az_upload_bf16(n, &w.w_out, wo->data(), wo->size())) ||
+            (rc = az_upload_bf16(n, &w.w_in, wi_f.data(), wi_f.size())) || (rc = az_upload_bf16(n, &w.w_out, wo->data(), wo->size())) ||
             (rc = az_upload_bf16(n, &w.w1, w1->data(), w1->size())) || (rc = az_upload_bf16(n, &w.w2, w2->data(), w2->size())))
             return rc;
         if ((rc = az_make_tmap(&w.tm_in, w.w_in, 3 * D, D, D, az_pick_bn(3 * D))) ||
@@ -322,6 +366,54 @@ extern "C" int az_net_finalize(az_net* n) {
             (rc = az_make_tmap(&w.tm_w1, w.w1, 4 * D, D, D, az_pick_bn(4 * D))) ||
             (rc = az_make_tmap(&w.tm_w2, w.w2, D, 4 * D, 4 * D, az_pick_bn(D))))
             return rc;
+    }
+    // ---- depth 1: fold the (constant) cls query into the K projection
+    n->folded = false;
+    {
+        const int H = n->H, hd = D / H;
+        const bool pow2 = (hd & (hd - 1)) == 0;
+        if (n->L == 1 && pow2 && hd >= 8 && H <= 64 && !getenv("AZ_NO_FOLD")) {
+            const std::vector<float>& wi = n->host_folded_w_in;
+            const std::vector<float>& bi = n->host_folded_b_in;
+            auto r16 = [](float v) { return __bfloat162float(__float2bfloat16(v)); };
+            std::vector<double> x0(D), xh(D), q(D);
+            double mean = 0, var = 0;
+            for (int d = 0; d < D; ++d) {
+                const float raw = (*pos)[d] + (*cls)[d];
+                x0[d] = n->emb_kblocks ? r16(raw) : raw;    // the tensor-core embedding carries pos/cls in bf16
+                mean += x0[d];
+            }
+            mean /= D;
+            for (int d = 0; d < D; ++d) var += (x0[d] - mean) * (x0[d] - mean);
+            const double rstd = 1.0 / sqrt(var / D + 1e-5);
+            for (int d = 0; d < D; ++d) xh[d] = r16((float)((x0[d] - mean) * rstd));
+            for (int r = 0; r < D; ++r) {
+                double acc = bi[r];
+                for (int k = 0; k < D; ++k) acc += (double)r16(wi[(size_t)r * D + k]) * xh[k];
+                q[r] = acc;
+            }
+            const int N2 = D + 64;
+            const double scale = 1.0 / sqrt((double)hd);
+            std::vector<float> w2((size_t)N2 * D, 0.f), b2((size_t)N2, 0.f);
+            for (int r = 0; r < D; ++r) {
+                for (int k = 0; k < D; ++k) w2[(size_t)r * D + k] = wi[(size_t)(2 * D + r) * D + k];
+                b2[r] = bi[2 * D + r];
+            }
+            for (int h = 0; h < H; ++h) {
+                double c = 0;
+                for (int d = 0; d < hd; ++d) c += q[h * hd + d] * bi[D + h * hd + d];
+                b2[D + h] = (float)(c * scale);
+                for (int k = 0; k < D; ++k) {
+                    double u = 0;
+                    for (int d = 0; d < hd; ++d) u += q[h * hd + d] * (double)r16(wi[(size_t)(D + h * hd + d) * D + k]);
+                    w2[(size_t)(D + h) * D + k] = (float)(u * scale);
+                }
+            }
+            if ((rc = az_upload_bf16(n, &n->w_vs, w2.data(), w2.size())) || (rc = az_upload_f32(n, &n->b_vs, b2))) return rc;
+            if ((rc = az_make_tmap(&n->tm_vs, n->w_vs, N2, D, D, az_pick_bn(N2)))) return rc;
+            n->n2 = N2;
+            n->folded = true;
+        }
     }
     // ---- heads
     AZ_P(gf, "norm.weight", (size_t)D) AZ_P(bf, "norm.bias", (size_t)D)
@@ -341,6 +433,7 @@ extern "C" int az_net_finalize(az_net* n) {
         (rc = az_net_alloc(n, &n->xc, B * D)) || (rc = az_net_alloc(n, &n->xcn, B * D)) ||
         (rc = az_net_alloc(n, &n->hc, B * 4 * D)) || (rc = az_net_alloc(n, &n->xc2, B * D)))
         return rc;
+    if (n->folded && (rc = az_net_alloc(n, &n->sc, M * 64))) return rc;
     if (deep && ((rc = az_net_alloc(n, &n->ao, M * D)) || (rc = az_net_alloc(n, &n->hbuf, M * 4 * D)))) return rc;
     const int nw = cells <= 64 ? 1 : AZ_MAX_WORDS;
     if ((rc = az_net_alloc(n, &n->in_words, B * 2 * nw)) || (rc = az_net_alloc(n, &n->in_player, B)) ||
@@ -389,13 +482,40 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
     const int cap = batch.cap;                               // grid bound (items)
     const long long max_rows = (long long)cap * T;
     int rc;
-    // 1. boards -> tokens -> LN1 of block 0
-    AzEmbedArgs ea{};
-    ea.batch = batch; ea.leaf_words = words; ea.leaf_player = players; ea.nw = nw;
-    ea.rows = n->rows; ea.cols = n->cols; ea.planes = n->C; ea.patch = n->patch; ea.D = D; ea.T = T;
-    ea.wt = n->wt_embed; ea.posb = n->posb; ea.ln_g = n->blk[0].ln1_g; ea.ln_b = n->blk[0].ln1_b;
-    ea.x = n->x; ea.xn = n->xn; ea.write_all_x = L > 1;
-    {
+    // 1. boards -> tokens -> LN1 of block 0 (affine folded into block 0's in_proj at load time)
+    if (n->emb_kblocks) {
+        AzProfScope ps(n, AZ_K_EMBED, s);
+        AzEmbedMmaArgs ma{};
+        ma.batch = batch; ma.leaf_words = words; ma.leaf_player = players; ma.nw = nw;
+        ma.rows = n->rows; ma.cols = n->cols; ma.planes = n->C; ma.patch = n->patch; ma.D = D; ma.T = T;
+        ma.kc = n->emb_kc; ma.kblocks = n->emb_kblocks; ma.x = n->x; ma.xn = n->xn; ma.write_all_x = L > 1;
+        const size_t smem = az_embed_mma_smem(D, n->emb_kblocks, T, n->patch * n->patch);
+        if (!g_num_sms) {
+            int dev = 0;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+        }
+        const int tiles = (int)((max_rows + 127) / 128);
+        const int grid = tiles < g_num_sms ? (tiles > 0 ? tiles : 1) : g_num_sms;
+#define AZ_EMB(COLS)                                                                                                  \
+    {                                                                                                                 \
+        static bool done = false;                                                                                     \
+        if (!done) {                                                                                                  \
+            AZ_CUDA_OK(cudaFuncSetAttribute(az_embed_mma_kernel<COLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
+            done = true;                                                                                              \
+        }                                                                                                             \
+        az_embed_mma_kernel<COLS><<<grid, 288, smem, s>>>(n->tm_emb, ma);                                             \
+    }
+        if (D <= 64) AZ_EMB(64) else if (D <= 128) AZ_EMB(128) else if (D <= 256) AZ_EMB(256) else AZ_EMB(512)
+#undef AZ_EMB
+        AZ_CUDA_OK(cudaGetLastError());
+        ++n->launches;
+    } else {
+        AzEmbedArgs ea{};
+        ea.batch = batch; ea.leaf_words = words; ea.leaf_player = players; ea.nw = nw;
+        ea.rows = n->rows; ea.cols = n->cols; ea.planes = n->C; ea.patch = n->patch; ea.D = D; ea.T = T;
+        ea.wt = n->wt_embed; ea.posb = n->posb; ea.ln_g = n->ones; ea.ln_b = n->zeros;
+        ea.x = n->x; ea.xn = n->xn; ea.write_all_x = L > 1;
         AzProfScope ps(n, AZ_K_EMBED, s);
         const int grid = (int)((max_rows + 7) / 8);
         az_ln_dispatch(D, [&](auto nv) { az_embed_ln_kernel<decltype(nv)::value><<<grid, 256, 0, s>>>(ea); });
@@ -436,6 +556,19 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
     {                                                        // last block, cls-pruned
         AzBlockW& w = n->blk[L - 1];
         if (L > 1) layernorm(T, n->x, D, n->xn, D, w.ln1_g, w.ln1_b);
+        if (n->folded) {
+            // V of every token + the 64 folded score columns (fp32) in one projection
+            AzGemmArgs ga = az_gargs(batch, T, n->b_vs, nullptr, 0, n->qkv, n->n2, n->n2, D);
+            ga.out_f32 = n->sc;
+            ga.f32_col0 = D;
+            if ((rc = gemm(AZ_K_GEMM_KV, n->tm_xn, n->tm_vs, ga, AZ_EPI_BIAS, (int)max_rows))) return rc;
+            {
+                AzProfScope ps(n, AZ_K_CLS_ATT, s);
+                az_cls_attention_folded_kernel<<<(cap * H + 3) / 4, 128, 0, s>>>(batch, n->sc, n->qkv, n->n2, n->oc, T, D, H);
+            }
+            AZ_CUDA_OK(cudaGetLastError());
+            n->launches -= 1;                                 // one kernel fewer than the generic path
+        } else {
         // K,V of every token; Q of the cls token only (rows of xn with stride T*D)
         if ((rc = gemm(AZ_K_GEMM_KV, n->tm_xn, w.tm_kv, az_gargs(batch, T, w.b_in + D, nullptr, 0, n->qkv, 2 * D, 2 * D, D), AZ_EPI_BIAS, (int)max_rows))) return rc;
         if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_xn_cls, w.tm_q, az_gargs(batch, 1, w.b_in, nullptr, 0, n->qc, D, D, D), AZ_EPI_BIAS, cap))) return rc;
@@ -444,6 +577,7 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
             az_cls_attention_kernel<<<(cap * H + 3) / 4, 128, 0, s>>>(batch, n->qc, n->qkv, n->oc, T, D, H);
         }
         AZ_CUDA_OK(cudaGetLastError());
+        }
         if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out, az_gargs(batch, 1, w.b_out, n->x, T * D, n->xc, D, D, D), AZ_EPI_RESID, cap))) return rc;
         layernorm(1, n->xc, D, n->xcn, D, w.ln2_g, w.ln2_b);
         if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_xcn, w.tm_w1, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap))) return rc;
@@ -519,6 +653,10 @@ extern "C" int az_net_forward_planes(az_net* n, const float* planes_host, int B,
     cudaFree(pl_dev);
     return AZ_OK;
 }
+
+// Output width of the all-token projection of the last block (the dominant GEMM): D + 64 when the
+// cls query is folded (depth 1), else 2D (K and V).
+extern "C" int az_net_proj_width(az_net* n) { return n ? (n->folded ? n->n2 : 2 * n->D) : 0; }
 
 extern "C" long long az_net_launch_count(az_net* n) { return n ? (long long)n->launches : 0; }
 

@@ -398,3 +398,64 @@ __global__ void __launch_bounds__(128) az_head_kernel(AzHeadArgs a) {
         if (a.logits) a.logits[ob + i] = lg[i];
     }
 }
+
+// cls-query attention when the net has ONE block: the cls query is then a constant of the
+// model (LayerNorm(cls + pos[0]) does not depend on the board), so q.K^T is folded into the
+// projection itself: scores[t][h] = xn[t] . (Wk_h^T q_h)/sqrt(hd) + c_h arrive as 64 extra
+// fp32 output columns of the V projection and K is never materialised.
+// One warp per (board, head): softmax over the T scores, then sum_t p_t V[t, head] with
+// 16-byte V loads (lane = token group x 8-dim chunk).  hd = 8 * 2^k <= 128.
+__global__ void __launch_bounds__(128) az_cls_attention_folded_kernel(AzBatch batch, const float* __restrict__ sc,
+                                                                      const bf16* __restrict__ v, int ldv,
+                                                                      bf16* __restrict__ oc, int T, int D, int H) {
+    const int items = az_batch_items(batch);
+    const int lane = threadIdx.x & 31;
+    const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int b = w / H, h = w - b * H;
+    if (b >= items) return;
+    const int hd = D / H, chunks = hd >> 3, groups = 32 / chunks;
+    const float* sb = sc + (size_t)b * T * 64 + h;
+    float s[8];
+    float mx = -1e30f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int t = j * 32 + lane;
+        s[j] = t < T ? __ldg(sb + (size_t)t * 64) : -1e30f;
+        mx = fmaxf(mx, s[j]);
+    }
+    mx = az_warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        s[j] = (j * 32 + lane < T) ? __expf(s[j] - mx) : 0.f;
+        sum += s[j];
+    }
+    const float inv = 1.0f / az_warp_sum(sum);
+    const int grp = lane / chunks, c = lane - grp * chunks;
+    const bf16* vb = v + (size_t)b * T * ldv + h * hd + c * 8;
+    float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        if (j * 32 >= T) break;
+#pragma unroll 4
+        for (int base = 0; base < 32; base += groups) {
+            const int tt = base + grp;                      // token within this block of 32
+            const float pt = __shfl_sync(0xffffffffu, s[j], tt);
+            const int t = j * 32 + tt;
+            if (t < T) {
+                float f[8];
+                az_unpack8(__ldg(reinterpret_cast<const uint4*>(vb + (size_t)t * ldv)), f);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) o[e] += pt * f[e];
+            }
+        }
+    }
+    for (int off = chunks; off < 32; off <<= 1)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] += __shfl_xor_sync(0xffffffffu, o[e], off);
+    if (grp == 0) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] *= inv;
+        *reinterpret_cast<uint4*>(oc + (size_t)b * D + h * hd + c * 8) = az_pack8(o);
+    }
+}

@@ -230,6 +230,7 @@ def run_b200(args, wl, rank, world):
         out["profile"] = {k: dict(ms=v[0] / max(v[1], 1), launches=v[1]) for k, v in prof.items() if v[1]}
         out["profile"]["forest_advance"] = dict(ms=sum(a.elapsed_time(b) for a, b in adv) / len(adv), launches=len(adv))
         out["leaves_per_step"] = leaves
+        out["proj_width"] = eng.proj_width()
     out["clocks"] = clocks.summary(t_clock0, t_clock1)
     forest.close()
     eng.close()
@@ -280,9 +281,9 @@ def main():
     if "gemm_kv" in prof:
         G = game_class(wl)
         T = G.rows * G.cols + 1
-        flops = 2.0 * r["leaves_per_step"] * T * NET["dim"] * 2 * NET["dim"]     # [leaves*T, D] x [D, 2D]
+        flops = 2.0 * r["leaves_per_step"] * T * NET["dim"] * r["proj_width"]    # [leaves*T, D] x [D, N]
         ach = flops / (prof["gemm_kv"]["ms"] / 1e3) / 1e12
-        line["roofline"] = dict(kernel="az_gemm_kernel<256,bias> (K/V projection of all tokens, tcgen05)", bound="tensor",
+        line["roofline"] = dict(kernel=f"az_gemm_kernel (all-token projection of the last block, N={r['proj_width']}, tcgen05)", bound="tensor",
                                 achieved=ach, peak=pk["tflops"], unit="TFLOP/s", frac=ach / pk["tflops"], traffic=None,
                                 peak_source=pk["src"], flops_per_launch=flops, ms_per_launch=prof["gemm_kv"]["ms"])
         line["kernel_ms"] = {k: round(v["ms"], 4) for k, v in prof.items()}

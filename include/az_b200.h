@@ -125,6 +125,7 @@ AZ_API int az_net_eval_leaves(az_net* n, az_forest* f, void* stream);
 AZ_API int az_net_forward_planes(az_net* n, const float* planes_host, int B, float* logits_host, float* values_host,
                                  float* priors_host, void* stream);
 AZ_API long long az_net_launch_count(az_net* n);
+AZ_API int az_net_proj_width(az_net* n);   /* N of the all-token projection GEMM of the last block */
 /* MCTS.mcts with the built-in net for every tree of the forest: `iters` simulations per tree,
  * one CUDA graph per step (advance + net), no per-node host work. */
 AZ_API int az_forest_search_net(az_forest* f, az_net* n, int iters, void* stream);
