@@ -1,0 +1,327 @@
+// Fused front end of the depth-1 policy/value net on sm_100a: leaf bitboards in, the cls
+// token's attention output out -- embedding, LayerNorm 1, V / score projection and the
+// cls-query attention of ai/nn.py:9-36,52-56 in ONE kernel, nothing per token leaves the SM.
+//
+// Algebra (exact in real arithmetic; checked in fp64 by tests/test_fold_algebra.py):
+//   token row       x_t  = Wemb^T a_t          a_t in {0,1}^K = [im2col taps | one-hot(t)]
+//   centred         x_t - mean(x_t) 1 = Wc^T a_t,   Wc = Wemb with every K-row centred over D
+//   LayerNorm 1     xn_t = r_t (x_t - mean) (.) gamma + beta,   r_t = rsqrt(a_t^T G a_t / D + eps),
+//                   G = Wc Wc^T  (K x K Gram matrix)
+//   V projection    v_t  = r_t (Wv' Wc^T) a_t + bv'        (gamma/beta folded into Wv', bv')
+//   cls scores      s_t,h = r_t (Ws Wc^T)_h a_t (+ const)  (constant cls query folded into Ws)
+//   attention       o_h = sum_t softmax_t(s_.,h) v_t,h
+// so per token only ONE contraction over K <= 128 binary inputs is needed.  Two tcgen05 MMAs per
+// tile of `nb` boards read the same bit-built operand tile A [tokens][K] (bf16 0/1, exact):
+//   stats : D1[token][j]   = A  x Wst^T   (M = 128 token rows, N = NS: 8 score columns + K Gram columns)
+//   values: D2[feature][t] = Wv2 x A^T    (M = 128 features per block, N = NTP token columns)
+// D1 has tokens on TMEM lanes (the masked Gram sum a^T G a is thread-local); D2 has FEATURES on
+// lanes, so the softmax-weighted sum over a board's tokens is thread-local as well.
+//   warps 0-3  epilogue   warps 4-7  A-tile builders   warp 8  TMA (weights, once) + MMA issue
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include "az_net_kernels.cuh"
+#include "az_ptx.cuh"
+
+struct AzFrontArgs {
+    AzBatch batch;
+    const uint64_t* leaf_words;   // [items][2]: mine, theirs (boards of <= 64 cells)
+    const uint8_t* leaf_player;   // side to move (plane 2 of the 3-plane games)
+    int rows, cols, planes, patch, T, kc, D, H;
+    int nb;                       // boards per tile
+    int TS;                       // token rows per board inside a tile (T rounded up to 8)
+    int NTP;                      // token rows per tile = nb*TS rounded up to 16 (<= 128)
+    int NS;                       // stat columns: 8 + kc + T rounded up to 16 (<= 128)
+    int KB;                       // K blocks of 64 bf16 (1 or 2)
+    int ksteps;                   // K = 16 MMA steps that carry non-zero columns
+    int nslots;                   // TMEM accumulator slots for the value blocks
+    const float* bias_v;          // [D]
+    bf16* oc;                     // [cap][D] (chunk-local rows) attention output of the cls query (before out_proj)
+};
+
+static inline size_t az_front_smem(const AzFrontArgs& a) {
+    const size_t tile = (size_t)a.NTP * 128;
+    return 1024 + 2 * (size_t)a.KB * tile + (size_t)a.KB * a.NS * 128 + (size_t)a.KB * a.D * 128 +
+           2 * 128 * 16 + 8 * 128 * 4 + 128 * 4 + 128 + 256;
+}
+
+namespace azptx {
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr));
+}
+__device__ __forceinline__ void bar_sync_named(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+}  // namespace azptx
+
+template <int TS8>
+__global__ void __launch_bounds__(288, 1) az_front_kernel(const __grid_constant__ CUtensorMap tm_wst,
+                                                          const __grid_constant__ CUtensorMap tm_wv, AzFrontArgs a) {
+    extern __shared__ unsigned char smem_dyn[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
+    const int KB = a.KB, D = a.D, T = a.T, P = a.patch, NTP = a.NTP, NS = a.NS, TS = TS8 * 8;
+    const int FB = D >> 7;                                       // feature blocks of 128
+    const uint32_t tile_bytes = (uint32_t)NTP * 128;
+    unsigned char* s_a = smem;                                   // [2 stages][KB][NTP rows][128 B]
+    unsigned char* s_wst = s_a + 2 * (size_t)KB * tile_bytes;    // [KB][NS rows][128 B]
+    unsigned char* s_wv = s_wst + (size_t)KB * NS * 128;         // [FB][KB][128 rows][128 B]
+    uint4* s_mask = reinterpret_cast<uint4*>(s_wv + (size_t)FB * KB * 16384);   // [2][128] row bit masks (K bits)
+    float* s_w = reinterpret_cast<float*>(s_mask + 2 * 128);     // [8 heads][128 rows] scores, then softmax weight * r
+    float* s_r = s_w + 8 * 128;                                  // [128] LayerNorm rstd per row
+    uint2* s_lut = reinterpret_cast<uint2*>(s_r + 128);          // 16 entries: nibble -> 4 bf16 (0 / 1.0)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_lut + 16);
+    uint64_t* w_full = bars;            // 1
+    uint64_t* a_full = bars + 1;        // 2   (128 builder arrivals)
+    uint64_t* a_empty = bars + 3;       // 2   (MMA commit + epilogue "masks consumed")
+    uint64_t* st_full = bars + 5;       // 1
+    uint64_t* st_empty = bars + 6;      // 1   (128 epilogue arrivals)
+    uint64_t* v_full = bars + 7;        // 4
+    uint64_t* v_empty = bars + 11;      // 4   (128 epilogue arrivals)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int items = az_batch_items(a.batch);
+    const int tiles = (items + a.nb - 1) / a.nb;
+    const int nslots = a.nslots;
+
+    if (threadIdx.x < 16) {
+        const uint32_t n = threadIdx.x;
+        s_lut[n] = make_uint2(((n & 1u) ? 0x00003F80u : 0u) | ((n & 2u) ? 0x3F800000u : 0u),
+                              ((n & 4u) ? 0x00003F80u : 0u) | ((n & 8u) ? 0x3F800000u : 0u));
+    }
+    if (warp == 8 && lane == 0) {
+        azptx::prefetch_tmap(&tm_wst);
+        azptx::prefetch_tmap(&tm_wv);
+        azptx::mbar_init(w_full, 1);
+        for (int i = 0; i < 2; ++i) {
+            azptx::mbar_init(&a_full[i], 128);
+            azptx::mbar_init(&a_empty[i], 2);
+        }
+        azptx::mbar_init(st_full, 1);
+        azptx::mbar_init(st_empty, 128);
+        for (int i = 0; i < 4; ++i) {
+            azptx::mbar_init(&v_full[i], 1);
+            azptx::mbar_init(&v_empty[i], 128);
+        }
+        azptx::fence_barrier_init();
+    }
+    if (warp == 0) azptx::tmem_alloc<512>(tmem_slot);
+    azptx::tc_fence_before();
+    __syncthreads();
+    azptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    // TMEM columns: [0, 128) stats accumulator, value slots of NTP columns from 128 on.
+
+    if (warp == 8) {
+        // ------------------------------ weights in once, then MMA issue -----------------------------
+        if (lane == 0) {
+            azptx::mbar_arrive_expect_tx(w_full, (uint32_t)(KB * NS * 128 + FB * KB * 16384));
+            for (int kb = 0; kb < KB; ++kb) azptx::tma_load_2d(s_wst + (size_t)kb * NS * 128, &tm_wst, w_full, kb * 64, 0);
+            for (int fb = 0; fb < FB; ++fb)
+                for (int kb = 0; kb < KB; ++kb)
+                    azptx::tma_load_2d(s_wv + ((size_t)fb * KB + kb) * 16384, &tm_wv, w_full, kb * 64, fb * 128);
+        }
+        azptx::mbar_wait(w_full, 0);
+        const uint32_t idesc_st = azptx::umma_idesc_bf16(128, (uint32_t)NS);
+        const uint32_t idesc_v = azptx::umma_idesc_bf16(128, (uint32_t)NTP);
+        int it = 0;
+        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+            const int st = it & 1;
+            const unsigned char* at = s_a + (size_t)st * KB * tile_bytes;
+            azptx::mbar_wait(&a_full[st], (it >> 1) & 1);
+            azptx::mbar_wait(st_empty, (it & 1) ^ 1);
+            azptx::tc_fence_after();
+            if (lane == 0) {
+                for (int ks = 0; ks < a.ksteps; ++ks) {
+                    const int kb = ks >> 2, k = ks & 3;
+                    const uint64_t da = azptx::umma_desc_k128(azptx::smem_u32(at + (size_t)kb * tile_bytes));
+                    const uint64_t db = azptx::umma_desc_k128(azptx::smem_u32(s_wst + (size_t)kb * NS * 128));
+                    azptx::umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc_st, ks != 0);
+                }
+                azptx::umma_commit(st_full);
+            }
+            __syncwarp();
+            for (int fb = 0; fb < FB; ++fb) {
+                const int g = it * FB + fb, slot = g % nslots;
+                azptx::mbar_wait(&v_empty[slot], ((g / nslots) & 1) ^ 1);
+                azptx::tc_fence_after();
+                if (lane == 0) {
+                    for (int ks = 0; ks < a.ksteps; ++ks) {
+                        const int kb = ks >> 2, k = ks & 3;
+                        const uint64_t da = azptx::umma_desc_k128(azptx::smem_u32(s_wv + ((size_t)fb * KB + kb) * 16384));
+                        const uint64_t db = azptx::umma_desc_k128(azptx::smem_u32(at + (size_t)kb * tile_bytes));
+                        azptx::umma_bf16(tmem_base + 128 + slot * NTP, da + 2 * k, db + 2 * k, idesc_v, ks != 0);
+                    }
+                    azptx::umma_commit(&v_full[slot]);
+                    if (fb == FB - 1) azptx::umma_commit(&a_empty[st]);   // every MMA reading this A stage is done
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp >= 4) {
+        // ------------------------------ A-tile builders: one thread per token row -------------------
+        const int r = threadIdx.x - 128;
+        const int b_in_tile = r / TS, t = r - b_in_tile * TS;
+        const bool row_used = b_in_tile < a.nb && t < T;
+        int cr = 0, cc = 0;
+        if (row_used && t > 0) { cr = (t - 1) / a.cols; cc = (t - 1) - cr * a.cols; }
+        const int half = P >> 1;
+        const uint32_t colmask = (1u << a.cols) - 1u, pmask = (1u << P) - 1u;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+            const int st = it & 1;
+            azptx::mbar_wait(&a_empty[st], ((it >> 1) & 1) ^ 1);
+            const int item = tile * a.nb + b_in_tile;
+            const bool live = row_used && item < items;
+            unsigned __int128 km = 0;
+            if (live) {
+                if (t > 0) {
+                    const uint64_t w0 = a.leaf_words[(size_t)(a.batch.offset + item) * 2];
+                    const uint64_t w1 = a.leaf_words[(size_t)(a.batch.offset + item) * 2 + 1];
+                    const bool stm = a.planes == 3 && a.leaf_player[a.batch.offset + item] != 0;
+                    for (int kr = 0; kr < P; ++kr) {
+                        const int rr = cr + kr - half;
+                        if (rr < 0 || rr >= a.rows) continue;
+                        const int sh = rr * a.cols;
+                        // window columns cc-half .. cc+half of board row rr, tap kcol at bit kcol
+                        uint32_t b0 = (uint32_t)(w0 >> sh) & colmask, b1 = (uint32_t)(w1 >> sh) & colmask, b2 = colmask;
+                        if (cc >= half) { b0 >>= (cc - half); b1 >>= (cc - half); b2 >>= (cc - half); }
+                        else { b0 <<= (half - cc); b1 <<= (half - cc); b2 <<= (half - cc); }
+                        b0 &= pmask; b1 &= pmask; b2 &= pmask;
+                        km |= (unsigned __int128)b0 << (kr * P);
+                        km |= (unsigned __int128)b1 << (P * P + kr * P);
+                        if (stm) km |= (unsigned __int128)b2 << (2 * P * P + kr * P);
+                    }
+                }
+                km |= (unsigned __int128)1 << (a.kc + t);           // one-hot token index -> pos-emb / bias row
+            }
+            const uint64_t klo = (uint64_t)km, khi = (uint64_t)(km >> 64);
+            if (r < NTP) {
+                unsigned char* arow = s_a + (size_t)st * KB * tile_bytes + (size_t)r * 128;
+                for (int kb = 0; kb < KB; ++kb) {
+                    const uint64_t kw = kb == 0 ? klo : khi;
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        const uint32_t by = (uint32_t)(kw >> (c * 8)) & 0xFFu;
+                        const uint2 lo = s_lut[by & 15u], hi = s_lut[by >> 4];
+                        *reinterpret_cast<uint4*>(arow + (size_t)kb * tile_bytes + ((c ^ (r & 7)) << 4)) = make_uint4(lo.x, lo.y, hi.x, hi.y);
+                    }
+                }
+            }
+            // Gram columns sit behind the 8 score columns: shift the row mask to column numbering
+            const unsigned __int128 ks = km << 8;
+            s_mask[st * 128 + r] = make_uint4((uint32_t)ks, (uint32_t)(ks >> 32), (uint32_t)(ks >> 64), (uint32_t)(ks >> 96));
+            azptx::fence_proxy_async();                              // generic-proxy writes -> visible to the MMA
+            azptx::mbar_arrive(&a_full[st]);
+        }
+    } else {
+        // ------------------------------ epilogue ----------------------------------------------------
+        const int tid = threadIdx.x;                                 // token row (stats) / feature in block (values)
+        const uint32_t tq = tmem_base + ((uint32_t)(warp * 32) << 16);
+        const int H = a.H, hd = D / H;
+        const int pairs = a.nb * H;
+        int tpp = 32;
+        while (tpp * pairs > 128) tpp >>= 1;                         // threads per (board, head) softmax
+        const int pair = tid / tpp, sub = tid - pair * tpp;
+        const float inv_d = 1.0f / (float)D;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+            const int st = it & 1;
+            // ---- per-row LayerNorm statistic and scores from the stats accumulator
+            azptx::mbar_wait(st_full, it & 1);
+            azptx::tc_fence_after();
+            const uint4 mk = s_mask[st * 128 + tid];
+            const uint32_t mw[4] = {mk.x, mk.y, mk.z, mk.w};
+            float q = 0.f, zs[8];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                if (c * 32 < NS) {
+                    uint32_t v[32];
+                    azptx::tmem_ld32(tq + c * 32, v);
+                    azptx::tmem_ld_wait();
+                    if (c == 0) {
+#pragma unroll
+                        for (int h = 0; h < 8; ++h) zs[h] = __uint_as_float(v[h]);
+                    }
+                    const uint32_t m = mw[c];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) q += ((m >> i) & 1u) ? __uint_as_float(v[i]) : 0.f;
+                }
+            }
+            azptx::tc_fence_before();
+            azptx::mbar_arrive(st_empty);
+            const float rstd = rsqrtf(fmaxf(q, 0.f) * inv_d + 1e-5f);
+            s_r[tid] = rstd;
+#pragma unroll
+            for (int h = 0; h < 8; ++h) s_w[h * 128 + tid] = zs[h] * rstd;
+            azptx::bar_sync_named(1, 128);
+            if (tid == 0) azptx::mbar_arrive(&a_empty[st]);          // row masks of this stage consumed
+            // ---- softmax over the T tokens of each (board, head); weight = p * rstd
+            {
+                const bool on = pair < pairs;
+                const int b = on ? pair / H : 0, h = on ? pair - b * H : 0;
+                float* sw = s_w + h * 128 + b * TS;
+                const float* sr = s_r + b * TS;
+                float mx = -1e30f;
+                for (int t = sub; t < T; t += tpp) mx = fmaxf(mx, sw[t]);
+                for (int o = tpp >> 1; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                float sum = 0.f;
+                for (int t = sub; t < T; t += tpp) sum += __expf(sw[t] - mx);
+                for (int o = tpp >> 1; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                const float inv = 1.0f / sum;
+                if (on)
+                    for (int t = sub; t < TS; t += tpp) sw[t] = t < T ? __expf(sw[t] - mx) * inv * sr[t] : 0.f;
+            }
+            azptx::bar_sync_named(1, 128);
+            // ---- value blocks: o[f] = sum_t w[h(f)][t] * z[f][t] + bias, features on TMEM lanes
+            for (int fb = 0; fb < FB; ++fb) {
+                const int g = it * FB + fb, slot = g % nslots;
+                azptx::mbar_wait(&v_full[slot], (g / nslots) & 1);
+                azptx::tc_fence_after();
+                const int f = fb * 128 + tid;
+                const float* wrow = s_w + (f / hd) * 128;
+                const float bias = __ldg(a.bias_v + f);
+                const uint32_t tcol = tq + 128 + slot * NTP;
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};                 // <= 4 boards at a time in registers
+                for (int b0 = 0; b0 < a.nb; b0 += 4) {
+#pragma unroll
+                    for (int bi = 0; bi < 4; ++bi) {
+                        const int b = b0 + bi;
+                        acc[bi] = 0.f;
+                        if (b < a.nb) {
+                            uint32_t v[TS8][8];
+#pragma unroll
+                            for (int j = 0; j < TS8; ++j) azptx::tmem_ld8(tcol + b * TS + j * 8, v[j]);
+                            azptx::tmem_ld_wait();
+#pragma unroll
+                            for (int j = 0; j < TS8; ++j) {
+                                const float4 w0 = *reinterpret_cast<const float4*>(wrow + b * TS + j * 8);
+                                const float4 w1 = *reinterpret_cast<const float4*>(wrow + b * TS + j * 8 + 4);
+                                acc[bi] += w0.x * __uint_as_float(v[j][0]) + w0.y * __uint_as_float(v[j][1]) +
+                                           w0.z * __uint_as_float(v[j][2]) + w0.w * __uint_as_float(v[j][3]) +
+                                           w1.x * __uint_as_float(v[j][4]) + w1.y * __uint_as_float(v[j][5]) +
+                                           w1.z * __uint_as_float(v[j][6]) + w1.w * __uint_as_float(v[j][7]);
+                            }
+                        }
+                    }
+                    if (b0 + 4 >= a.nb) {                            // slot fully read: hand it back before the stores
+                        azptx::tc_fence_before();
+                        azptx::mbar_arrive(&v_empty[slot]);
+                    }
+#pragma unroll
+                    for (int bi = 0; bi < 4; ++bi) {
+                        const int item = tile * a.nb + b0 + bi;
+                        if (b0 + bi < a.nb && item < items)
+                            a.oc[(size_t)item * D + f] = __float2bfloat16(acc[bi] + bias);
+                    }
+                }
+            }
+            azptx::bar_sync_named(1, 128);                           // s_w / s_r are rewritten by the next tile
+        }
+    }
+    azptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) azptx::tmem_dealloc<512>(tmem_base);
+}

@@ -129,6 +129,7 @@ extern "C" int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const
 // ======================================================================================
 #include "az_net_kernels.cuh"
 #include "az_embed_mma.cuh"
+#include "az_front.cuh"
 
 struct AzBlockW {
     float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
@@ -140,6 +141,7 @@ struct AzBlockW {
 struct az_net {
     int rows = 0, cols = 0, C = 0, patch = 0, D = 0, H = 0, L = 0, A = 0, T = 0;
     int chunk = 0;                       // boards per pass through the activation buffers
+    int max_batch = 0;
     bool finalized = false;
     std::vector<void*> allocs;
     std::map<std::string, std::vector<float>> host;   // raw fp32 parameters until finalize
@@ -157,6 +159,14 @@ struct az_net {
     bf16* w_vs = nullptr;
     float *b_vs = nullptr, *sc = nullptr;
     CUtensorMap tm_vs;
+    // depth-1 nets on boards of <= 63 cells: embedding .. cls attention in one kernel (az_front.cuh)
+    bool front = false;
+    std::vector<double> host_wemb;       // [kpad][D] rows: conv taps, then pos-emb + bias rows (fp64 copy for the folds)
+    int host_wemb_kpad = 0;
+    bf16 *f_wst = nullptr, *f_wv = nullptr;
+    float *f_bias_v = nullptr, *b_out_x0 = nullptr;
+    CUtensorMap tm_fwst, tm_fwv;
+    AzFrontArgs fa{};
     std::vector<AzBlockW> blk;
     float *lnf_g = nullptr, *lnf_b = nullptr, *w_pol = nullptr, *b_pol = nullptr, *w_val = nullptr, *b_val = nullptr;
     // activations (one chunk)
@@ -177,9 +187,9 @@ struct az_net {
     double prof_units[16] = {0};         // flops (GEMMs) or bytes (others) of the profiled launches
 };
 
-enum { AZ_K_EMBED = 0, AZ_K_GEMM_KV, AZ_K_GEMM_CLS, AZ_K_CLS_ATT, AZ_K_LN, AZ_K_HEAD, AZ_K_GEMM_FULL, AZ_K_ATT_FULL, AZ_K_COUNT };
+enum { AZ_K_EMBED = 0, AZ_K_GEMM_KV, AZ_K_GEMM_CLS, AZ_K_CLS_ATT, AZ_K_LN, AZ_K_HEAD, AZ_K_GEMM_FULL, AZ_K_ATT_FULL, AZ_K_FRONT, AZ_K_COUNT };
 static const char* const AZ_K_NAMES[AZ_K_COUNT] = {"embed_ln", "gemm_kv", "gemm_cls_rows", "cls_attention", "layernorm",
-                                                   "head_softmax", "gemm_full_block", "attention_full"};
+                                                   "head_softmax", "gemm_full_block", "attention_full", "front_fused"};
 
 struct AzProfScope {
     az_net* n; cudaStream_t s; int idx = -1;
@@ -235,6 +245,7 @@ extern "C" int az_net_create(int rows, int cols, int planes, int patch, int embe
     az_net* n = new az_net();
     n->rows = rows; n->cols = cols; n->C = planes; n->patch = patch; n->D = embed_dim; n->H = num_heads;
     n->L = depth; n->A = action_dim; n->T = rows * cols + 1;
+    n->max_batch = max_batch;
     n->chunk = max_batch < 4096 ? max_batch : 4096;
     n->blk.resize(depth);
     *out = n;
@@ -313,6 +324,18 @@ extern "C" int az_net_finalize(az_net* n) {
         const int kc = C * P * P;
         n->emb_kc = kc;
         n->emb_kblocks = 0;
+        n->host_wemb.clear();
+        n->host_wemb_kpad = 0;
+        if (kc + T <= 128) {
+            const int kpad = (kc + T + 63) / 64 * 64;
+            n->host_wemb.assign((size_t)kpad * D, 0.0);
+            for (int d = 0; d < D; ++d) {
+                for (int k = 0; k < kc; ++k) n->host_wemb[(size_t)k * D + d] = (*cw)[(size_t)d * kc + k];
+                for (int t = 0; t < T; ++t)
+                    n->host_wemb[(size_t)(kc + t) * D + d] = (double)(*pos)[(size_t)t * D + d] + (t == 0 ? (*cls)[d] : (*cb)[d]);
+            }
+            n->host_wemb_kpad = kpad;
+        }
         const bool d_ok = (D <= 256 && D % 16 == 0) || D == 512;
         if (kc + T <= 128 && d_ok && !getenv("AZ_EMBED_SIMT")) {
             const int kb = (kc + T + 63) / 64, kpad = kb * 64;
@@ -415,6 +438,91 @@ extern "C" int az_net_finalize(az_net* n) {
             n->folded = true;
         }
     }
+    // ---- depth 1, small boards: fold the embedding into the projection as well (az_front.cuh)
+    n->front = false;
+    {
+        const int H = n->H, kc = n->emb_kc, kused = kc + T;
+        if (n->folded && n->host_wemb_kpad && cells <= 63 && H <= 8 && kused + 8 <= 128 && D % 128 == 0 && D <= 512 &&
+            !getenv("AZ_NO_FRONT")) {
+            const int kpad = n->host_wemb_kpad, KB = kpad / 64;
+            const std::vector<float>& wi = n->host_folded_w_in;
+            const std::vector<float>& bi = n->host_folded_b_in;
+            // Wc: every K-row of Wemb centred over D
+            std::vector<double> wc(n->host_wemb);
+            for (int k = 0; k < kused; ++k) {
+                double m = 0;
+                for (int d = 0; d < D; ++d) m += wc[(size_t)k * D + d];
+                m /= D;
+                for (int d = 0; d < D; ++d) wc[(size_t)k * D + d] -= m;
+            }
+            // the cls query (a constant of the model) and the folded score rows Ws [H][D], fp64
+            std::vector<double> x0(D), q(D), ws((size_t)H * D, 0.0);
+            {
+                double mean = 0, var = 0;
+                for (int d = 0; d < D; ++d) { x0[d] = n->host_wemb[(size_t)kc * D + d]; mean += x0[d]; }
+                mean /= D;
+                for (int d = 0; d < D; ++d) var += (x0[d] - mean) * (x0[d] - mean);
+                const double rstd = 1.0 / sqrt(var / D + 1e-5);
+                for (int r = 0; r < D; ++r) {
+                    double acc = bi[r];
+                    for (int k = 0; k < D; ++k) acc += (double)wi[(size_t)r * D + k] * ((x0[k] - mean) * rstd);
+                    q[r] = acc;
+                }
+                const int hd = D / H;
+                const double scale = 1.0 / sqrt((double)hd);
+                for (int h = 0; h < H; ++h)
+                    for (int d = 0; d < hd; ++d) {
+                        const double qq = q[h * hd + d] * scale;
+                        const float* wk = &wi[(size_t)(D + h * hd + d) * D];
+                        for (int k = 0; k < D; ++k) ws[(size_t)h * D + k] += qq * wk[k];
+                    }
+            }
+            const int NS = (8 + kused + 15) / 16 * 16;
+            std::vector<float> wst((size_t)NS * kpad, 0.f), wv2((size_t)D * kpad, 0.f), bv(D), box(D);
+            for (int h = 0; h < H; ++h)                                  // rows 0..7: scores
+                for (int k = 0; k < kused; ++k) {
+                    double acc = 0;
+                    for (int d = 0; d < D; ++d) acc += ws[(size_t)h * D + d] * wc[(size_t)k * D + d];
+                    wst[(size_t)h * kpad + k] = (float)acc;
+                }
+            for (int i = 0; i < kused; ++i)                              // rows 8..: Gram matrix of the centred rows
+                for (int k = 0; k <= i; ++k) {
+                    double acc = 0;
+                    for (int d = 0; d < D; ++d) acc += wc[(size_t)i * D + d] * wc[(size_t)k * D + d];
+                    wst[(size_t)(8 + i) * kpad + k] = (float)acc;
+                    wst[(size_t)(8 + k) * kpad + i] = (float)acc;
+                }
+            for (int f = 0; f < D; ++f) {                                // V rows with the embedding folded in
+                const float* wr = &wi[(size_t)(2 * D + f) * D];
+                for (int k = 0; k < kused; ++k) {
+                    double acc = 0;
+                    for (int d = 0; d < D; ++d) acc += (double)wr[d] * wc[(size_t)k * D + d];
+                    wv2[(size_t)f * kpad + k] = (float)acc;
+                }
+                bv[f] = bi[2 * D + f];
+            }
+            const std::vector<float>* bo = az_param(n, "blocks.0.attn.out_proj.bias", (size_t)D, &err);
+            if (!bo) return az_fail(AZ_EINVAL, "az_net_finalize: " + err);
+            for (int d = 0; d < D; ++d) box[d] = (*bo)[d] + (float)x0[d];   // residual of the cls row is a constant
+            if ((rc = az_upload_bf16(n, &n->f_wst, wst.data(), wst.size())) || (rc = az_upload_bf16(n, &n->f_wv, wv2.data(), wv2.size())) ||
+                (rc = az_upload_f32(n, &n->f_bias_v, bv)) || (rc = az_upload_f32(n, &n->b_out_x0, box)))
+                return rc;
+            if ((rc = az_make_tmap(&n->tm_fwst, n->f_wst, NS, kpad, kpad, NS)) || (rc = az_make_tmap(&n->tm_fwv, n->f_wv, D, kpad, kpad, 128)))
+                return rc;
+            AzFrontArgs& fa = n->fa;
+            fa = AzFrontArgs{};
+            fa.rows = n->rows; fa.cols = n->cols; fa.planes = C; fa.patch = P; fa.T = T; fa.kc = kc; fa.D = D; fa.H = H;
+            fa.TS = (T + 7) / 8 * 8;
+            fa.nb = std::min(128 / fa.TS, 128 / H);
+            fa.NTP = (fa.nb * fa.TS + 15) / 16 * 16;
+            fa.NS = NS;
+            fa.KB = KB;
+            fa.ksteps = (kused + 15) / 16;
+            fa.nslots = std::min(std::min(4, D / 128), 384 / fa.NTP);
+            fa.bias_v = n->f_bias_v;
+            n->front = fa.nb >= 1 && fa.nslots >= 1 && az_front_smem(fa) <= 227 * 1024;
+        }
+    }
     // ---- heads
     AZ_P(gf, "norm.weight", (size_t)D) AZ_P(bf, "norm.bias", (size_t)D)
     AZ_P(wp, "policy_head.weight", (size_t)A * D) AZ_P(bp, "policy_head.bias", (size_t)A)
@@ -425,7 +533,9 @@ extern "C" int az_net_finalize(az_net* n) {
         (rc = az_upload_f32(n, &n->w_val, *wv)) || (rc = az_upload_f32(n, &n->b_val, *bv)))
         return rc;
     // ---- activations for one chunk of boards
-    const size_t B = (size_t)n->chunk, M = B * T;
+    // the fused front end keeps every per-token quantity on chip: only per-board rows remain
+    n->chunk = n->front ? std::min(n->max_batch, 65536) : std::min(n->max_batch, 4096);
+    const size_t B = (size_t)n->chunk, M = n->front ? 128 : B * T;
     const bool deep = n->L > 1;
     if ((rc = az_net_alloc(n, &n->x, M * D)) || (rc = az_net_alloc(n, &n->xn, M * D)) ||
         (rc = az_net_alloc(n, &n->qkv, M * (deep ? 3 : 2) * D)) ||
@@ -443,7 +553,7 @@ extern "C" int az_net_finalize(az_net* n) {
     AZ_CUDA_OK(cudaMemset(n->x, 0, M * D * 2));
     AZ_CUDA_OK(cudaMemset(n->xn, 0, M * D * 2));
     if ((rc = az_make_tmap(&n->tm_xn, n->xn, M, D, D, 128)) ||
-        (rc = az_make_tmap(&n->tm_xn_cls, n->xn, B, D, (uint64_t)T * D, 128)) ||
+        (rc = az_make_tmap(&n->tm_xn_cls, n->xn, n->front ? 1 : B, D, (uint64_t)T * D, 128)) ||
         (rc = az_make_tmap(&n->tm_oc, n->oc, B, D, D, 128)) || (rc = az_make_tmap(&n->tm_xcn, n->xcn, B, D, D, 128)) ||
         (rc = az_make_tmap(&n->tm_hc, n->hc, B, 4 * D, 4 * D, 128)))
         return rc;
@@ -482,6 +592,71 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
     const int cap = batch.cap;                               // grid bound (items)
     const long long max_rows = (long long)cap * T;
     int rc;
+    auto layernorm = [&](int rows_per_item, const bf16* in, int ld_in, bf16* out, int ld_out, const float* g, const float* b) {
+        AzProfScope ps(n, AZ_K_LN, s);
+        const long long rows = (long long)cap * rows_per_item;
+        const int grid = (int)((rows + 7) / 8);
+        az_ln_dispatch(D, [&](auto nv) {
+            az_layernorm_kernel<decltype(nv)::value><<<grid, 256, 0, s>>>(batch, rows_per_item, in, ld_in, out, ld_out, D, g, b);
+        });
+        ++n->launches;
+    };
+    auto gemm = [&](int kind, const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& ga, int epi, int mr) {
+        AzProfScope ps(n, kind, s);
+        return az_launch_gemm(ta, tb, ga, epi, mr, s);
+    };
+    auto heads = [&](const bf16* xc_final) -> int {
+        AzHeadArgs ha{};
+        ha.batch = batch; ha.xc = xc_final; ha.D = D; ha.A = A; ha.ln_g = n->lnf_g; ha.ln_b = n->lnf_b;
+        ha.w_pol = n->w_pol; ha.b_pol = n->b_pol; ha.w_val = n->w_val; ha.b_val = n->b_val;
+        ha.priors = priors; ha.values = values; ha.logits = logits;
+        {
+            AzProfScope ps(n, AZ_K_HEAD, s);
+            az_head_kernel<<<cap, 128, (size_t)(D + A + 8) * sizeof(float), s>>>(ha);
+        }
+        AZ_CUDA_OK(cudaGetLastError());
+        ++n->launches;
+        return AZ_OK;
+    };
+    if (!g_num_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    if (n->front) {
+        // embedding + LN1 + V/score projection + cls attention, all on chip (az_front.cuh)
+        AzBlockW& w = n->blk[0];
+        AzFrontArgs fa = n->fa;
+        fa.batch = batch; fa.leaf_words = words; fa.leaf_player = players; fa.oc = n->oc;
+        const size_t smem = az_front_smem(fa);
+        const int tiles = (cap + fa.nb - 1) / fa.nb;
+        const int grid = tiles < g_num_sms ? (tiles > 0 ? tiles : 1) : g_num_sms;
+        {
+            AzProfScope ps(n, AZ_K_FRONT, s);
+#define AZ_FRONT(TS8_)                                                                                                     \
+    case TS8_: {                                                                                                           \
+        static bool done = false;                                                                                          \
+        if (!done) {                                                                                                       \
+            AZ_CUDA_OK(cudaFuncSetAttribute(az_front_kernel<TS8_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
+            done = true;                                                                                                   \
+        }                                                                                                                  \
+        az_front_kernel<TS8_><<<grid, 288, smem, s>>>(n->tm_fwst, n->tm_fwv, fa);                                          \
+    } break;
+            switch (fa.TS / 8) {
+                AZ_FRONT(1) AZ_FRONT(2) AZ_FRONT(3) AZ_FRONT(4) AZ_FRONT(5) AZ_FRONT(6) AZ_FRONT(7) AZ_FRONT(8)
+                default: return az_fail(AZ_ESTATE, "front kernel: unsupported token stride");
+            }
+#undef AZ_FRONT
+        }
+        AZ_CUDA_OK(cudaGetLastError());
+        ++n->launches;
+        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out, az_gargs(batch, 1, n->b_out_x0, nullptr, 0, n->xc, D, D, D), AZ_EPI_BIAS, cap))) return rc;
+        layernorm(1, n->xc, D, n->xcn, D, w.ln2_g, w.ln2_b);
+        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_xcn, w.tm_w1, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap))) return rc;
+        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap))) return rc;
+        n->launches += 3;
+        return heads(n->xc2);
+    }
     // 1. boards -> tokens -> LN1 of block 0 (affine folded into block 0's in_proj at load time)
     if (n->emb_kblocks) {
         AzProfScope ps(n, AZ_K_EMBED, s);
@@ -490,11 +665,6 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         ma.rows = n->rows; ma.cols = n->cols; ma.planes = n->C; ma.patch = n->patch; ma.D = D; ma.T = T;
         ma.kc = n->emb_kc; ma.kblocks = n->emb_kblocks; ma.x = n->x; ma.xn = n->xn; ma.write_all_x = L > 1;
         const size_t smem = az_embed_mma_smem(D, n->emb_kblocks, T, n->patch * n->patch);
-        if (!g_num_sms) {
-            int dev = 0;
-            cudaGetDevice(&dev);
-            cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-        }
         const int tiles = (int)((max_rows + 127) / 128);
         const int grid = tiles < g_num_sms ? (tiles > 0 ? tiles : 1) : g_num_sms;
 #define AZ_EMB(COLS)                                                                                                  \
@@ -522,19 +692,6 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         AZ_CUDA_OK(cudaGetLastError());
         ++n->launches;
     }
-    auto layernorm = [&](int rows_per_item, const bf16* in, int ld_in, bf16* out, int ld_out, const float* g, const float* b) {
-        AzProfScope ps(n, AZ_K_LN, s);
-        const long long rows = (long long)cap * rows_per_item;
-        const int grid = (int)((rows + 7) / 8);
-        az_ln_dispatch(D, [&](auto nv) {
-            az_layernorm_kernel<decltype(nv)::value><<<grid, 256, 0, s>>>(batch, rows_per_item, in, ld_in, out, ld_out, D, g, b);
-        });
-        ++n->launches;
-    };
-    auto gemm = [&](int kind, const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& ga, int epi, int mr) {
-        AzProfScope ps(n, kind, s);
-        return az_launch_gemm(ta, tb, ga, epi, mr, s);
-    };
     for (int l = 0; l < L - 1; ++l) {                        // full blocks (ai/nn.py:52-61)
         AzBlockW& w = n->blk[l];
         if (l > 0) layernorm(T, n->x, D, n->xn, D, w.ln1_g, w.ln1_b);
@@ -584,17 +741,7 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap))) return rc;
         n->launches += 6;
     }
-    AzHeadArgs ha{};
-    ha.batch = batch; ha.xc = n->xc2; ha.D = D; ha.A = A; ha.ln_g = n->lnf_g; ha.ln_b = n->lnf_b;
-    ha.w_pol = n->w_pol; ha.b_pol = n->b_pol; ha.w_val = n->w_val; ha.b_val = n->b_val;
-    ha.priors = priors; ha.values = values; ha.logits = logits;
-    {
-        AzProfScope ps(n, AZ_K_HEAD, s);
-        az_head_kernel<<<cap, 128, (size_t)(D + A + 8) * sizeof(float), s>>>(ha);
-    }
-    AZ_CUDA_OK(cudaGetLastError());
-    ++n->launches;
-    return AZ_OK;
+    return heads(n->xc2);
 }
 
 // Evaluate the forest's pending leaves (the `model(...)` call of ai/mcts.py:46 for the whole

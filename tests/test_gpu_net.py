@@ -60,6 +60,8 @@ def test_net_matches_reference_goldens():
     (7, 7, 2, 49, 512, 1, 5, 9000),       # Gomoku, main.py:134
     (7, 7, 2, 49, 256, 2, 5, 1500),       # main.py:187-188 (depth 2: full block + pruned block)
     (3, 3, 3, 9, 64, 1, 3, 700),          # TicTacToe small net
+    (3, 3, 3, 9, 128, 1, 3, 700),         # TicTacToe on the fused front end (8 boards per tile)
+    (6, 7, 3, 7, 256, 1, 5, 1111),        # Connect4, two feature blocks, ragged last tile
     (15, 15, 2, 225, 128, 2, 3, 300),     # 15x15: T = 226 tokens
 ])
 def test_net_matches_torch_fp32(rows, cols, C, A, dim, depth, patch, B):
