@@ -132,6 +132,10 @@ class B200Net:
     def profile(self, enable=True):
         _lib.check(self._L.az_net_profile(self.h, int(enable)), "az_net_profile")
 
+    def profile_on(self, on):
+        """Pause / resume the timing without clearing the totals."""
+        _lib.check(self._L.az_net_profile(self.h, 2 if on else 3), "az_net_profile")
+
     def profile_read(self):
         """{kernel kind: (total ms, launches)} of the eager passes since profile(True)."""
         names = (C.c_char_p * 16)()

@@ -26,11 +26,25 @@ __device__ __forceinline__ unsigned az_group_mask() {
 
 // fp32 PUCT of the reference under NumPy >= 2 promotion:
 //   s = (float)sqrt((double)Np); t = P*s; u = t/(float)(n+1); q = (float)(W/n); ucb = q+u
-__device__ __forceinline__ float az_puct32(double W, float P, int n, float s) {
+// q is cached in the node by the backup that last changed W and n (az_backup_node); s is formed with
+// the fp32 square root, which equals the rounded f64 root for every Np < 2^24 (53 >= 2*24+2 bits;
+// checked exhaustively in tests/test_oracle_golden.py).
+__device__ __forceinline__ float az_puct32(float q, float P, int n, float s) {
     const float u = __fdiv_rn(__fmul_rn(P, s), (float)(n + 1));
     if (n == 0) return u;                                     // utils.py:32-35
-    const float q = __double2float_rn(__ddiv_rn(W, (double)n));
     return __fadd_rn(q, u);                                   // utils.py:40
+}
+__device__ __forceinline__ float az_q32(double W, int n) { return __double2float_rn(__ddiv_rn(W, (double)n)); }
+
+// node.py:69-72 for one node of the path: visit += 1; value += v; (+ refresh the cached quotient)
+__device__ __forceinline__ void az_backup_node(AzHot* hot, double* wsum, uint32_t nd, double v, bool release_vl) {
+    AzHot h = hot[nd];
+    const double W = __dadd_rn(wsum[nd], v);
+    h.N += 1;
+    h.Q = az_q32(W, h.N);
+    if (release_vl) h.V -= 1;
+    hot[nd] = h;
+    wsum[nd] = W;
 }
 
 // f64 variant: root children when Dirichlet noise made their priors np.float64.
@@ -53,6 +67,10 @@ __device__ __forceinline__ void az_group_argmax(unsigned gmask, T& best, int& id
     }
 }
 
+// Expansion of up to AZ_LP pending leaves of a tree runs in parallel (one lane per leaf generates
+// that leaf's legal moves -- for Gomoku the sequential CPython-set emulation -- into its own scratch).
+#define AZ_LP 8
+
 template <int NW, int G>
 __global__ void __launch_bounds__(128) az_advance_kernel(AzForestDev f, int smem_per_group) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -61,153 +79,190 @@ __global__ void __launch_bounds__(128) az_advance_kernel(AzForestDev f, int smem
     const int tree = blockIdx.x * (blockDim.x / G) + grp;
     const unsigned gmask = az_group_mask<G>();
     if (tree >= f.n_trees) return;
-    if (!f.active[tree] || f.done_flag[tree]) return;
-
-    const AzGame& g = f.g;
-    unsigned char* sm = smem_raw + (size_t)grp * smem_per_group;
-    uint32_t* s_path = reinterpret_cast<uint32_t*>(sm);
-    uint8_t* s_moves = sm + 4 * f.max_depth;
-    uint8_t* s_tab_a = s_moves + ((g.max_children + 15) & ~15);
-    uint8_t* s_tab_b = s_tab_a + g.set_slots;
-
-    AzHot* hot = f.hot + (size_t)tree * f.cap;
-    AzMeta* meta = f.meta + (size_t)tree * f.cap;
-    uint8_t* vlc = f.vlc + (size_t)tree * f.cap;
-    const bool use_vl = f.vl > 1;
-    const int A = g.action_dim;
-
-    unsigned st_sims = 0, st_term = 0, st_exp = 0, st_child = 0, st_sel = 0, st_reads = 0, st_coll = 0;
+    // independent loads first, decisions after: one memory round trip
+    const uint8_t is_active = f.active[tree], is_done = f.done_flag[tree];
     int n_nodes = f.n_nodes[tree];
     int sims = f.sims_done[tree];
-
-    // ---------------- phase A: expand + backup the evaluated leaves -----------------------
     const int npend = f.n_pending[tree];
-    for (int j = 0; j < npend; ++j) {
-        const size_t pj = (size_t)tree * f.vl + j;
-        const int slot = f.leaf_slot[pj];
-        const int len = f.path_len[pj];
-        const uint32_t* gpath = f.path + pj * f.max_depth;
-        const uint32_t leaf = gpath[len - 1];
-        AzBoard<NW> b;
-#pragma unroll
-        for (int w = 0; w < NW; ++w) {
-            b.w[0][w] = f.pend_words[pj * 2 * NW + w];
-            b.w[1][w] = f.pend_words[pj * 2 * NW + NW + w];
-        }
-        int nc = 0;
-        if (lane == 0) nc = az_legal_moves<NW>(g, b, f.cell_hash, s_tab_a, s_tab_b, s_moves);
-        nc = __shfl_sync(gmask, nc, 0, G);
-        __syncwarp(gmask);                                    // s_moves visible to the group
-        const uint32_t base = (uint32_t)n_nodes;
-        n_nodes += nc;
-        const float* pri = f.priors + (size_t)slot * A;
-        const bool noisy_root = (leaf == 0) && f.use_noise;
-        for (int c = lane; c < nc; c += G) {
-            const int cell = s_moves[c];
-            const int ai = az_action_index(g, cell);
-            float p = pri[ai];                               // node.py:57 gather, unmasked softmax
-            if (noisy_root) {                                // utils.py:24: f32*0.75 + f64 noise*0.25
-                const double p64 = __dadd_rn((double)__fmul_rn(0.75f, p),
-                                             __dmul_rn(0.25, f.root_noise[(size_t)tree * A + ai]));
-                f.root_prior64[(size_t)tree * g.max_children + c] = p64;
-                p = __double2float_rn(p64);                  // kept for reporting only
-            }
-            AzHot h;
-            h.W = 0.0;
-            h.P = p;
-            h.N = 0;
-            hot[base + c] = h;
-            AzMeta m;
-            m.child_base = 0;
-            m.action = (uint16_t)cell;
-            m.nchild = 0;
-            m.status = AZ_ST_LEAF;
-            meta[base + c] = m;
-            if (use_vl) vlc[base + c] = 0;
-        }
-        if (lane == 0) {
-            AzMeta m = meta[leaf];
-            m.child_base = base;
-            m.nchild = (uint8_t)nc;
-            m.status = AZ_ST_EXPANDED;
-            meta[leaf] = m;
-        }
-        const double result = -(double)f.values[slot];        // mcts.py:56
-        for (int i = lane; i < len; i += G) {                 // node.py:69-72
-            const uint32_t nd = gpath[i];
-            AzHot h = hot[nd];
-            h.N += 1;
-            h.W = __dadd_rn(h.W, ((len - 1 - i) & 1) ? -result : result);
-            hot[nd] = h;
-            if (use_vl) vlc[nd] -= 1;
-        }
-        __syncwarp(gmask);
-        ++st_exp;
-        st_child += nc;
-        ++st_sims;
-        ++sims;
-    }
-
-    // ---------------- phase B: descend until `vl` leaves are pending -----------------------
+    const int root_player = f.root_player[tree];
+    const int root_mc = f.root_mc[tree];
     AzBoard<NW> rootb;
 #pragma unroll
     for (int w = 0; w < NW; ++w) {
         rootb.w[0][w] = f.root_words[(size_t)tree * 2 * NW + w];
         rootb.w[1][w] = f.root_words[(size_t)tree * 2 * NW + NW + w];
     }
-    const int root_player = f.root_player[tree];
-    const int root_mc = f.root_mc[tree];
+    if (!is_active || is_done) return;
+
+    const AzGame& g = f.g;
+    unsigned char* sm = smem_raw + (size_t)grp * smem_per_group;
+    uint32_t* s_path = reinterpret_cast<uint32_t*>(sm);
+    const int moves_pad = (g.max_children + 15) & ~15;
+    const int lm_bytes = moves_pad + 2 * g.set_slots;           // legal-move scratch of one pending leaf
+    uint8_t* s_lm = sm + 4 * f.max_depth;
+
+    AzHot* hot = f.hot + (size_t)tree * f.cap;
+    AzMeta* meta = f.meta + (size_t)tree * f.cap;
+    const unsigned long long* meta64 = reinterpret_cast<const unsigned long long*>(meta);
+    double* wsum = f.wsum + (size_t)tree * f.cap;
+    const bool use_vl = f.vl > 1;
+    const int A = g.action_dim;
+    const int LP = f.lp;
+
+    unsigned st_sims = 0, st_term = 0, st_exp = 0, st_child = 0, st_sel = 0, st_reads = 0, st_coll = 0;
+
+    // ---------------- phase A: expand + backup the evaluated leaves -----------------------
+    for (int j0 = 0; j0 < npend; j0 += LP) {
+        const int nj = min(LP, npend - j0);
+        int my_nc = 0, my_slot = 0, my_len = 0, my_action = 0;
+        uint32_t my_leaf = 0;
+        float my_val = 0.f;
+        if (lane < nj) {                                      // lane j: scalars + legal moves of leaf j0 + j
+            const size_t pj = (size_t)tree * f.vl + j0 + lane;
+            AzBoard<NW> b;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                b.w[0][w] = f.pend_words[pj * 2 * NW + w];
+                b.w[1][w] = f.pend_words[pj * 2 * NW + NW + w];
+            }
+            my_slot = f.leaf_slot[pj];
+            my_len = f.path_len[pj];
+            my_action = f.pend_action[pj];
+            my_val = f.values[my_slot];
+            my_leaf = f.path[pj * f.max_depth + my_len - 1];
+            uint8_t* lm = s_lm + (size_t)lane * lm_bytes;
+            my_nc = az_legal_moves<NW>(g, b, f.cell_hash, lm + moves_pad, lm + moves_pad + g.set_slots, lm);
+        }
+        __syncwarp(gmask);                                    // move lists visible to the group
+        for (int j = 0; j < nj; ++j) {                        // in selection order: node numbering and f64 sums depend on it
+            const size_t pj = (size_t)tree * f.vl + j0 + j;
+            const int nc = __shfl_sync(gmask, my_nc, j, G);
+            const int slot = __shfl_sync(gmask, my_slot, j, G);
+            const int len = __shfl_sync(gmask, my_len, j, G);
+            const int action = __shfl_sync(gmask, my_action, j, G);
+            const uint32_t leaf = __shfl_sync(gmask, my_leaf, j, G);
+            const float val = __shfl_sync(gmask, my_val, j, G);
+            const uint8_t* s_moves = s_lm + (size_t)j * lm_bytes;
+            const uint32_t* gpath = f.path + pj * f.max_depth;
+            const uint32_t base = (uint32_t)n_nodes;
+            n_nodes += nc;
+            const float* pri = f.priors + (size_t)slot * A;
+            const bool noisy_root = (leaf == 0) && f.use_noise;
+            for (int c = lane; c < nc; c += G) {
+                const int cell = s_moves[c];
+                const int ai = az_action_index(g, cell);
+                float p = pri[ai];                               // node.py:57 gather, unmasked softmax
+                if (noisy_root) {                                // utils.py:24: f32*0.75 + f64 noise*0.25
+                    const double p64 = __dadd_rn((double)__fmul_rn(0.75f, p),
+                                                 __dmul_rn(0.25, f.root_noise[(size_t)tree * A + ai]));
+                    f.root_prior64[(size_t)tree * g.max_children + c] = p64;
+                    p = __double2float_rn(p64);                  // kept for reporting only
+                }
+                AzHot h;
+                h.N = 0;
+                h.Q = 0.f;
+                h.P = p;
+                h.V = 0;
+                hot[base + c] = h;
+                wsum[base + c] = 0.0;
+                AzMeta m;
+                m.child_base = 0;
+                m.action = (uint16_t)cell;
+                m.nchild = 0;
+                m.status = AZ_ST_LEAF;
+                meta[base + c] = m;
+            }
+            if (lane == 0) {
+                AzMeta m;
+                m.child_base = base;
+                m.action = (uint16_t)action;
+                m.nchild = (uint8_t)nc;
+                m.status = AZ_ST_EXPANDED;
+                meta[leaf] = m;
+            }
+            const double result = -(double)val;                   // mcts.py:56
+            for (int i = lane; i < len; i += G)                   // node.py:69-72
+                az_backup_node(hot, wsum, gpath[i], ((len - 1 - i) & 1) ? -result : result, use_vl);
+            __syncwarp(gmask);
+            ++st_exp;
+            st_child += nc;
+            ++st_sims;
+            ++sims;
+        }
+    }
+
+    // ---------------- phase B: descend until `vl` leaves are pending -----------------------
     int started = sims;
     int np = 0;
     // A tree whose best line ends in a terminal node burns simulation after simulation without
     // ever needing the evaluator; left unbounded, one such tree (up to `iters` descents) sets the
     // duration of the whole launch.  While nothing is pending the launch may stop after a few of
     // them -- the next launch resumes the very same sequence, so results do not change.
-    constexpr unsigned kMaxTerminalPerLaunch = 4;
+    const unsigned kMaxTerminalPerLaunch = f.vl == 1 ? 1u : 4u;   // vl == 1: exactly one descent per launch
     while (started < f.iters && np < f.vl && !(np == 0 && st_term >= kMaxTerminalPerLaunch)) {
         AzBoard<NW> b = rootb;
         int player = root_player, mc = root_mc, len = 1;
         uint32_t node = 0;
         if (lane == 0) s_path[0] = 0;
         AzMeta m = meta[0];
-        while (m.status == AZ_ST_EXPANDED) {                  // mcts.py:20-23
+        int pn;
+        {
+            const AzHot hr = hot[0];
+            pn = hr.N + (int)hr.V;
+        }
+        // One memory round trip per level: every lane fetches hot AND meta of its children, the
+        // winner's meta / visit count arrive by shuffle (mcts.py:20-23, node.py:42-47).
+        while (m.status == AZ_ST_EXPANDED) {
             const int nc = m.nchild;
             const uint32_t cb = m.child_base;
-            int pn = hot[node].N;
-            if (use_vl) pn += vlc[node];
-            int bi = 0x7fffffff;
+            int bi = 0x7fffffff, bn = 0;
+            unsigned long long bm = 0ull;
             if (node == 0 && f.use_noise) {
                 const double s = __dsqrt_rn((double)pn);
                 double best = -1.0 / 0.0;
                 for (int c = lane; c < nc; c += G) {
-                    AzHot h = hot[cb + c];
-                    int n = h.N;
-                    double W = h.W;
-                    if (use_vl) { const int v = vlc[cb + c]; n += v; W -= (double)v; }
+                    const AzHot h = hot[cb + c];
+                    const unsigned long long mm = meta64[cb + c];
+                    const int n = h.N + (int)h.V;
+                    const double W = wsum[cb + c] - (double)h.V;
                     const double sc = az_puct64(W, f.root_prior64[(size_t)tree * g.max_children + c], n, s);
-                    if (sc > best) { best = sc; bi = c; }
+                    if (sc > best) { best = sc; bi = c; bm = mm; bn = n; }
                 }
                 az_group_argmax<G, double>(gmask, best, bi);
             } else {
-                const float s = __double2float_rn(__dsqrt_rn((double)pn));
+                const float s = __fsqrt_rn((float)pn);
                 float best = -1.0f / 0.0f;
                 for (int c = lane; c < nc; c += G) {
-                    AzHot h = hot[cb + c];
+                    const AzHot h = hot[cb + c];
+                    const unsigned long long mm = meta64[cb + c];
+                    const double Wc = use_vl ? wsum[cb + c] : 0.0;    // independent of h: same round trip
                     int n = h.N;
-                    double W = h.W;
-                    if (use_vl) { const int v = vlc[cb + c]; n += v; W -= (double)v; }
-                    const float sc = az_puct32(W, h.P, n, s);
-                    if (sc > best) { best = sc; bi = c; }
+                    float q = h.Q;
+                    if (use_vl && h.V) {                              // virtual loss: n + v visits, v losses
+                        n += (int)h.V;
+                        q = az_q32(Wc - (double)h.V, n);
+                    }
+                    const float sc = az_puct32(q, h.P, n, s);
+                    if (sc > best) { best = sc; bi = c; bm = mm; bn = n; }
                 }
                 az_group_argmax<G, float>(gmask, best, bi);
             }
-            if (bi == 0x7fffffff) bi = 0;                     // all-NaN guard: max() keeps the first
             st_reads += nc;
             ++st_sel;
+            if (bi == 0x7fffffff) {                               // all-NaN guard: max() keeps the first
+                bi = 0;
+                bm = meta64[cb];
+                const AzHot h0 = hot[cb];
+                bn = h0.N + (int)h0.V;
+            } else {                                              // the lane that scored child bi holds its records
+                bm = __shfl_sync(gmask, bm, bi % G, G);
+                bn = __shfl_sync(gmask, bn, bi % G, G);
+            }
             node = cb + bi;
+            pn = bn;
             if (lane == 0) s_path[len] = node;
             ++len;
-            m = meta[node];
+            m = *reinterpret_cast<const AzMeta*>(&bm);
             b.put(player, m.action);                          // Game.make_move (mcts.py:23)
             player ^= 1;
             ++mc;
@@ -228,13 +283,7 @@ __global__ void __launch_bounds__(128) az_advance_kernel(AzForestDev f, int smem
         }
         if (status == AZ_ST_WIN || status == AZ_ST_DRAW) {
             const double v = status == AZ_ST_WIN ? 1.0 : 0.0;
-            for (int i = lane; i < len; i += G) {
-                const uint32_t nd = s_path[i];
-                AzHot h = hot[nd];
-                h.N += 1;
-                h.W = __dadd_rn(h.W, ((len - 1 - i) & 1) ? -v : v);
-                hot[nd] = h;
-            }
+            for (int i = lane; i < len; i += G) az_backup_node(hot, wsum, s_path[i], ((len - 1 - i) & 1) ? -v : v, false);
             __syncwarp(gmask);
             ++st_term;
             ++st_sims;
@@ -251,13 +300,12 @@ __global__ void __launch_bounds__(128) az_advance_kernel(AzForestDev f, int smem
         for (int i = lane; i < len; i += G) {
             const uint32_t nd = s_path[i];
             gpath[i] = nd;
-            if (use_vl) vlc[nd] += 1;
+            if (use_vl) hot[nd].V += 1;
         }
         if (lane == 0) {
             f.path_len[pj] = (uint16_t)len;
             f.leaf_slot[pj] = slot;
-            f.pend_player[pj] = (uint8_t)player;
-            f.pend_mc[pj] = (uint16_t)mc;
+            f.pend_action[pj] = m.action;
             f.leaf_player[slot] = (uint8_t)player;
             f.leaf_tree[slot] = tree;
             if (use_vl) {
@@ -306,17 +354,18 @@ __global__ void az_begin_move_kernel(AzForestDev f) {
     const int tree = blockIdx.x * blockDim.x + threadIdx.x;
     if (tree >= f.n_trees) return;
     AzHot h;
-    h.W = 0.0;
-    h.P = 0.f;
     h.N = 0;
+    h.Q = 0.f;
+    h.P = 0.f;
+    h.V = 0;
     f.hot[(size_t)tree * f.cap] = h;
+    f.wsum[(size_t)tree * f.cap] = 0.0;
     AzMeta m;
     m.child_base = 0;
     m.action = 0;
     m.nchild = 0;
     m.status = AZ_ST_LEAF;
     f.meta[(size_t)tree * f.cap] = m;
-    f.vlc[(size_t)tree * f.cap] = 0;
     f.n_nodes[tree] = 1;
     f.sims_done[tree] = 0;
     f.n_pending[tree] = 0;
@@ -423,7 +472,7 @@ __global__ void az_root_visits_kernel(AzForestDev f, int* visits, double* q) {
     if (m.status == AZ_ST_EXPANDED)
         for (int c = threadIdx.x; c < m.nchild; c += blockDim.x)
             visits[(size_t)tree * A + az_action_index(f.g, meta[m.child_base + c].action)] = hot[m.child_base + c].N;
-    if (threadIdx.x == 0 && q) q[tree] = hot[0].N ? hot[0].W / (double)hot[0].N : 0.0;   // gomoku.py:141
+    if (threadIdx.x == 0 && q) q[tree] = hot[0].N ? f.wsum[(size_t)tree * f.cap] / (double)hot[0].N : 0.0;   // gomoku.py:141
 }
 
 }  // namespace
@@ -595,7 +644,12 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     // re-enables them for experiments.
     f->G = 32;
     if (const char* e = getenv("AZ_FOREST_GROUP")) if (atoi(e) == 8 && g.max_children <= 9) f->G = 8;
-    size_t per_group = 4 * (size_t)d.max_depth + ((g.max_children + 15) & ~15) + 2 * (size_t)g.set_slots;
+    // legal-move scratch for up to AZ_LP pending leaves expanded in parallel, bounded by ~24 KB per tree
+    const size_t lm_bytes = ((g.max_children + 15) & ~15) + 2 * (size_t)g.set_slots;
+    int lp = std::min(vl_batch, AZ_LP);
+    while (lp > 1 && lp * lm_bytes > 24 * 1024) --lp;
+    d.lp = lp;
+    size_t per_group = 4 * (size_t)d.max_depth + lp * lm_bytes;
     f->smem_per_group = (int)((per_group + 15) & ~(size_t)15);
     const size_t nodes = (size_t)n_trees * d.cap;
     const int nw = g.nw;
@@ -606,7 +660,7 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     }
     AZ_ALLOC(d.hot, nodes);
     AZ_ALLOC(d.meta, nodes);
-    AZ_ALLOC(d.vlc, nodes);
+    AZ_ALLOC(d.wsum, nodes);
     AZ_ALLOC(d.root_words, (size_t)n_trees * 2 * nw);
     AZ_ALLOC(d.root_player, (size_t)n_trees);
     AZ_ALLOC(d.root_mc, (size_t)n_trees);
@@ -621,6 +675,7 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     AZ_ALLOC(d.pend_words, (size_t)d.max_leaves * 2 * nw);
     AZ_ALLOC(d.pend_player, (size_t)d.max_leaves);
     AZ_ALLOC(d.pend_mc, (size_t)d.max_leaves);
+    AZ_ALLOC(d.pend_action, (size_t)d.max_leaves);
     AZ_ALLOC(d.n_leaves, 4);
     d.n_done = d.n_leaves + 1;
     AZ_ALLOC(d.leaf_words, (size_t)d.max_leaves * 2 * nw);
@@ -840,23 +895,26 @@ extern "C" int az_forest_root_children(az_forest* f, int tree, int max_children,
     AZ_CUDA_OK(cudaStreamSynchronize(s));
     AzMeta m;
     AzHot h;
+    double w0 = 0.0;
     AZ_CUDA_OK(cudaMemcpy(&m, f->d.meta + (size_t)tree * f->d.cap, sizeof(m), cudaMemcpyDeviceToHost));
     AZ_CUDA_OK(cudaMemcpy(&h, f->d.hot + (size_t)tree * f->d.cap, sizeof(h), cudaMemcpyDeviceToHost));
+    AZ_CUDA_OK(cudaMemcpy(&w0, f->d.wsum + (size_t)tree * f->d.cap, sizeof(w0), cudaMemcpyDeviceToHost));
     if (root_visit) *root_visit = h.N;
-    if (root_value) *root_value = h.W;
+    if (root_value) *root_value = w0;
     if (m.status != AZ_ST_EXPANDED) return 0;
     const int nc = std::min<int>(m.nchild, max_children);
     std::vector<AzHot> hh(nc);
     std::vector<AzMeta> mm(nc);
-    std::vector<double> p64(nc);
+    std::vector<double> ww(nc), p64(nc);
     AZ_CUDA_OK(cudaMemcpy(hh.data(), f->d.hot + (size_t)tree * f->d.cap + m.child_base, nc * sizeof(AzHot), cudaMemcpyDeviceToHost));
     AZ_CUDA_OK(cudaMemcpy(mm.data(), f->d.meta + (size_t)tree * f->d.cap + m.child_base, nc * sizeof(AzMeta), cudaMemcpyDeviceToHost));
+    AZ_CUDA_OK(cudaMemcpy(ww.data(), f->d.wsum + (size_t)tree * f->d.cap + m.child_base, nc * sizeof(double), cudaMemcpyDeviceToHost));
     if (f->d.use_noise)
         AZ_CUDA_OK(cudaMemcpy(p64.data(), f->d.root_prior64 + (size_t)tree * f->d.g.max_children, nc * 8, cudaMemcpyDeviceToHost));
     for (int c = 0; c < nc; ++c) {
         if (cells_host) cells_host[c] = mm[c].action;
         if (visits_host) visits_host[c] = hh[c].N;
-        if (values_host) values_host[c] = hh[c].W;
+        if (values_host) values_host[c] = ww[c];
         if (priors_host) priors_host[c] = f->d.use_noise ? p64[c] : (double)hh[c].P;
     }
     return m.nchild;

@@ -1,9 +1,9 @@
 // Device-side view of a forest of concurrent search trees (one per game) in HBM.
 //
 // Layout (SoA across node fields, grouped by access pattern):
-//   hot [tree*cap + i]   AzHot  {W f64, P f32, N i32}  -- 16 B, one vector load per child in PUCT
-//   meta[tree*cap + i]   AzMeta {child_base, action, nchild, status} -- 8 B, selected child only
-//   vlc [tree*cap + i]   u8 virtual-loss count (only touched when vl > 1)
+//   hot [tree*cap + i]   AzHot  {N i32, Q f32, P f32, V u32}  -- 16 B, one vector load per child in PUCT
+//   meta[tree*cap + i]   AzMeta {child_base, action, nchild, status} -- 8 B, fetched together with hot
+//   wsum[tree*cap + i]   f64 value sum W -- read-modify-written by backups only (Q caches (float)(W/N))
 // Children of a node are contiguous (bump allocator per tree), in the reference's child
 // order (= order of Game.get_valid_moves, ai/node.py:55-59).  Node 0 is the root.
 #pragma once
@@ -29,10 +29,11 @@ struct AzForestDev {
     int max_depth;    // path entries per leaf
     int max_leaves;   // n_trees * vl
     int use_noise;    // Dirichlet noise mixed into the root priors (utils.py:12-27)
+    int lp;           // pending leaves of a tree expanded in parallel (<= AZ_LP, <= vl)
 
     AzHot* hot;
     AzMeta* meta;
-    uint8_t* vlc;
+    double* wsum;     // W of every node (f64 running sum in visitation order)
 
     // per tree
     uint64_t* root_words;    // [n_trees][2*nw]  side-0 words then side-1 words
@@ -51,6 +52,7 @@ struct AzForestDev {
     uint64_t* pend_words;    // [n_trees][vl][2*nw]  leaf position (side 0, side 1)
     uint8_t* pend_player;
     uint16_t* pend_mc;
+    uint16_t* pend_action;   // cell of the move that led to the leaf (meta.action, rewritten at expansion)
 
     // evaluation batch (compacted)
     int* n_leaves;           // device counter, zeroed before every advance

@@ -16,7 +16,7 @@
 //   values: D2[feature][t] = Wv2 x A^T    (M = 128 features per block, N = NTP token columns)
 // D1 has tokens on TMEM lanes (the masked Gram sum a^T G a is thread-local); D2 has FEATURES on
 // lanes, so the softmax-weighted sum over a board's tokens is thread-local as well.
-//   warps 0-3  epilogue   warps 4-7  A-tile builders   warp 8  TMA (weights, once) + MMA issue
+//   warps 0-7  epilogue (two groups)   warps 8-11  A-tile builders   warp 12  TMA (weights, once) + MMA issue
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -42,7 +42,7 @@ struct AzFrontArgs {
 static inline size_t az_front_smem(const AzFrontArgs& a) {
     const size_t tile = (size_t)a.NTP * 128;
     return 1024 + 2 * (size_t)a.KB * tile + (size_t)a.KB * a.NS * 128 + (size_t)a.KB * a.D * 128 +
-           2 * 128 * 16 + 8 * 128 * 4 + 128 * 4 + 128 + 256;
+           2 * 128 * 16 + 8 * 128 * 4 + 2 * 128 * 4 + 128 + 256;
 }
 
 namespace azptx {
@@ -56,12 +56,18 @@ __device__ __forceinline__ void bar_sync_named(int id, int nthreads) {
 }
 }  // namespace azptx
 
+// Threads: warps 0-3 epilogue group 0, warps 4-7 epilogue group 1 (same TMEM lane quarters, the two
+// groups split the stat columns and the value blocks), warps 8-11 A-tile builders, warp 12 TMA + MMA.
+#define AZ_FRONT_THREADS 416
+
 template <int TS8>
-__global__ void __launch_bounds__(288, 1) az_front_kernel(const __grid_constant__ CUtensorMap tm_wst,
-                                                          const __grid_constant__ CUtensorMap tm_wv, AzFrontArgs a) {
+__global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __grid_constant__ CUtensorMap tm_wst,
+                                                                       const __grid_constant__ CUtensorMap tm_wv, AzFrontArgs a) {
     extern __shared__ unsigned char smem_dyn[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
-    const int KB = a.KB, D = a.D, T = a.T, P = a.patch, NTP = a.NTP, NS = a.NS, TS = TS8 * 8;
+    // pointer arithmetic (not an integer round trip) keeps the shared address space: LDS/STS, not generic
+    unsigned char* smem = smem_dyn + ((1024u - (azptx::smem_u32(smem_dyn) & 1023u)) & 1023u);
+    const int KB = a.KB, D = a.D, T = a.T, P = a.patch, NTP = a.NTP, NS = a.NS;
+    constexpr int TS = TS8 * 8;
     const int FB = D >> 7;                                       // feature blocks of 128
     const uint32_t tile_bytes = (uint32_t)NTP * 128;
     unsigned char* s_a = smem;                                   // [2 stages][KB][NTP rows][128 B]
@@ -69,16 +75,16 @@ __global__ void __launch_bounds__(288, 1) az_front_kernel(const __grid_constant_
     unsigned char* s_wv = s_wst + (size_t)KB * NS * 128;         // [FB][KB][128 rows][128 B]
     uint4* s_mask = reinterpret_cast<uint4*>(s_wv + (size_t)FB * KB * 16384);   // [2][128] row bit masks (K bits)
     float* s_w = reinterpret_cast<float*>(s_mask + 2 * 128);     // [8 heads][128 rows] scores, then softmax weight * r
-    float* s_r = s_w + 8 * 128;                                  // [128] LayerNorm rstd per row
-    uint2* s_lut = reinterpret_cast<uint2*>(s_r + 128);          // 16 entries: nibble -> 4 bf16 (0 / 1.0)
+    float* s_q = s_w + 8 * 128;                                  // [2][128] partial Gram sums of the two groups
+    uint2* s_lut = reinterpret_cast<uint2*>(s_q + 2 * 128);      // 16 entries: nibble -> 4 bf16 (0 / 1.0)
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_lut + 16);
     uint64_t* w_full = bars;            // 1
     uint64_t* a_full = bars + 1;        // 2   (128 builder arrivals)
     uint64_t* a_empty = bars + 3;       // 2   (MMA commit + epilogue "masks consumed")
     uint64_t* st_full = bars + 5;       // 1
-    uint64_t* st_empty = bars + 6;      // 1   (128 epilogue arrivals)
+    uint64_t* st_empty = bars + 6;      // 1   (256 epilogue arrivals)
     uint64_t* v_full = bars + 7;        // 4
-    uint64_t* v_empty = bars + 11;      // 4   (128 epilogue arrivals)
+    uint64_t* v_empty = bars + 11;      // 4   (128 arrivals of the group that owns the block)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -91,7 +97,7 @@ __global__ void __launch_bounds__(288, 1) az_front_kernel(const __grid_constant_
         s_lut[n] = make_uint2(((n & 1u) ? 0x00003F80u : 0u) | ((n & 2u) ? 0x3F800000u : 0u),
                               ((n & 4u) ? 0x00003F80u : 0u) | ((n & 8u) ? 0x3F800000u : 0u));
     }
-    if (warp == 8 && lane == 0) {
+    if (warp == 12 && lane == 0) {
         azptx::prefetch_tmap(&tm_wst);
         azptx::prefetch_tmap(&tm_wv);
         azptx::mbar_init(w_full, 1);
@@ -100,7 +106,7 @@ __global__ void __launch_bounds__(288, 1) az_front_kernel(const __grid_constant_
             azptx::mbar_init(&a_empty[i], 2);
         }
         azptx::mbar_init(st_full, 1);
-        azptx::mbar_init(st_empty, 128);
+        azptx::mbar_init(st_empty, 256);
         for (int i = 0; i < 4; ++i) {
             azptx::mbar_init(&v_full[i], 1);
             azptx::mbar_init(&v_empty[i], 128);
@@ -114,7 +120,7 @@ __global__ void __launch_bounds__(288, 1) az_front_kernel(const __grid_constant_
     const uint32_t tmem_base = *tmem_slot;
     // TMEM columns: [0, 128) stats accumulator, value slots of NTP columns from 128 on.
 
-    if (warp == 8) {
+    if (warp == 12) {
         // ------------------------------ weights in once, then MMA issue -----------------------------
         if (lane == 0) {
             azptx::mbar_arrive_expect_tx(w_full, (uint32_t)(KB * NS * 128 + FB * KB * 16384));
@@ -126,7 +132,7 @@ __global__ void __launch_bounds__(288, 1) az_front_kernel(const __grid_constant_
         azptx::mbar_wait(w_full, 0);
         const uint32_t idesc_st = azptx::umma_idesc_bf16(128, (uint32_t)NS);
         const uint32_t idesc_v = azptx::umma_idesc_bf16(128, (uint32_t)NTP);
-        int it = 0;
+        int it = 0, slot = 0, round = 0;                           // value-block counter g = round * nslots + slot
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it & 1;
             const unsigned char* at = s_a + (size_t)st * KB * tile_bytes;
@@ -144,8 +150,7 @@ __global__ void __launch_bounds__(288, 1) az_front_kernel(const __grid_constant_
             }
             __syncwarp();
             for (int fb = 0; fb < FB; ++fb) {
-                const int g = it * FB + fb, slot = g % nslots;
-                azptx::mbar_wait(&v_empty[slot], ((g / nslots) & 1) ^ 1);
+                azptx::mbar_wait(&v_empty[slot], (round & 1) ^ 1);
                 azptx::tc_fence_after();
                 if (lane == 0) {
                     for (int ks = 0; ks < a.ksteps; ++ks) {
@@ -158,55 +163,63 @@ __global__ void __launch_bounds__(288, 1) az_front_kernel(const __grid_constant_
                     if (fb == FB - 1) azptx::umma_commit(&a_empty[st]);   // every MMA reading this A stage is done
                 }
                 __syncwarp();
+                if (++slot == nslots) { slot = 0; ++round; }
             }
         }
-    } else if (warp >= 4) {
+    } else if (warp >= 8) {
         // ------------------------------ A-tile builders: one thread per token row -------------------
-        const int r = threadIdx.x - 128;
+        const int r = threadIdx.x - 256;
         const int b_in_tile = r / TS, t = r - b_in_tile * TS;
         const bool row_used = b_in_tile < a.nb && t < T;
         int cr = 0, cc = 0;
         if (row_used && t > 0) { cr = (t - 1) / a.cols; cc = (t - 1) - cr * a.cols; }
-        const int half = P >> 1;
+        const int half = P >> 1, pp = P * P;
         const uint32_t colmask = (1u << a.cols) - 1u, pmask = (1u << P) - 1u;
+        // the window geometry of this row does not depend on the board: fold it into constants
+        const int rshift = cc >= half ? cc - half : 0, lshift = cc >= half ? 0 : half - cc;
+        uint32_t inb = 0;                                            // in-bounds taps (plane 2 is all ones)
+        for (int kr = 0; kr < P; ++kr) {
+            const int rr = cr + kr - half;
+            if (rr >= 0 && rr < a.rows) inb |= (((colmask >> rshift) << lshift) & pmask) << (kr * P);
+        }
+        const unsigned __int128 onehot = (unsigned __int128)1 << (a.kc + t);
+        unsigned char* const arow0 = s_a + (size_t)r * 128;
+        const int sw = r & 7;
         int it = 0;
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it & 1;
-            azptx::mbar_wait(&a_empty[st], ((it >> 1) & 1) ^ 1);
             const int item = tile * a.nb + b_in_tile;
             const bool live = row_used && item < items;
             unsigned __int128 km = 0;
             if (live) {
                 if (t > 0) {
-                    const uint64_t w0 = a.leaf_words[(size_t)(a.batch.offset + item) * 2];
-                    const uint64_t w1 = a.leaf_words[(size_t)(a.batch.offset + item) * 2 + 1];
+                    const ulonglong2 w = *reinterpret_cast<const ulonglong2*>(a.leaf_words + (size_t)(a.batch.offset + item) * 2);
                     const bool stm = a.planes == 3 && a.leaf_player[a.batch.offset + item] != 0;
+                    uint32_t p0 = 0, p1 = 0;                         // taps of planes 0 / 1, bit kr*P + kcol  (P*P <= 32)
+#pragma unroll 5
                     for (int kr = 0; kr < P; ++kr) {
                         const int rr = cr + kr - half;
                         if (rr < 0 || rr >= a.rows) continue;
                         const int sh = rr * a.cols;
-                        // window columns cc-half .. cc+half of board row rr, tap kcol at bit kcol
-                        uint32_t b0 = (uint32_t)(w0 >> sh) & colmask, b1 = (uint32_t)(w1 >> sh) & colmask, b2 = colmask;
-                        if (cc >= half) { b0 >>= (cc - half); b1 >>= (cc - half); b2 >>= (cc - half); }
-                        else { b0 <<= (half - cc); b1 <<= (half - cc); b2 <<= (half - cc); }
-                        b0 &= pmask; b1 &= pmask; b2 &= pmask;
-                        km |= (unsigned __int128)b0 << (kr * P);
-                        km |= (unsigned __int128)b1 << (P * P + kr * P);
-                        if (stm) km |= (unsigned __int128)b2 << (2 * P * P + kr * P);
+                        const uint32_t b0 = (uint32_t)(w.x >> sh) & colmask, b1 = (uint32_t)(w.y >> sh) & colmask;
+                        p0 |= (((b0 >> rshift) << lshift) & pmask) << (kr * P);
+                        p1 |= (((b1 >> rshift) << lshift) & pmask) << (kr * P);
                     }
+                    km = (unsigned __int128)p0 | ((unsigned __int128)p1 << pp);
+                    if (stm) km |= (unsigned __int128)inb << (2 * pp);
                 }
-                km |= (unsigned __int128)1 << (a.kc + t);           // one-hot token index -> pos-emb / bias row
+                km |= onehot;                                        // one-hot token index -> pos-emb / bias row
             }
-            const uint64_t klo = (uint64_t)km, khi = (uint64_t)(km >> 64);
+            azptx::mbar_wait(&a_empty[st], ((it >> 1) & 1) ^ 1);
             if (r < NTP) {
-                unsigned char* arow = s_a + (size_t)st * KB * tile_bytes + (size_t)r * 128;
+                unsigned char* arow = arow0 + (size_t)st * KB * tile_bytes;
                 for (int kb = 0; kb < KB; ++kb) {
-                    const uint64_t kw = kb == 0 ? klo : khi;
+                    const uint64_t kw = kb == 0 ? (uint64_t)km : (uint64_t)(km >> 64);
 #pragma unroll
                     for (int c = 0; c < 8; ++c) {
                         const uint32_t by = (uint32_t)(kw >> (c * 8)) & 0xFFu;
                         const uint2 lo = s_lut[by & 15u], hi = s_lut[by >> 4];
-                        *reinterpret_cast<uint4*>(arow + (size_t)kb * tile_bytes + ((c ^ (r & 7)) << 4)) = make_uint4(lo.x, lo.y, hi.x, hi.y);
+                        *reinterpret_cast<uint4*>(arow + (size_t)kb * tile_bytes + ((c ^ sw) << 4)) = make_uint4(lo.x, lo.y, hi.x, hi.y);
                     }
                 }
             }
@@ -217,108 +230,111 @@ __global__ void __launch_bounds__(288, 1) az_front_kernel(const __grid_constant_
             azptx::mbar_arrive(&a_full[st]);
         }
     } else {
-        // ------------------------------ epilogue ----------------------------------------------------
-        const int tid = threadIdx.x;                                 // token row (stats) / feature in block (values)
-        const uint32_t tq = tmem_base + ((uint32_t)(warp * 32) << 16);
+        // ------------------------------ epilogue (two groups of 128 threads) ------------------------
+        const int grp = warp >> 2;
+        const int tid = threadIdx.x & 127;                           // token row (stats) / feature in block (values)
+        const uint32_t tq = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
         const int H = a.H, hd = D / H;
         const int pairs = a.nb * H;
         int tpp = 32;
-        while (tpp * pairs > 128) tpp >>= 1;                         // threads per (board, head) softmax
-        const int pair = tid / tpp, sub = tid - pair * tpp;
+        while (tpp * pairs > 256) tpp >>= 1;                         // threads per (board, head) softmax
+        const int pair = (int)threadIdx.x / tpp, sub = (int)threadIdx.x - pair * tpp;
+        const bool pair_on = pair < pairs;
+        const int pb = pair_on ? pair / H : 0, ph = pair_on ? pair - pb * H : 0;
         const float inv_d = 1.0f / (float)D;
-        int it = 0;
+        int it = 0, slot0 = 0, round0 = 0;                           // block counter at fb = 0 of the current tile
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it & 1;
-            // ---- per-row LayerNorm statistic and scores from the stats accumulator
+            // ---- Gram sum a^T G a (this group's half of the columns) and raw scores
             azptx::mbar_wait(st_full, it & 1);
             azptx::tc_fence_after();
             const uint4 mk = s_mask[st * 128 + tid];
-            const uint32_t mw[4] = {mk.x, mk.y, mk.z, mk.w};
-            float q = 0.f, zs[8];
+            float q0 = 0.f, q1 = 0.f;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int cc = 0; cc < 2; ++cc) {
+                const int c = grp * 2 + cc;
                 if (c * 32 < NS) {
                     uint32_t v[32];
                     azptx::tmem_ld32(tq + c * 32, v);
                     azptx::tmem_ld_wait();
                     if (c == 0) {
 #pragma unroll
-                        for (int h = 0; h < 8; ++h) zs[h] = __uint_as_float(v[h]);
+                        for (int h = 0; h < 8; ++h) s_w[h * 128 + tid] = __uint_as_float(v[h]);
                     }
-                    const uint32_t m = mw[c];
+                    const uint32_t m = c == 0 ? mk.x : (c == 1 ? mk.y : (c == 2 ? mk.z : mk.w));
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) q += ((m >> i) & 1u) ? __uint_as_float(v[i]) : 0.f;
+                    for (int i = 0; i < 32; i += 2) {
+                        q0 += ((m >> i) & 1u) ? __uint_as_float(v[i]) : 0.f;
+                        q1 += ((m >> (i + 1)) & 1u) ? __uint_as_float(v[i + 1]) : 0.f;
+                    }
                 }
             }
             azptx::tc_fence_before();
             azptx::mbar_arrive(st_empty);
-            const float rstd = rsqrtf(fmaxf(q, 0.f) * inv_d + 1e-5f);
-            s_r[tid] = rstd;
-#pragma unroll
-            for (int h = 0; h < 8; ++h) s_w[h * 128 + tid] = zs[h] * rstd;
-            azptx::bar_sync_named(1, 128);
-            if (tid == 0) azptx::mbar_arrive(&a_empty[st]);          // row masks of this stage consumed
+            s_q[grp * 128 + tid] = q0 + q1;
+            azptx::bar_sync_named(1, 256);
+            if (threadIdx.x == 0) azptx::mbar_arrive(&a_empty[st]);  // row masks of this stage consumed
             // ---- softmax over the T tokens of each (board, head); weight = p * rstd
             {
-                const bool on = pair < pairs;
-                const int b = on ? pair / H : 0, h = on ? pair - b * H : 0;
-                float* sw = s_w + h * 128 + b * TS;
-                const float* sr = s_r + b * TS;
+                float* sw = s_w + ph * 128 + pb * TS;
+                const float* sq = s_q + pb * TS;
                 float mx = -1e30f;
-                for (int t = sub; t < T; t += tpp) mx = fmaxf(mx, sw[t]);
+                for (int t = sub; t < T; t += tpp) {
+                    const float rstd = rsqrtf(fmaxf(sq[t] + sq[128 + t], 0.f) * inv_d + 1e-5f);
+                    const float sc = sw[t] * rstd;
+                    if (pair_on) sw[t] = sc;
+                    mx = fmaxf(mx, sc);
+                }
                 for (int o = tpp >> 1; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
                 float sum = 0.f;
                 for (int t = sub; t < T; t += tpp) sum += __expf(sw[t] - mx);
                 for (int o = tpp >> 1; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
                 const float inv = 1.0f / sum;
-                if (on)
-                    for (int t = sub; t < TS; t += tpp) sw[t] = t < T ? __expf(sw[t] - mx) * inv * sr[t] : 0.f;
+                if (pair_on)
+                    for (int t = sub; t < TS; t += tpp) {
+                        float wgt = 0.f;
+                        if (t < T) wgt = __expf(sw[t] - mx) * inv * rsqrtf(fmaxf(sq[t] + sq[128 + t], 0.f) * inv_d + 1e-5f);
+                        sw[t] = wgt;
+                    }
             }
-            azptx::bar_sync_named(1, 128);
+            azptx::bar_sync_named(1, 256);
             // ---- value blocks: o[f] = sum_t w[h(f)][t] * z[f][t] + bias, features on TMEM lanes
+            int slot = slot0, round = round0;
             for (int fb = 0; fb < FB; ++fb) {
-                const int g = it * FB + fb, slot = g % nslots;
-                azptx::mbar_wait(&v_full[slot], (g / nslots) & 1);
-                azptx::tc_fence_after();
-                const int f = fb * 128 + tid;
-                const float* wrow = s_w + (f / hd) * 128;
-                const float bias = __ldg(a.bias_v + f);
-                const uint32_t tcol = tq + 128 + slot * NTP;
-                float acc[4] = {0.f, 0.f, 0.f, 0.f};                 // <= 4 boards at a time in registers
-                for (int b0 = 0; b0 < a.nb; b0 += 4) {
+                if ((fb & 1) == grp) {
+                    azptx::mbar_wait(&v_full[slot], round & 1);
+                    azptx::tc_fence_after();
+                    const int f = fb * 128 + tid;
+                    const float* wrow = s_w + (f / hd) * 128;
+                    const float bias = __ldg(a.bias_v + f);
+                    const uint32_t tcol = tq + 128 + slot * NTP;
+                    bf16* dst = a.oc + (size_t)tile * a.nb * D + f;
+                    for (int b = 0; b < a.nb; ++b) {
+                        uint32_t v[TS8][8];
 #pragma unroll
-                    for (int bi = 0; bi < 4; ++bi) {
-                        const int b = b0 + bi;
-                        acc[bi] = 0.f;
-                        if (b < a.nb) {
-                            uint32_t v[TS8][8];
-#pragma unroll
-                            for (int j = 0; j < TS8; ++j) azptx::tmem_ld8(tcol + b * TS + j * 8, v[j]);
-                            azptx::tmem_ld_wait();
-#pragma unroll
-                            for (int j = 0; j < TS8; ++j) {
-                                const float4 w0 = *reinterpret_cast<const float4*>(wrow + b * TS + j * 8);
-                                const float4 w1 = *reinterpret_cast<const float4*>(wrow + b * TS + j * 8 + 4);
-                                acc[bi] += w0.x * __uint_as_float(v[j][0]) + w0.y * __uint_as_float(v[j][1]) +
-                                           w0.z * __uint_as_float(v[j][2]) + w0.w * __uint_as_float(v[j][3]) +
-                                           w1.x * __uint_as_float(v[j][4]) + w1.y * __uint_as_float(v[j][5]) +
-                                           w1.z * __uint_as_float(v[j][6]) + w1.w * __uint_as_float(v[j][7]);
-                            }
+                        for (int j = 0; j < TS8; ++j) azptx::tmem_ld8(tcol + b * TS + j * 8, v[j]);
+                        azptx::tmem_ld_wait();
+                        if (b == a.nb - 1) {                         // slot fully read: hand it back to the MMA warp
+                            azptx::tc_fence_before();
+                            azptx::mbar_arrive(&v_empty[slot]);
                         }
-                    }
-                    if (b0 + 4 >= a.nb) {                            // slot fully read: hand it back before the stores
-                        azptx::tc_fence_before();
-                        azptx::mbar_arrive(&v_empty[slot]);
-                    }
+                        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
-                    for (int bi = 0; bi < 4; ++bi) {
-                        const int item = tile * a.nb + b0 + bi;
-                        if (b0 + bi < a.nb && item < items)
-                            a.oc[(size_t)item * D + f] = __float2bfloat16(acc[bi] + bias);
+                        for (int j = 0; j < TS8; ++j) {
+                            const float4 w0 = *reinterpret_cast<const float4*>(wrow + b * TS + j * 8);
+                            const float4 w1 = *reinterpret_cast<const float4*>(wrow + b * TS + j * 8 + 4);
+                            a0 += w0.x * __uint_as_float(v[j][0]) + w1.x * __uint_as_float(v[j][4]);
+                            a1 += w0.y * __uint_as_float(v[j][1]) + w1.y * __uint_as_float(v[j][5]);
+                            a2 += w0.z * __uint_as_float(v[j][2]) + w1.z * __uint_as_float(v[j][6]);
+                            a3 += w0.w * __uint_as_float(v[j][3]) + w1.w * __uint_as_float(v[j][7]);
+                        }
+                        if (tile * a.nb + b < items) dst[(size_t)b * D] = __float2bfloat16((a0 + a1) + (a2 + a3) + bias);
                     }
                 }
+                if (++slot == nslots) { slot = 0; ++round; }
             }
-            azptx::bar_sync_named(1, 128);                           // s_w / s_r are rewritten by the next tile
+            slot0 = slot; round0 = round;
+            azptx::bar_sync_named(1, 256);                           // s_w / s_q are rewritten by the next tile
         }
     }
     azptx::tc_fence_before();

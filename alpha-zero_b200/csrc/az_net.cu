@@ -442,7 +442,7 @@ extern "C" int az_net_finalize(az_net* n) {
     n->front = false;
     {
         const int H = n->H, kc = n->emb_kc, kused = kc + T;
-        if (n->folded && n->host_wemb_kpad && cells <= 63 && H <= 8 && kused + 8 <= 128 && D % 128 == 0 && D <= 512 &&
+        if (n->folded && n->host_wemb_kpad && cells <= 63 && H <= 8 && kused + 8 <= 128 && P <= 5 && D % 128 == 0 && D <= 512 &&
             !getenv("AZ_NO_FRONT")) {
             const int kpad = n->host_wemb_kpad, KB = kpad / 64;
             const std::vector<float>& wi = n->host_folded_w_in;
@@ -513,7 +513,7 @@ extern "C" int az_net_finalize(az_net* n) {
             fa = AzFrontArgs{};
             fa.rows = n->rows; fa.cols = n->cols; fa.planes = C; fa.patch = P; fa.T = T; fa.kc = kc; fa.D = D; fa.H = H;
             fa.TS = (T + 7) / 8 * 8;
-            fa.nb = std::min(128 / fa.TS, 128 / H);
+            fa.nb = std::min(128 / fa.TS, 256 / H);
             fa.NTP = (fa.nb * fa.TS + 15) / 16 * 16;
             fa.NS = NS;
             fa.KB = KB;
@@ -640,7 +640,7 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
             AZ_CUDA_OK(cudaFuncSetAttribute(az_front_kernel<TS8_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
             done = true;                                                                                                   \
         }                                                                                                                  \
-        az_front_kernel<TS8_><<<grid, 288, smem, s>>>(n->tm_fwst, n->tm_fwv, fa);                                          \
+        az_front_kernel<TS8_><<<grid, AZ_FRONT_THREADS, smem, s>>>(n->tm_fwst, n->tm_fwv, fa);                                          \
     } break;
             switch (fa.TS / 8) {
                 AZ_FRONT(1) AZ_FRONT(2) AZ_FRONT(3) AZ_FRONT(4) AZ_FRONT(5) AZ_FRONT(6) AZ_FRONT(7) AZ_FRONT(8)
@@ -886,6 +886,10 @@ extern "C" int az_net_invalidate_graphs(az_net* n) {
 // ---- per-kernel timing of eager forward passes (CUDA events on the launching stream) -------
 extern "C" int az_net_profile(az_net* n, int enable) {
     if (!n) return az_fail(AZ_EINVAL, "az_net_profile: null");
+    if (enable == 2 || enable == 3) {                          // resume / pause, totals kept
+        n->prof_on = enable == 2;
+        return AZ_OK;
+    }
     n->prof_on = enable != 0;
     if (enable) {
         for (int k = 0; k < 16; ++k) { n->prof_ms[k] = 0; n->prof_n[k] = 0; }

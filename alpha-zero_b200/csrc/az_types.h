@@ -32,10 +32,13 @@ struct AzGame {
 
 // Hot per-node record: everything PUCT reads for one child, one 16-byte load.
 struct __attribute__((aligned(16))) AzHot {
-    double W;         // ai/node.py:34  value sum, viewpoint of the player who moved in
-    float P;          // ai/node.py:36  prior (fp32, gathered from the unmasked softmax)
     int N;            // ai/node.py:33  visit count
+    float Q;          // (float)(W / N) exactly as utils.py:40 forms it, refreshed by every backup (unused while N == 0)
+    float P;          // ai/node.py:36  prior (fp32, gathered from the unmasked softmax)
+    uint32_t V;       // virtual-loss count (vl > 1 only)
 };
+// ai/node.py:34 value sum W (viewpoint of the player who moved in) lives in its own f64 array
+// (AzForestDev::wsum): only backups touch it.
 
 // Cold per-node record, read only for the selected child.
 struct __attribute__((aligned(8))) AzMeta {

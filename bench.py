@@ -115,6 +115,45 @@ def peaks():
         return dict(tflops=1400.0, hbm=6650.0, src="fallback (B200_PROFILING.md: ~1.4 PF sustained, 6.65 TB/s)")
 
 
+def roofline(wl, r, prof, pk, kind=None):
+    """Roofline entry of one kernel kind (default: the kind with the largest share of the step).
+    Algorithmic work per launch = per-leaf (or per-simulation) figure of DESIGN.md section 4 x the units of
+    one launch; duration = CUDA-event average over the profiled launches."""
+    G = game_class(wl)
+    D, H, P = NET["dim"], NET["heads"], NET["patch"]
+    T = G.rows * G.cols + 1
+    kused = G.feature_dim * P * P + T
+    leaves = r["leaves_per_step"]
+    per_step = {k: v["ms"] * (v["launches"] / max(prof["forest_advance"]["launches"], 1) if k != "forest_advance" else 1.0)
+                for k, v in prof.items()}
+    if kind is None:
+        kind = max(per_step, key=per_step.get)
+    ms = prof[kind]["ms"]
+    st = r["stats"]
+    flops = None
+    if kind == "front_fused":       # one contraction over the K binary inputs per token: D value + H score + K Gram columns
+        flops, name = 2.0 * leaves * T * kused * (D + H + kused), "az_front_kernel (embedding+LN1+V/score projection+cls attention, tcgen05)"
+    elif kind == "gemm_kv":
+        flops, name = 2.0 * leaves * T * D * r["proj_width"], f"az_gemm_kernel (all-token projection, N={r['proj_width']}, tcgen05)"
+    elif kind == "gemm_cls_rows":   # out_proj D*D, mlp D*4D, 4D*D over 3 launches -> average launch
+        flops, name = 2.0 * leaves * 9 * D * D / 3.0, "az_gemm_kernel (cls-row out_proj / MLP GEMMs, tcgen05; average of the 3 launches)"
+    elif kind == "embed_ln":
+        flops, name = 2.0 * leaves * T * 128 * D, "az_embed_mma_kernel (im2col embedding + LN, tcgen05)"
+    if flops is not None:
+        ach = flops / (ms / 1e3) / 1e12
+        return dict(kernel=name, bound="tensor", achieved=ach, peak=pk["tflops"], unit="TFLOP/s", frac=ach / pk["tflops"],
+                    traffic=None, peak_source=pk["src"], flops_per_launch=flops, ms_per_launch=ms, share_of_step=per_step[kind] / sum(per_step.values()))
+    if kind == "forest_advance":    # SURVEY 8d: 16 B per child scored + 8 B header per select + 24 B RMW per path node + 26 B per child written
+        sims = max(st["sims"], 1)
+        per_sim = (16.0 * st["child_reads"] + 8.0 * st["selects"] + 24.0 * (st["selects"] + st["sims"]) + 26.0 * st["children"]) / sims
+        nbytes = per_sim * wl["trees"] * wl["vl"]
+        ach = nbytes / (ms / 1e3) / 1e9
+        return dict(kernel="az_advance_kernel (PUCT select + expand + backup, one warp per tree)", bound="hbm", achieved=ach, peak=pk["hbm"],
+                    unit="GB/s", frac=ach / pk["hbm"], traffic=None, peak_source=pk["src"], bytes_per_sim=per_sim, bytes_per_launch=nbytes,
+                    ms_per_launch=ms, share_of_step=per_step[kind] / sum(per_step.values()))
+    return None
+
+
 def game_class(wl):
     from alpha_zero_b200 import games
     G = {"connect4": games.Connect4, "gomoku": games.Gomoku, "tictactoe": games.TicTacToe}[wl["game"]]
@@ -212,21 +251,23 @@ def run_b200(args, wl, rank, world):
         planes, players, mcs = roots[-1]
         forest.set_roots_planes(planes, players, mcs)
         forest.begin_move(iters)
-        adv = []
-        nprof = min(iters, 120)                                       # up to 120 steps into a search
-        for s in range(nprof):
+        adv, lv = [], []
+        eng.profile(True)
+        eng.profile(False)                                            # zero the totals, timing off
+        for s in range(iters // vl + 1 if vl > 1 else iters):         # the whole search, every 8th step timed
+            timed = s % 8 == 4
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            if s == nprof // 2:
-                eng.profile(True)
+            eng.profile_on(timed)
             a.record(stream)
             forest.advance()
             b.record(stream)
             eng.eval_leaves(forest, stream.cuda_stream)
-            if s >= nprof // 2:
+            if timed:
                 adv.append((a, b))
+                lv.append(forest.counts()[0])
         prof = eng.profile_read()
         eng.profile(False)
-        leaves, _ = forest.counts()
+        leaves = sum(lv) / max(len(lv), 1)
         out["profile"] = {k: dict(ms=v[0] / max(v[1], 1), launches=v[1]) for k, v in prof.items() if v[1]}
         out["profile"]["forest_advance"] = dict(ms=sum(a.elapsed_time(b) for a, b in adv) / len(adv), launches=len(adv))
         out["leaves_per_step"] = leaves
@@ -278,15 +319,10 @@ def main():
                 e2e=dict(value=e2e, unit="simulations/s", h2d_bytes_per_step=r["h2d"], d2h_bytes_per_step=r["d2h"]),
                 gpu_launches=r["gpu_launches"], search_stats=r["stats"])
     prof = r.get("profile", {})
-    if "gemm_kv" in prof:
-        G = game_class(wl)
-        T = G.rows * G.cols + 1
-        flops = 2.0 * r["leaves_per_step"] * T * NET["dim"] * r["proj_width"]    # [leaves*T, D] x [D, N]
-        ach = flops / (prof["gemm_kv"]["ms"] / 1e3) / 1e12
-        line["roofline"] = dict(kernel=f"az_gemm_kernel (all-token projection of the last block, N={r['proj_width']}, tcgen05)", bound="tensor",
-                                achieved=ach, peak=pk["tflops"], unit="TFLOP/s", frac=ach / pk["tflops"], traffic=None,
-                                peak_source=pk["src"], flops_per_launch=flops, ms_per_launch=prof["gemm_kv"]["ms"])
+    if prof:
         line["kernel_ms"] = {k: round(v["ms"], 4) for k, v in prof.items()}
+        line["roofline"] = roofline(wl, r, prof, pk)
+        line["rooflines_all"] = {k: rl for k, rl in ((k, roofline(wl, r, prof, pk, k)) for k in prof) if rl}
     if cb:
         line["cpu_baseline"] = cb
     print(json.dumps(line))

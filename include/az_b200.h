@@ -130,7 +130,8 @@ AZ_API int az_net_proj_width(az_net* n);   /* N of the all-token projection GEMM
  * one CUDA graph per step (advance + net), no per-node host work. */
 AZ_API int az_forest_search_net(az_forest* f, az_net* n, int iters, void* stream);
 AZ_API int az_net_invalidate_graphs(az_net* n);
-/* Per-kernel CUDA-event timing of eager forward passes (roofline numbers of bench.py). */
+/* Per-kernel CUDA-event timing of eager forward passes (roofline numbers of bench.py).
+ * enable: 1 = clear totals and start, 0 = stop, 2 = resume, 3 = pause (totals kept). */
 AZ_API int az_net_profile(az_net* n, int enable);
 AZ_API int az_net_profile_read(az_net* n, int max_kinds, const char** names_out, double* ms_out, long long* count_out);
 

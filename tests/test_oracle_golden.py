@@ -106,3 +106,10 @@ def test_selfplay_and_buffer_transform():
             assert np.array_equal(np.stack([s[0] for s in samples]), arrs[f"t{i}_buf_states"])
             assert np.array_equal(np.stack([s[1] for s in samples]), arrs[f"t{i}_buf_policies"])
             assert np.array_equal(np.asarray([s[2] for s in samples], dtype=np.float64), arrs[f"t{i}_buf_z"])
+
+
+def test_fp32_sqrt_equals_rounded_f64_sqrt_for_every_visit_count():
+    """The select kernel forms s = (float)sqrt((double)N_p) (utils.py:34,40 under NumPy 2) with one fp32
+    square root.  Double rounding is innocuous for sqrt when 53 >= 2*24 + 2; checked for every N_p < 2^24."""
+    n = np.arange(0, 1 << 24, dtype=np.int64)
+    assert np.array_equal(np.sqrt(n.astype(np.float64)).astype(np.float32), np.sqrt(n.astype(np.float32)))
