@@ -65,6 +65,26 @@ static int g_num_sms = 0;
 
 static int az_pick_bn(int N) { return N % 256 == 0 ? 256 : (N % 192 == 0 ? 192 : (N % 128 == 0 ? 128 : (N % 64 == 0 ? 64 : 0))); }
 
+// Column-tile width for a GEMM with few row tiles (the cls-row GEMMs: M = boards): the widest tile
+// is not the best one when it leaves SMs idle.  cost ~ waves x bytes staged per k-block.
+static int az_pick_bn_small_m(int N, int max_rows) {
+    if (!g_num_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int cands[3] = {256, 128, 64};
+    int best = 0;
+    long long best_cost = 0;
+    for (int bn : cands) {
+        if (N % bn) continue;
+        const long long tiles = (long long)((max_rows + 127) / 128) * (N / bn);
+        const long long cost = ((tiles + g_num_sms - 1) / g_num_sms) * (128 + bn);
+        if (!best || cost < best_cost) { best = bn; best_cost = cost; }
+    }
+    return best ? best : az_pick_bn(N);
+}
+
 template <int BN, int EPI>
 static int az_launch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& a, int max_rows, cudaStream_t s) {
     static bool attr_done = false;
@@ -86,8 +106,8 @@ static int az_launch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const 
 
 // A: bf16 [rows][K] (ld = lda), W: bf16 [N][K]; max_rows bounds the grid when M is device-side.
 static int az_launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& a, int epi, int max_rows,
-                          cudaStream_t s) {
-    const int bn = az_pick_bn(a.N);
+                          cudaStream_t s, int bn_forced = 0) {
+    const int bn = bn_forced ? bn_forced : az_pick_bn(a.N);
     if (!bn || a.K % 64) return az_fail(AZ_EINVAL, "gemm: N and K must be multiples of 64");
 #define AZ_G(BN_)                                                                              \
     if (bn == BN_) {                                                                           \
@@ -136,6 +156,8 @@ struct AzBlockW {
     bf16 *w_in = nullptr, *w_out = nullptr, *w1 = nullptr, *w2 = nullptr;
     float *b_in = nullptr, *b_out = nullptr, *b1 = nullptr, *b2 = nullptr;
     CUtensorMap tm_in, tm_q, tm_kv, tm_out, tm_w1, tm_w2;
+    CUtensorMap tm_out_c, tm_w1_c, tm_w2_c;     // same weights, tile width chosen for the cls-row GEMMs
+    int bn_out_c = 0, bn_w1_c = 0, bn_w2_c = 0;
 };
 
 struct az_net {
@@ -169,6 +191,11 @@ struct az_net {
     AzFrontArgs fa{};
     std::vector<AzBlockW> blk;
     float *lnf_g = nullptr, *lnf_b = nullptr, *w_pol = nullptr, *b_pol = nullptr, *w_val = nullptr, *b_val = nullptr;
+    // heads on tensor cores when 32 < A + 1 <= 64: [policy rows ; value row ; zero rows] as one [64][D] bf16 weight
+    bf16* w_head = nullptr;
+    float *b_head = nullptr, *head_out = nullptr;
+    CUtensorMap tm_whead;
+    bool head_gemm = false;
     // activations (one chunk)
     bf16 *x = nullptr, *xn = nullptr, *qkv = nullptr, *ao = nullptr, *hbuf = nullptr;
     bf16 *qc = nullptr, *oc = nullptr, *xc = nullptr, *xcn = nullptr, *hc = nullptr, *xc2 = nullptr;
@@ -559,6 +586,30 @@ extern "C" int az_net_finalize(az_net* n) {
         return rc;
     if (deep && ((rc = az_make_tmap(&n->tm_ao, n->ao, M, D, D, 128)) || (rc = az_make_tmap(&n->tm_hbuf, n->hbuf, M, 4 * D, 4 * D, 128))))
         return rc;
+    {   // cls-row GEMMs of the last block: M = boards of one chunk, tile width chosen for that M
+        AzBlockW& w = n->blk[n->L - 1];
+        w.bn_out_c = az_pick_bn_small_m(D, n->chunk);
+        w.bn_w1_c = az_pick_bn_small_m(4 * D, n->chunk);
+        w.bn_w2_c = az_pick_bn_small_m(D, n->chunk);
+        if ((rc = az_make_tmap(&w.tm_out_c, w.w_out, D, D, D, w.bn_out_c)) ||
+            (rc = az_make_tmap(&w.tm_w1_c, w.w1, 4 * D, D, D, w.bn_w1_c)) ||
+            (rc = az_make_tmap(&w.tm_w2_c, w.w2, D, 4 * D, 4 * D, w.bn_w2_c)))
+            return rc;
+    }
+    n->head_gemm = false;
+    if (A + 1 > 32 && A + 1 <= 64 && !getenv("AZ_NO_HEAD_GEMM")) {   // heads as one N = 64 tensor-core GEMM
+        std::vector<float> wh((size_t)64 * D, 0.f), bh(64, 0.f);
+        for (int o = 0; o < A; ++o) {
+            for (int d = 0; d < D; ++d) wh[(size_t)o * D + d] = (*wp)[(size_t)o * D + d];
+            bh[o] = (*bp)[o];
+        }
+        for (int d = 0; d < D; ++d) wh[(size_t)A * D + d] = (*wv)[d];
+        bh[A] = (*bv)[0];
+        if ((rc = az_upload_bf16(n, &n->w_head, wh.data(), wh.size())) || (rc = az_upload_f32(n, &n->b_head, bh)) ||
+            (rc = az_net_alloc(n, &n->head_out, B * 64)) || (rc = az_make_tmap(&n->tm_whead, n->w_head, 64, D, D, 64)))
+            return rc;
+        n->head_gemm = true;
+    }
     AZ_CUDA_OK(cudaDeviceSynchronize());
     n->finalized = true;
     return AZ_OK;
@@ -605,12 +656,46 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         AzProfScope ps(n, kind, s);
         return az_launch_gemm(ta, tb, ga, epi, mr, s);
     };
+    auto gemm_bn = [&](int kind, const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& ga, int epi, int mr, int bn) {
+        AzProfScope ps(n, kind, s);
+        return az_launch_gemm(ta, tb, ga, epi, mr, s, bn);
+    };
+    if (!g_num_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    // Net.norm + heads + softmax (ai/nn.py:78-83, ai/mcts.py:49) on the cls rows xc_final [cap][D]
     auto heads = [&](const bf16* xc_final) -> int {
         AzHeadArgs ha{};
         ha.batch = batch; ha.xc = xc_final; ha.D = D; ha.A = A; ha.ln_g = n->lnf_g; ha.ln_b = n->lnf_b;
         ha.w_pol = n->w_pol; ha.b_pol = n->b_pol; ha.w_val = n->w_val; ha.b_val = n->b_val;
         ha.priors = priors; ha.values = values; ha.logits = logits;
-        {
+        if (n->head_gemm) {                                    // LayerNorm -> [cap][D] x [64][D]^T on tensor cores -> softmax
+            layernorm(1, xc_final, D, n->xcn, D, n->lnf_g, n->lnf_b);
+            AzGemmArgs ga = az_gargs(batch, 1, n->b_head, nullptr, 0, n->xcn, 64, 64, D);
+            ga.out_f32 = n->head_out;
+            ga.f32_col0 = 0;
+            int rc2 = gemm_bn(AZ_K_HEAD, n->tm_xcn, n->tm_whead, ga, AZ_EPI_BIAS, cap, 64);
+            if (rc2) return rc2;
+            {
+                AzProfScope ps(n, AZ_K_HEAD, s);
+                az_head_softmax_kernel<<<(cap + 7) / 8, 256, 0, s>>>(batch, n->head_out, A, priors, values, logits);
+            }
+            AZ_CUDA_OK(cudaGetLastError());
+            n->launches += 2;
+            return AZ_OK;
+        }
+        if (A + 1 <= 32 && (size_t)(A + 1) * D * 4 <= 96 * 1024) {   // one warp per board, weights in shared memory
+            const size_t smem = (size_t)(A + 1) * D * sizeof(float);
+            const int grid = std::max(1, std::min((cap + 7) / 8, g_num_sms * 4));
+            AzProfScope ps(n, AZ_K_HEAD, s);
+            az_ln_dispatch(D, [&](auto nv) {
+                constexpr int NV = decltype(nv)::value;
+                if (smem > 48 * 1024) cudaFuncSetAttribute(az_head_warp_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                az_head_warp_kernel<NV><<<grid, 256, smem, s>>>(ha);
+            });
+        } else {
             AzProfScope ps(n, AZ_K_HEAD, s);
             az_head_kernel<<<cap, 128, (size_t)(D + A + 8) * sizeof(float), s>>>(ha);
         }
@@ -618,11 +703,6 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         ++n->launches;
         return AZ_OK;
     };
-    if (!g_num_sms) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    }
     if (n->front) {
         // embedding + LN1 + V/score projection + cls attention, all on chip (az_front.cuh)
         AzBlockW& w = n->blk[0];
@@ -650,10 +730,10 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         }
         AZ_CUDA_OK(cudaGetLastError());
         ++n->launches;
-        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out, az_gargs(batch, 1, n->b_out_x0, nullptr, 0, n->xc, D, D, D), AZ_EPI_BIAS, cap))) return rc;
+        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out_c, az_gargs(batch, 1, n->b_out_x0, nullptr, 0, n->xc, D, D, D), AZ_EPI_BIAS, cap, w.bn_out_c))) return rc;
         layernorm(1, n->xc, D, n->xcn, D, w.ln2_g, w.ln2_b);
-        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_xcn, w.tm_w1, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap))) return rc;
-        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap))) return rc;
+        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_xcn, w.tm_w1_c, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap, w.bn_w1_c))) return rc;
+        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2_c, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap, w.bn_w2_c))) return rc;
         n->launches += 3;
         return heads(n->xc2);
     }
@@ -735,10 +815,10 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         }
         AZ_CUDA_OK(cudaGetLastError());
         }
-        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out, az_gargs(batch, 1, w.b_out, n->x, T * D, n->xc, D, D, D), AZ_EPI_RESID, cap))) return rc;
+        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out_c, az_gargs(batch, 1, w.b_out, n->x, T * D, n->xc, D, D, D), AZ_EPI_RESID, cap, w.bn_out_c))) return rc;
         layernorm(1, n->xc, D, n->xcn, D, w.ln2_g, w.ln2_b);
-        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_xcn, w.tm_w1, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap))) return rc;
-        if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap))) return rc;
+        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_xcn, w.tm_w1_c, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap, w.bn_w1_c))) return rc;
+        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2_c, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap, w.bn_w2_c))) return rc;
         n->launches += 6;
     }
     return heads(n->xc2);

@@ -459,3 +459,78 @@ __global__ void __launch_bounds__(128) az_cls_attention_folded_kernel(AzBatch ba
         *reinterpret_cast<uint4*>(oc + (size_t)b * D + h * hd + c * 8) = az_pack8(o);
     }
 }
+
+// Final LayerNorm + heads + softmax, one WARP per board, head weights resident in shared memory
+// (policy rows then the value row, fp32).  For A + 1 <= 32 outputs (TicTacToe, Connect4): lane o keeps
+// output o.  Persistent: every warp strides over the boards of the batch.
+template <int NV>
+__global__ void __launch_bounds__(256) az_head_warp_kernel(AzHeadArgs a) {
+    extern __shared__ float sm_hw[];                          // [(A + 1)][D]
+    const int items = az_batch_items(a.batch);
+    const int D = a.D, A = a.A;
+    for (int i = threadIdx.x; i < (A + 1) * D; i += blockDim.x) sm_hw[i] = i < A * D ? a.w_pol[i] : a.w_val[i - A * D];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    const float my_bias = lane < A ? a.b_pol[lane] : (lane == A ? a.b_val[0] : 0.f);
+    for (int b = blockIdx.x * wpb + (threadIdx.x >> 5); b < items; b += gridDim.x * wpb) {
+        float x[NV][8];
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            const int d0 = (v * 32 + lane) * 8;
+            if (d0 < D) az_unpack8(*reinterpret_cast<const uint4*>(a.xc + (size_t)b * D + d0), x[v]);
+            else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) x[v][e] = 0.f;
+            }
+        }
+        az_row_layernorm<NV>(x, D, lane, a.ln_g, a.ln_b);
+        float mine = 0.f;
+        for (int o = 0; o <= A; ++o) {
+            const float* wr = sm_hw + (size_t)o * D;
+            float acc = 0.f;
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+                const int d0 = (v * 32 + lane) * 8;
+                if (d0 < D) {
+                    const float4 w0 = *reinterpret_cast<const float4*>(wr + d0), w1 = *reinterpret_cast<const float4*>(wr + d0 + 4);
+                    acc += x[v][0] * w0.x + x[v][1] * w0.y + x[v][2] * w0.z + x[v][3] * w0.w + x[v][4] * w1.x + x[v][5] * w1.y +
+                           x[v][6] * w1.z + x[v][7] * w1.w;
+                }
+            }
+            acc = az_warp_sum(acc);
+            if (lane == o) mine = acc;
+        }
+        mine += my_bias;
+        const float mx = az_warp_max(lane < A ? mine : -1e30f);
+        const float e = lane < A ? expf(mine - mx) : 0.f;
+        const float sum = az_warp_sum(e);
+        const size_t ob = (size_t)(a.batch.offset + b) * A;
+        if (lane < A) {
+            a.priors[ob + lane] = e / sum;
+            if (a.logits) a.logits[ob + lane] = mine;
+        } else if (lane == A) {
+            a.values[a.batch.offset + b] = tanhf(mine);
+        }
+    }
+}
+
+// Softmax / tanh over head outputs produced by the tensor-core head GEMM: ho [items][64] fp32 holds
+// A policy logits then the value pre-activation (A + 1 <= 64).  One warp per board.
+__global__ void __launch_bounds__(256) az_head_softmax_kernel(AzBatch batch, const float* __restrict__ ho, int A,
+                                                              float* priors, float* values, float* logits) {
+    const int items = az_batch_items(batch);
+    const int lane = threadIdx.x & 31;
+    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (b >= items) return;
+    const float l0 = ho[(size_t)b * 64 + lane], l1 = ho[(size_t)b * 64 + 32 + lane];
+    const bool p0 = lane < A, p1 = lane + 32 < A;
+    const float mx = az_warp_max(fmaxf(p0 ? l0 : -1e30f, p1 ? l1 : -1e30f));
+    const float e0 = p0 ? expf(l0 - mx) : 0.f, e1 = p1 ? expf(l1 - mx) : 0.f;
+    const float inv = 1.0f / az_warp_sum(e0 + e1);
+    const size_t ob = (size_t)(batch.offset + b) * A;
+    if (p0) { priors[ob + lane] = e0 * inv; if (logits) logits[ob + lane] = l0; }
+    if (p1) { priors[ob + lane + 32] = e1 * inv; if (logits) logits[ob + lane + 32] = l1; }
+    if (lane == A) values[batch.offset + b] = tanhf(l0);
+    if (lane + 32 == A) values[batch.offset + b] = tanhf(l1);
+}
