@@ -55,13 +55,14 @@ def save_data_to_buffer(Game, buffer, data):
                 buffer.add(*flip_data(b_rot, p_rot, "tb"), z)
 
 
-def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True):
-    """n_games concurrent self-play games; returns the reference's 5-tuple per game."""
+def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, return_visits=False):
+    """n_games concurrent self-play games; returns the reference's 5-tuple per game (and, on request,
+    the raw root visit counts per ply -- the compact form parallel.pack_games ships between ranks)."""
     boards = np.stack([Game().board for _ in range(n_games)])
     players = np.zeros(n_games, np.int32)
     plies = np.zeros(n_games, np.int32)
     alive = np.ones(n_games, np.uint8)
-    rec = [dict(boards=[], actions=[(-1, -1)], policies=[], qs=[], winner=-1) for _ in range(n_games)]
+    rec = [dict(boards=[], actions=[(-1, -1)], policies=[], qs=[], winner=-1, visits=[]) for _ in range(n_games)]
     sample_until = 8 if Game.name == "gomoku" else Game.state_dim + 1          # gomoku.py:143 / connect4.py:133
     A = Game.action_dim
     while alive.any():
@@ -71,6 +72,7 @@ def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True):
             pi = visits[g] / visits[g].sum()
             r = rec[g]
             r["policies"].append(pi)
+            r["visits"].append(visits[g].copy())
             r["boards"].append(boards[g].copy())
             r["qs"].append(q[g])
             legal = {Game.get_action_idx(m): m for m in Game.get_valid_moves(boards[g])}
@@ -87,7 +89,10 @@ def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True):
             if w != -1 or plies[g] == Game.state_dim:
                 r["winner"] = w
                 alive[g] = 0
-    return [(r["boards"], r["actions"], r["policies"], r["qs"], r["winner"]) for r in rec]
+    games = [(r["boards"], r["actions"], r["policies"], r["qs"], r["winner"]) for r in rec]
+    if return_visits:
+        return games, [np.stack(r["visits"]) for r in rec]
+    return games
 
 
 def collect_data(Game, model, buffer, iterations, mcts_iter, display=False, vl=1):
