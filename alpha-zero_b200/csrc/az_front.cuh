@@ -6,15 +6,15 @@
 //   token row       x_t  = Wemb^T a_t          a_t in {0,1}^K = [im2col taps | one-hot(t)]
 //   centred         x_t - mean(x_t) 1 = Wc^T a_t,   Wc = Wemb with every K-row centred over D
 //   LayerNorm 1     xn_t = r_t (x_t - mean) (.) gamma + beta,   r_t = rsqrt(a_t^T G a_t / D + eps),
-//                   G = Wc Wc^T  (K x K Gram matrix)
+//                   G = Wc Wc^T = L L^T  (K x K Gram matrix, Cholesky factor L):  a^T G a = |L^T a|^2
 //   V projection    v_t  = r_t (Wv' Wc^T) a_t + bv'        (gamma/beta folded into Wv', bv')
 //   cls scores      s_t,h = r_t (Ws Wc^T)_h a_t (+ const)  (constant cls query folded into Ws)
 //   attention       o_h = sum_t softmax_t(s_.,h) v_t,h
 // so per token only ONE contraction over K <= 128 binary inputs is needed.  Two tcgen05 MMAs per
 // tile of `nb` boards read the same bit-built operand tile A [tokens][K] (bf16 0/1, exact):
-//   stats : D1[token][j]   = A  x Wst^T   (M = 128 token rows, N = NS: 8 score columns + K Gram columns)
+//   stats : D1[token][j]   = A  x Wst^T   (M = 128 token rows, N = NS: 8 score columns + K columns of L^T a)
 //   values: D2[feature][t] = Wv2 x A^T    (M = 128 features per block, N = NTP token columns)
-// D1 has tokens on TMEM lanes (the masked Gram sum a^T G a is thread-local); D2 has FEATURES on
+// D1 has tokens on TMEM lanes (the sum of squares |L^T a|^2 is thread-local); D2 has FEATURES on
 // lanes, so the softmax-weighted sum over a board's tokens is thread-local as well.
 //   warps 0-7  epilogue (two groups)   warps 8-11  A-tile builders   warp 12  TMA (weights, once) + MMA issue
 #pragma once
@@ -31,7 +31,7 @@ struct AzFrontArgs {
     int nb;                       // boards per tile
     int TS;                       // token rows per board inside a tile (T rounded up to 8)
     int NTP;                      // token rows per tile = nb*TS rounded up to 16 (<= 128)
-    int NS;                       // stat columns: 8 + kc + T rounded up to 16 (<= 128)
+    int NS;                       // stat columns: 8 + kc + T rounded up to 32 (<= 128)
     int KB;                       // K blocks of 64 bf16 (1 or 2)
     int ksteps;                   // K = 16 MMA steps that carry non-zero columns
     int nslots;                   // TMEM accumulator slots for the value blocks
@@ -42,7 +42,7 @@ struct AzFrontArgs {
 static inline size_t az_front_smem(const AzFrontArgs& a) {
     const size_t tile = (size_t)a.NTP * 128;
     return 1024 + 2 * (size_t)a.KB * tile + (size_t)a.KB * a.NS * 128 + (size_t)a.KB * a.D * 128 +
-           2 * 128 * 16 + 8 * 128 * 4 + 2 * 128 * 4 + 128 + 256;
+           8 * 128 * 4 + 2 * 128 * 4 + 128 + 256;
 }
 
 namespace azptx {
@@ -73,14 +73,13 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
     unsigned char* s_a = smem;                                   // [2 stages][KB][NTP rows][128 B]
     unsigned char* s_wst = s_a + 2 * (size_t)KB * tile_bytes;    // [KB][NS rows][128 B]
     unsigned char* s_wv = s_wst + (size_t)KB * NS * 128;         // [FB][KB][128 rows][128 B]
-    uint4* s_mask = reinterpret_cast<uint4*>(s_wv + (size_t)FB * KB * 16384);   // [2][128] row bit masks (K bits)
-    float* s_w = reinterpret_cast<float*>(s_mask + 2 * 128);     // [8 heads][128 rows] scores, then softmax weight * r
+    float* s_w = reinterpret_cast<float*>(s_wv + (size_t)FB * KB * 16384);   // [8 heads][128 rows] scores, then softmax weight * r
     float* s_q = s_w + 8 * 128;                                  // [2][128] partial Gram sums of the two groups
     uint2* s_lut = reinterpret_cast<uint2*>(s_q + 2 * 128);      // 16 entries: nibble -> 4 bf16 (0 / 1.0)
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_lut + 16);
     uint64_t* w_full = bars;            // 1
     uint64_t* a_full = bars + 1;        // 2   (128 builder arrivals)
-    uint64_t* a_empty = bars + 3;       // 2   (MMA commit + epilogue "masks consumed")
+    uint64_t* a_empty = bars + 3;       // 2   (MMA commit: every MMA reading the stage is done)
     uint64_t* st_full = bars + 5;       // 1
     uint64_t* st_empty = bars + 6;      // 1   (256 epilogue arrivals)
     uint64_t* v_full = bars + 7;        // 4
@@ -103,7 +102,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         azptx::mbar_init(w_full, 1);
         for (int i = 0; i < 2; ++i) {
             azptx::mbar_init(&a_full[i], 128);
-            azptx::mbar_init(&a_empty[i], 2);
+            azptx::mbar_init(&a_empty[i], 1);
         }
         azptx::mbar_init(st_full, 1);
         azptx::mbar_init(st_empty, 256);
@@ -223,9 +222,6 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                     }
                 }
             }
-            // Gram columns sit behind the 8 score columns: shift the row mask to column numbering
-            const unsigned __int128 ks = km << 8;
-            s_mask[st * 128 + r] = make_uint4((uint32_t)ks, (uint32_t)(ks >> 32), (uint32_t)(ks >> 64), (uint32_t)(ks >> 96));
             azptx::fence_proxy_async();                              // generic-proxy writes -> visible to the MMA
             azptx::mbar_arrive(&a_full[st]);
         }
@@ -242,13 +238,13 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         const bool pair_on = pair < pairs;
         const int pb = pair_on ? pair / H : 0, ph = pair_on ? pair - pb * H : 0;
         const float inv_d = 1.0f / (float)D;
+        const int ne = (TS + tpp - 1) / tpp;                         // tokens per softmax thread (<= 8, checked on the host)
         int it = 0, slot0 = 0, round0 = 0;                           // block counter at fb = 0 of the current tile
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it & 1;
-            // ---- Gram sum a^T G a (this group's half of the columns) and raw scores
+            // ---- |L^T a|^2 = a^T G a (this group's half of the columns) and raw scores
             azptx::mbar_wait(st_full, it & 1);
             azptx::tc_fence_after();
-            const uint4 mk = s_mask[st * 128 + tid];
             float q0 = 0.f, q1 = 0.f;
 #pragma unroll
             for (int cc = 0; cc < 2; ++cc) {
@@ -259,13 +255,15 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                     azptx::tmem_ld_wait();
                     if (c == 0) {
 #pragma unroll
-                        for (int h = 0; h < 8; ++h) s_w[h * 128 + tid] = __uint_as_float(v[h]);
+                        for (int h = 0; h < 8; ++h) {
+                            s_w[h * 128 + tid] = __uint_as_float(v[h]);
+                            v[h] = 0u;                               // score columns are not part of the sum of squares
+                        }
                     }
-                    const uint32_t m = c == 0 ? mk.x : (c == 1 ? mk.y : (c == 2 ? mk.z : mk.w));
 #pragma unroll
                     for (int i = 0; i < 32; i += 2) {
-                        q0 += ((m >> i) & 1u) ? __uint_as_float(v[i]) : 0.f;
-                        q1 += ((m >> (i + 1)) & 1u) ? __uint_as_float(v[i + 1]) : 0.f;
+                        q0 = fmaf(__uint_as_float(v[i]), __uint_as_float(v[i]), q0);
+                        q1 = fmaf(__uint_as_float(v[i + 1]), __uint_as_float(v[i + 1]), q1);
                     }
                 }
             }
@@ -273,29 +271,40 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
             azptx::mbar_arrive(st_empty);
             s_q[grp * 128 + tid] = q0 + q1;
             azptx::bar_sync_named(1, 256);
-            if (threadIdx.x == 0) azptx::mbar_arrive(&a_empty[st]);  // row masks of this stage consumed
-            // ---- softmax over the T tokens of each (board, head); weight = p * rstd
+            // ---- softmax over the T tokens of each (board, head); weight = p * rstd.  Thread `sub` of the
+            //      pair's group owns tokens sub, sub + tpp, ... (at most 8), kept in registers.
             {
                 float* sw = s_w + ph * 128 + pb * TS;
                 const float* sq = s_q + pb * TS;
+                float sc[8], rs[8];
                 float mx = -1e30f;
-                for (int t = sub; t < T; t += tpp) {
-                    const float rstd = rsqrtf(fmaxf(sq[t] + sq[128 + t], 0.f) * inv_d + 1e-5f);
-                    const float sc = sw[t] * rstd;
-                    if (pair_on) sw[t] = sc;
-                    mx = fmaxf(mx, sc);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int t = sub + i * tpp;
+                    sc[i] = -1e30f;
+                    rs[i] = 0.f;
+                    if (i < ne && t < T) {
+                        rs[i] = rsqrtf((sq[t] + sq[128 + t]) * inv_d + 1e-5f);
+                        sc[i] = sw[t] * rs[i];
+                    }
+                    mx = fmaxf(mx, sc[i]);
                 }
                 for (int o = tpp >> 1; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
                 float sum = 0.f;
-                for (int t = sub; t < T; t += tpp) sum += __expf(sw[t] - mx);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    sc[i] = (i < ne && sub + i * tpp < T) ? __expf(sc[i] - mx) : 0.f;
+                    sum += sc[i];
+                }
                 for (int o = tpp >> 1; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
                 const float inv = 1.0f / sum;
-                if (pair_on)
-                    for (int t = sub; t < TS; t += tpp) {
-                        float wgt = 0.f;
-                        if (t < T) wgt = __expf(sw[t] - mx) * inv * rsqrtf(fmaxf(sq[t] + sq[128 + t], 0.f) * inv_d + 1e-5f);
-                        sw[t] = wgt;
+                if (pair_on) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int t = sub + i * tpp;
+                        if (i < ne && t < TS) sw[t] = sc[i] * inv * rs[i];   // pad rows (t >= T) get weight 0
                     }
+                }
             }
             azptx::bar_sync_named(1, 256);
             // ---- value blocks: o[f] = sum_t w[h(f)][t] * z[f][t] + bias, features on TMEM lanes
@@ -309,26 +318,37 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                     const float bias = __ldg(a.bias_v + f);
                     const uint32_t tcol = tq + 128 + slot * NTP;
                     bf16* dst = a.oc + (size_t)tile * a.nb * D + f;
-                    for (int b = 0; b < a.nb; ++b) {
-                        uint32_t v[TS8][8];
+                    constexpr int NBV = TS8 >= 5 ? 1 : (8 / TS8 > 4 ? 4 : 8 / TS8);   // boards fetched per TMEM round trip
+                    for (int b0 = 0; b0 < a.nb; b0 += NBV) {
+                        uint32_t v[NBV][TS8][8];
 #pragma unroll
-                        for (int j = 0; j < TS8; ++j) azptx::tmem_ld8(tcol + b * TS + j * 8, v[j]);
+                        for (int bi = 0; bi < NBV; ++bi)
+                            if (b0 + bi < a.nb) {
+#pragma unroll
+                                for (int j = 0; j < TS8; ++j) azptx::tmem_ld8(tcol + (b0 + bi) * TS + j * 8, v[bi][j]);
+                            }
                         azptx::tmem_ld_wait();
-                        if (b == a.nb - 1) {                         // slot fully read: hand it back to the MMA warp
+                        if (b0 + NBV >= a.nb) {                      // slot fully read: hand it back to the MMA warp
                             azptx::tc_fence_before();
                             azptx::mbar_arrive(&v_empty[slot]);
                         }
-                        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
-                        for (int j = 0; j < TS8; ++j) {
-                            const float4 w0 = *reinterpret_cast<const float4*>(wrow + b * TS + j * 8);
-                            const float4 w1 = *reinterpret_cast<const float4*>(wrow + b * TS + j * 8 + 4);
-                            a0 += w0.x * __uint_as_float(v[j][0]) + w1.x * __uint_as_float(v[j][4]);
-                            a1 += w0.y * __uint_as_float(v[j][1]) + w1.y * __uint_as_float(v[j][5]);
-                            a2 += w0.z * __uint_as_float(v[j][2]) + w1.z * __uint_as_float(v[j][6]);
-                            a3 += w0.w * __uint_as_float(v[j][3]) + w1.w * __uint_as_float(v[j][7]);
+                        for (int bi = 0; bi < NBV; ++bi) {
+                            const int b = b0 + bi;
+                            if (b < a.nb) {
+                                float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+                                for (int j = 0; j < TS8; ++j) {
+                                    const float4 w0 = *reinterpret_cast<const float4*>(wrow + b * TS + j * 8);
+                                    const float4 w1 = *reinterpret_cast<const float4*>(wrow + b * TS + j * 8 + 4);
+                                    a0 += w0.x * __uint_as_float(v[bi][j][0]) + w1.x * __uint_as_float(v[bi][j][4]);
+                                    a1 += w0.y * __uint_as_float(v[bi][j][1]) + w1.y * __uint_as_float(v[bi][j][5]);
+                                    a2 += w0.z * __uint_as_float(v[bi][j][2]) + w1.z * __uint_as_float(v[bi][j][6]);
+                                    a3 += w0.w * __uint_as_float(v[bi][j][3]) + w1.w * __uint_as_float(v[bi][j][7]);
+                                }
+                                if (tile * a.nb + b < items) dst[(size_t)b * D] = __float2bfloat16((a0 + a1) + (a2 + a3) + bias);
+                            }
                         }
-                        if (tile * a.nb + b < items) dst[(size_t)b * D] = __float2bfloat16((a0 + a1) + (a2 + a3) + bias);
                     }
                 }
                 if (++slot == nslots) { slot = 0; ++round; }

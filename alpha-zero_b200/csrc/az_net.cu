@@ -504,7 +504,7 @@ extern "C" int az_net_finalize(az_net* n) {
                         for (int k = 0; k < D; ++k) ws[(size_t)h * D + k] += qq * wk[k];
                     }
             }
-            const int NS = (8 + kused + 15) / 16 * 16;
+            const int NS = (8 + kused + 31) / 32 * 32;
             std::vector<float> wst((size_t)NS * kpad, 0.f), wv2((size_t)D * kpad, 0.f), bv(D), box(D);
             for (int h = 0; h < H; ++h)                                  // rows 0..7: scores
                 for (int k = 0; k < kused; ++k) {
@@ -512,13 +512,33 @@ extern "C" int az_net_finalize(az_net* n) {
                     for (int d = 0; d < D; ++d) acc += ws[(size_t)h * D + d] * wc[(size_t)k * D + d];
                     wst[(size_t)h * kpad + k] = (float)acc;
                 }
-            for (int i = 0; i < kused; ++i)                              // rows 8..: Gram matrix of the centred rows
-                for (int k = 0; k <= i; ++k) {
-                    double acc = 0;
-                    for (int d = 0; d < D; ++d) acc += wc[(size_t)i * D + d] * wc[(size_t)k * D + d];
-                    wst[(size_t)(8 + i) * kpad + k] = (float)acc;
-                    wst[(size_t)(8 + k) * kpad + i] = (float)acc;
+            {   // rows 8..: L^T, with G = Wc Wc^T = L L^T (Cholesky; a vanishing pivot leaves a zero column,
+                // which is exact for a positive semi-definite G), so that |L^T a|^2 = a^T G a >= 0
+                std::vector<double> G((size_t)kused * kused), L((size_t)kused * kused, 0.0);
+                double trace = 0;
+                for (int i = 0; i < kused; ++i)
+                    for (int k = 0; k <= i; ++k) {
+                        double acc = 0;
+                        for (int d = 0; d < D; ++d) acc += wc[(size_t)i * D + d] * wc[(size_t)k * D + d];
+                        G[(size_t)i * kused + k] = G[(size_t)k * kused + i] = acc;
+                        if (i == k) trace += acc;
+                    }
+                const double tol = 1e-12 * (trace > 0 ? trace : 1.0);
+                for (int j = 0; j < kused; ++j) {
+                    double dj = G[(size_t)j * kused + j];
+                    for (int k = 0; k < j; ++k) dj -= L[(size_t)j * kused + k] * L[(size_t)j * kused + k];
+                    if (dj <= tol) continue;
+                    const double ljj = sqrt(dj);
+                    L[(size_t)j * kused + j] = ljj;
+                    for (int i = j + 1; i < kused; ++i) {
+                        double v = G[(size_t)i * kused + j];
+                        for (int k = 0; k < j; ++k) v -= L[(size_t)i * kused + k] * L[(size_t)j * kused + k];
+                        L[(size_t)i * kused + j] = v / ljj;
+                    }
                 }
+                for (int j = 0; j < kused; ++j)                          // output column 8 + j = sum_k L[k][j] a_k
+                    for (int k = j; k < kused; ++k) wst[(size_t)(8 + j) * kpad + k] = (float)L[(size_t)k * kused + j];
+            }
             for (int f = 0; f < D; ++f) {                                // V rows with the embedding folded in
                 const float* wr = &wi[(size_t)(2 * D + f) * D];
                 for (int k = 0; k < kused; ++k) {
@@ -547,7 +567,9 @@ extern "C" int az_net_finalize(az_net* n) {
             fa.ksteps = (kused + 15) / 16;
             fa.nslots = std::min(std::min(4, D / 128), 384 / fa.NTP);
             fa.bias_v = n->f_bias_v;
-            n->front = fa.nb >= 1 && fa.nslots >= 1 && az_front_smem(fa) <= 227 * 1024;
+            int tpp = 32;
+            while (tpp * fa.nb * H > 256) tpp >>= 1;
+            n->front = fa.nb >= 1 && fa.nslots >= 1 && tpp >= 1 && (fa.TS + tpp - 1) / tpp <= 8 && az_front_smem(fa) <= 227 * 1024;
         }
     }
     // ---- heads
