@@ -16,7 +16,7 @@
 //   values: D2[feature][t] = Wv2 x A^T    (M = 128 features per block, N = NTP token columns)
 // D1 has tokens on TMEM lanes (the sum of squares |L^T a|^2 is thread-local); D2 has FEATURES on
 // lanes, so the softmax-weighted sum over a board's tokens is thread-local as well.
-//   warps 0-7  epilogue (two groups)   warps 8-11  A-tile builders   warp 12  TMA (weights, once) + MMA issue
+//   warps 0-3 statistic + softmax | warps 4-11 value epilogue | warps 12-14 A-tile builders | warp 15 TMA + MMA issue
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -42,7 +42,7 @@ struct AzFrontArgs {
 static inline size_t az_front_smem(const AzFrontArgs& a) {
     const size_t tile = (size_t)a.NTP * 128;
     return 1024 + 2 * (size_t)a.KB * tile + (size_t)a.KB * a.NS * 128 + (size_t)a.KB * a.D * 128 +
-           8 * 128 * 4 + 2 * 128 * 4 + 128 + 256;
+           2 * 8 * 128 * 4 + 2 * 128 * 4 + 128 + 256;
 }
 
 namespace azptx {
@@ -56,9 +56,23 @@ __device__ __forceinline__ void bar_sync_named(int id, int nthreads) {
 }
 }  // namespace azptx
 
-// Threads: warps 0-3 epilogue group 0, warps 4-7 epilogue group 1 (same TMEM lane quarters, the two
-// groups split the stat columns and the value blocks), warps 8-11 A-tile builders, warp 12 TMA + MMA.
-#define AZ_FRONT_THREADS 416
+#ifdef AZ_FRONT_TRACE
+__device__ unsigned long long g_front_trace[4][64][8];   // [role: mma, builder, S, V][tile iteration][event]
+#define AZ_TR(role, ev) do { if (blockIdx.x == 0 && it < 64 && (threadIdx.x & 127) == 0) g_front_trace[role][it][ev] = clock64(); } while (0)
+#define AZ_TR1(role, ev) do { if (blockIdx.x == 0 && it < 64 && lane == 0) g_front_trace[role][it][ev] = clock64(); } while (0)
+#else
+#define AZ_TR(role, ev)
+#define AZ_TR1(role, ev)
+#endif
+
+// Threads (16 warps):
+//   warps 0-3    S group: per-row statistic + scores from the stats accumulator, softmax -> weights in smem
+//   warps 4-11   V group: two warps per TMEM lane quarter, each owning every other value block
+//   warps 12-14  A-tile builders (96 threads, token rows r and r + 96)
+//   warp  15     TMA (weights, once) + MMA issue
+// The S group works on tile i + 1 while the V group consumes the weights of tile i (double-buffered).
+#define AZ_FRONT_THREADS 512
+#define AZ_FRONT_BUILDERS 96
 
 template <int TS8>
 __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __grid_constant__ CUtensorMap tm_wst,
@@ -73,18 +87,20 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
     unsigned char* s_a = smem;                                   // [2 stages][KB][NTP rows][128 B]
     unsigned char* s_wst = s_a + 2 * (size_t)KB * tile_bytes;    // [KB][NS rows][128 B]
     unsigned char* s_wv = s_wst + (size_t)KB * NS * 128;         // [FB][KB][128 rows][128 B]
-    float* s_w = reinterpret_cast<float*>(s_wv + (size_t)FB * KB * 16384);   // [8 heads][128 rows] scores, then softmax weight * r
-    float* s_q = s_w + 8 * 128;                                  // [2][128] partial Gram sums of the two groups
+    float* s_w = reinterpret_cast<float*>(s_wv + (size_t)FB * KB * 16384);   // [2][8 heads][128 rows] scores -> softmax weight * r
+    float* s_q = s_w + 2 * 8 * 128;                              // [2][128] sum of squares per row
     uint2* s_lut = reinterpret_cast<uint2*>(s_q + 2 * 128);      // 16 entries: nibble -> 4 bf16 (0 / 1.0)
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_lut + 16);
     uint64_t* w_full = bars;            // 1
-    uint64_t* a_full = bars + 1;        // 2   (128 builder arrivals)
+    uint64_t* a_full = bars + 1;        // 2   (96 builder arrivals)
     uint64_t* a_empty = bars + 3;       // 2   (MMA commit: every MMA reading the stage is done)
     uint64_t* st_full = bars + 5;       // 1
-    uint64_t* st_empty = bars + 6;      // 1   (256 epilogue arrivals)
+    uint64_t* st_empty = bars + 6;      // 1   (128 S-group arrivals)
     uint64_t* v_full = bars + 7;        // 4
-    uint64_t* v_empty = bars + 11;      // 4   (128 arrivals of the group that owns the block)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+    uint64_t* v_empty = bars + 11;      // 4   (128 arrivals of the V sub-group that owns the block)
+    uint64_t* sw_full = bars + 15;      // 2   (128 S-group arrivals: weights of a tile are in s_w[buf])
+    uint64_t* sw_empty = bars + 17;     // 2   (256 V-group arrivals: s_w[buf] may be overwritten)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int items = az_batch_items(a.batch);
@@ -96,16 +112,18 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         s_lut[n] = make_uint2(((n & 1u) ? 0x00003F80u : 0u) | ((n & 2u) ? 0x3F800000u : 0u),
                               ((n & 4u) ? 0x00003F80u : 0u) | ((n & 8u) ? 0x3F800000u : 0u));
     }
-    if (warp == 12 && lane == 0) {
+    if (warp == 15 && lane == 0) {
         azptx::prefetch_tmap(&tm_wst);
         azptx::prefetch_tmap(&tm_wv);
         azptx::mbar_init(w_full, 1);
         for (int i = 0; i < 2; ++i) {
-            azptx::mbar_init(&a_full[i], 128);
+            azptx::mbar_init(&a_full[i], AZ_FRONT_BUILDERS);
             azptx::mbar_init(&a_empty[i], 1);
+            azptx::mbar_init(&sw_full[i], 128);
+            azptx::mbar_init(&sw_empty[i], 256);
         }
         azptx::mbar_init(st_full, 1);
-        azptx::mbar_init(st_empty, 256);
+        azptx::mbar_init(st_empty, 128);
         for (int i = 0; i < 4; ++i) {
             azptx::mbar_init(&v_full[i], 1);
             azptx::mbar_init(&v_empty[i], 128);
@@ -119,7 +137,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
     const uint32_t tmem_base = *tmem_slot;
     // TMEM columns: [0, 128) stats accumulator, value slots of NTP columns from 128 on.
 
-    if (warp == 12) {
+    if (warp == 15) {
         // ------------------------------ weights in once, then MMA issue -----------------------------
         if (lane == 0) {
             azptx::mbar_arrive_expect_tx(w_full, (uint32_t)(KB * NS * 128 + FB * KB * 16384));
@@ -131,70 +149,96 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         azptx::mbar_wait(w_full, 0);
         const uint32_t idesc_st = azptx::umma_idesc_bf16(128, (uint32_t)NS);
         const uint32_t idesc_v = azptx::umma_idesc_bf16(128, (uint32_t)NTP);
+        // The issuing thread is the pacemaker of the tensor pipe: every descriptor is formed once, outside
+        // the tile loop, and the K steps are fully unrolled -- nothing but tcgen05.mma in the hot sequence.
+        uint64_t d_wst[2], d_a[2][2], d_wv[4][2];
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+            const int kbe = kb < KB ? kb : 0;
+            d_wst[kb] = azptx::umma_desc_k128(azptx::smem_u32(s_wst + (size_t)kbe * NS * 128));
+#pragma unroll
+            for (int st = 0; st < 2; ++st)
+                d_a[st][kb] = azptx::umma_desc_k128(azptx::smem_u32(s_a + (size_t)st * KB * tile_bytes + (size_t)kbe * tile_bytes));
+#pragma unroll
+            for (int fb = 0; fb < 4; ++fb)
+                d_wv[fb][kb] = azptx::umma_desc_k128(azptx::smem_u32(s_wv + ((size_t)(fb < FB ? fb : 0) * KB + kbe) * 16384));
+        }
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {                             // keep the descriptors opaque 64-bit register values
+            asm volatile("" : "+l"(d_wst[kb]));
+            asm volatile("" : "+l"(d_a[0][kb]));
+            asm volatile("" : "+l"(d_a[1][kb]));
+#pragma unroll
+            for (int fb = 0; fb < 4; ++fb) asm volatile("" : "+l"(d_wv[fb][kb]));
+        }
         int it = 0, slot = 0, round = 0;                           // value-block counter g = round * nslots + slot
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it & 1;
-            const unsigned char* at = s_a + (size_t)st * KB * tile_bytes;
+            AZ_TR1(0, 0);
             azptx::mbar_wait(&a_full[st], (it >> 1) & 1);
+            AZ_TR1(0, 1);
             azptx::mbar_wait(st_empty, (it & 1) ^ 1);
+            AZ_TR1(0, 2);
             azptx::tc_fence_after();
+            const uint64_t da0 = st ? d_a[1][0] : d_a[0][0], da1 = st ? d_a[1][1] : d_a[0][1];
             if (lane == 0) {
-                for (int ks = 0; ks < a.ksteps; ++ks) {
-                    const int kb = ks >> 2, k = ks & 3;
-                    const uint64_t da = azptx::umma_desc_k128(azptx::smem_u32(at + (size_t)kb * tile_bytes));
-                    const uint64_t db = azptx::umma_desc_k128(azptx::smem_u32(s_wst + (size_t)kb * NS * 128));
-                    azptx::umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc_st, ks != 0);
+                // every K step is issued (columns beyond the used K are zero in both operands): no per-MMA predicate
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks)
+                    azptx::umma_bf16(tmem_base, da0 + 2 * ks, d_wst[0] + 2 * ks, idesc_st, ks != 0);
+                if (KB == 2) {
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) azptx::umma_bf16(tmem_base, da1 + 2 * ks, d_wst[1] + 2 * ks, idesc_st, 1);
                 }
                 azptx::umma_commit(st_full);
             }
             __syncwarp();
-            for (int fb = 0; fb < FB; ++fb) {
-                azptx::mbar_wait(&v_empty[slot], (round & 1) ^ 1);
-                azptx::tc_fence_after();
-                if (lane == 0) {
-                    for (int ks = 0; ks < a.ksteps; ++ks) {
-                        const int kb = ks >> 2, k = ks & 3;
-                        const uint64_t da = azptx::umma_desc_k128(azptx::smem_u32(s_wv + ((size_t)fb * KB + kb) * 16384));
-                        const uint64_t db = azptx::umma_desc_k128(azptx::smem_u32(at + (size_t)kb * tile_bytes));
-                        azptx::umma_bf16(tmem_base + 128 + slot * NTP, da + 2 * k, db + 2 * k, idesc_v, ks != 0);
+#pragma unroll
+            for (int fb = 0; fb < 4; ++fb) {
+                if (fb < FB) {
+                    azptx::mbar_wait(&v_empty[slot], (round & 1) ^ 1);
+                    if (fb == 0) AZ_TR1(0, 3);
+                    if (fb == FB - 1) AZ_TR1(0, 4);
+                    azptx::tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t dcol = tmem_base + 128 + slot * NTP;
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) azptx::umma_bf16(dcol, d_wv[fb][0] + 2 * ks, da0 + 2 * ks, idesc_v, ks != 0);
+                        if (KB == 2) {
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks) azptx::umma_bf16(dcol, d_wv[fb][1] + 2 * ks, da1 + 2 * ks, idesc_v, 1);
+                        }
+                        azptx::umma_commit(&v_full[slot]);
+                        if (fb == FB - 1) azptx::umma_commit(&a_empty[st]);   // every MMA reading this A stage is done
                     }
-                    azptx::umma_commit(&v_full[slot]);
-                    if (fb == FB - 1) azptx::umma_commit(&a_empty[st]);   // every MMA reading this A stage is done
+                    __syncwarp();
+                    if (++slot == nslots) { slot = 0; ++round; }
                 }
-                __syncwarp();
-                if (++slot == nslots) { slot = 0; ++round; }
             }
         }
-    } else if (warp >= 8) {
-        // ------------------------------ A-tile builders: one thread per token row -------------------
-        const int r = threadIdx.x - 256;
-        const int b_in_tile = r / TS, t = r - b_in_tile * TS;
-        const bool row_used = b_in_tile < a.nb && t < T;
-        int cr = 0, cc = 0;
-        if (row_used && t > 0) { cr = (t - 1) / a.cols; cc = (t - 1) - cr * a.cols; }
+    } else if (warp >= 12) {
+        // ------------------------------ A-tile builders: token rows bt and bt + 96 ---------------------
+        const int bt = threadIdx.x - 384;
         const int half = P >> 1, pp = P * P;
         const uint32_t colmask = (1u << a.cols) - 1u, pmask = (1u << P) - 1u;
-        // the window geometry of this row does not depend on the board: fold it into constants
-        const int rshift = cc >= half ? cc - half : 0, lshift = cc >= half ? 0 : half - cc;
-        uint32_t inb = 0;                                            // in-bounds taps (plane 2 is all ones)
-        for (int kr = 0; kr < P; ++kr) {
-            const int rr = cr + kr - half;
-            if (rr >= 0 && rr < a.rows) inb |= (((colmask >> rshift) << lshift) & pmask) << (kr * P);
-        }
-        const unsigned __int128 onehot = (unsigned __int128)1 << (a.kc + t);
-        unsigned char* const arow0 = s_a + (size_t)r * 128;
-        const int sw = r & 7;
         int it = 0;
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it & 1;
-            const int item = tile * a.nb + b_in_tile;
-            const bool live = row_used && item < items;
-            unsigned __int128 km = 0;
-            if (live) {
+            unsigned __int128 kms[2] = {0, 0};
+#pragma unroll
+            for (int pass = 0; pass < 2; ++pass) {
+                const int r = bt + pass * AZ_FRONT_BUILDERS;
+                if (r >= NTP) continue;
+                const int b_in_tile = r / TS, t = r - b_in_tile * TS;
+                const int item = tile * a.nb + b_in_tile;
+                if (!(b_in_tile < a.nb && t < T && item < items)) continue;
+                unsigned __int128 km = (unsigned __int128)1 << (a.kc + t);     // one-hot token index -> pos-emb / bias row
                 if (t > 0) {
+                    const int cr = (t - 1) / a.cols, cc = (t - 1) - cr * a.cols;
+                    const int rshift = cc >= half ? cc - half : 0, lshift = cc >= half ? 0 : half - cc;
                     const ulonglong2 w = *reinterpret_cast<const ulonglong2*>(a.leaf_words + (size_t)(a.batch.offset + item) * 2);
                     const bool stm = a.planes == 3 && a.leaf_player[a.batch.offset + item] != 0;
-                    uint32_t p0 = 0, p1 = 0;                         // taps of planes 0 / 1, bit kr*P + kcol  (P*P <= 32)
+                    uint32_t p0 = 0, p1 = 0, p2 = 0;                 // taps of planes 0 / 1 / 2, bit kr*P + kcol  (P*P <= 32)
 #pragma unroll 5
                     for (int kr = 0; kr < P; ++kr) {
                         const int rr = cr + kr - half;
@@ -203,17 +247,24 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                         const uint32_t b0 = (uint32_t)(w.x >> sh) & colmask, b1 = (uint32_t)(w.y >> sh) & colmask;
                         p0 |= (((b0 >> rshift) << lshift) & pmask) << (kr * P);
                         p1 |= (((b1 >> rshift) << lshift) & pmask) << (kr * P);
+                        p2 |= (((colmask >> rshift) << lshift) & pmask) << (kr * P);   // plane 2 is all ones inside the board
                     }
-                    km = (unsigned __int128)p0 | ((unsigned __int128)p1 << pp);
-                    if (stm) km |= (unsigned __int128)inb << (2 * pp);
+                    km |= (unsigned __int128)p0 | ((unsigned __int128)p1 << pp);
+                    if (stm) km |= (unsigned __int128)p2 << (2 * pp);
                 }
-                km |= onehot;                                        // one-hot token index -> pos-emb / bias row
+                kms[pass] = km;
             }
+            AZ_TR(1, 0);
             azptx::mbar_wait(&a_empty[st], ((it >> 1) & 1) ^ 1);
-            if (r < NTP) {
-                unsigned char* arow = arow0 + (size_t)st * KB * tile_bytes;
+            AZ_TR(1, 1);
+#pragma unroll
+            for (int pass = 0; pass < 2; ++pass) {
+                const int r = bt + pass * AZ_FRONT_BUILDERS;
+                if (r >= NTP) continue;
+                unsigned char* arow = s_a + (size_t)st * KB * tile_bytes + (size_t)r * 128;
+                const int sw = r & 7;
                 for (int kb = 0; kb < KB; ++kb) {
-                    const uint64_t kw = kb == 0 ? (uint64_t)km : (uint64_t)(km >> 64);
+                    const uint64_t kw = kb == 0 ? (uint64_t)kms[pass] : (uint64_t)(kms[pass] >> 64);
 #pragma unroll
                     for (int c = 0; c < 8; ++c) {
                         const uint32_t by = (uint32_t)(kw >> (c * 8)) & 0xFFu;
@@ -224,31 +275,36 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
             }
             azptx::fence_proxy_async();                              // generic-proxy writes -> visible to the MMA
             azptx::mbar_arrive(&a_full[st]);
+            AZ_TR(1, 2);
         }
-    } else {
-        // ------------------------------ epilogue (two groups of 128 threads) ------------------------
-        const int grp = warp >> 2;
-        const int tid = threadIdx.x & 127;                           // token row (stats) / feature in block (values)
-        const uint32_t tq = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
-        const int H = a.H, hd = D / H;
+    } else if (warp < 4) {
+        // ------------------------------ S group: statistic, scores, softmax ----------------------------
+        const int tid = threadIdx.x;                                 // token row
+        const uint32_t tq = tmem_base + ((uint32_t)(warp * 32) << 16);
+        const int H = a.H;
         const int pairs = a.nb * H;
         int tpp = 32;
-        while (tpp * pairs > 256) tpp >>= 1;                         // threads per (board, head) softmax
-        const int pair = (int)threadIdx.x / tpp, sub = (int)threadIdx.x - pair * tpp;
+        while (tpp * pairs > 128) tpp >>= 1;                         // threads per (board, head) softmax
+        const int pair = tid / tpp, sub = tid - pair * tpp;
         const bool pair_on = pair < pairs;
         const int pb = pair_on ? pair / H : 0, ph = pair_on ? pair - pb * H : 0;
         const float inv_d = 1.0f / (float)D;
         const int ne = (TS + tpp - 1) / tpp;                         // tokens per softmax thread (<= 8, checked on the host)
-        int it = 0, slot0 = 0, round0 = 0;                           // block counter at fb = 0 of the current tile
+        int it = 0;
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
-            const int st = it & 1;
-            // ---- |L^T a|^2 = a^T G a (this group's half of the columns) and raw scores
+            const int buf = it & 1;
+            float* swb = s_w + buf * 8 * 128;
+            float* sqb = s_q + buf * 128;
+            AZ_TR(2, 0);
+            azptx::mbar_wait(&sw_empty[buf], ((it >> 1) & 1) ^ 1);    // V group finished with this buffer
+            AZ_TR(2, 1);
+            // ---- |L^T a|^2 = a^T G a and raw scores from the stats accumulator
             azptx::mbar_wait(st_full, it & 1);
+            AZ_TR(2, 2);
             azptx::tc_fence_after();
             float q0 = 0.f, q1 = 0.f;
 #pragma unroll
-            for (int cc = 0; cc < 2; ++cc) {
-                const int c = grp * 2 + cc;
+            for (int c = 0; c < 4; ++c) {
                 if (c * 32 < NS) {
                     uint32_t v[32];
                     azptx::tmem_ld32(tq + c * 32, v);
@@ -256,7 +312,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                     if (c == 0) {
 #pragma unroll
                         for (int h = 0; h < 8; ++h) {
-                            s_w[h * 128 + tid] = __uint_as_float(v[h]);
+                            swb[h * 128 + tid] = __uint_as_float(v[h]);
                             v[h] = 0u;                               // score columns are not part of the sum of squares
                         }
                     }
@@ -269,13 +325,14 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
             }
             azptx::tc_fence_before();
             azptx::mbar_arrive(st_empty);
-            s_q[grp * 128 + tid] = q0 + q1;
-            azptx::bar_sync_named(1, 256);
-            // ---- softmax over the T tokens of each (board, head); weight = p * rstd.  Thread `sub` of the
-            //      pair's group owns tokens sub, sub + tpp, ... (at most 8), kept in registers.
+            sqb[tid] = q0 + q1;
+            AZ_TR(2, 3);
+            azptx::bar_sync_named(1, 128);
+            AZ_TR(2, 4);
+            // ---- softmax over the T tokens of each (board, head); weight = p * rstd
             {
-                float* sw = s_w + ph * 128 + pb * TS;
-                const float* sq = s_q + pb * TS;
+                float* sw = swb + ph * 128 + pb * TS;
+                const float* sq = sqb + pb * TS;
                 float sc[8], rs[8];
                 float mx = -1e30f;
 #pragma unroll
@@ -284,7 +341,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                     sc[i] = -1e30f;
                     rs[i] = 0.f;
                     if (i < ne && t < T) {
-                        rs[i] = rsqrtf((sq[t] + sq[128 + t]) * inv_d + 1e-5f);
+                        rs[i] = rsqrtf(sq[t] * inv_d + 1e-5f);
                         sc[i] = sw[t] * rs[i];
                     }
                     mx = fmaxf(mx, sc[i]);
@@ -306,15 +363,31 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                     }
                 }
             }
-            azptx::bar_sync_named(1, 256);
-            // ---- value blocks: o[f] = sum_t w[h(f)][t] * z[f][t] + bias, features on TMEM lanes
+            azptx::mbar_arrive(&sw_full[buf]);                       // release: this thread's weights are written
+            AZ_TR(2, 5);
+        }
+    } else {
+        // ------------------------------ V group: softmax-weighted sums of the value blocks -------------
+        const int vw = warp - 4;                                     // 0..7
+        const int grp = vw >> 2;                                     // owns blocks fb with (fb & 1) == grp
+        const int tid = (vw & 3) * 32 + lane;                        // feature inside a block = TMEM lane
+        const uint32_t tq = tmem_base + ((uint32_t)((vw & 3) * 32) << 16);
+        const int hd = D / a.H;
+        int it = 0, slot0 = 0, round0 = 0;                           // block counter at fb = 0 of the current tile
+        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+            const int buf = it & 1;
+            const float* swb = s_w + buf * 8 * 128;
+            AZ_TR(3, 0);
+            azptx::mbar_wait(&sw_full[buf], (it >> 1) & 1);
+            AZ_TR(3, 1);
             int slot = slot0, round = round0;
             for (int fb = 0; fb < FB; ++fb) {
                 if ((fb & 1) == grp) {
                     azptx::mbar_wait(&v_full[slot], round & 1);
+                    if (fb < 2) AZ_TR(3, 2); else AZ_TR(3, 4);
                     azptx::tc_fence_after();
                     const int f = fb * 128 + tid;
-                    const float* wrow = s_w + (f / hd) * 128;
+                    const float* wrow = swb + (f / hd) * 128;
                     const float bias = __ldg(a.bias_v + f);
                     const uint32_t tcol = tq + 128 + slot * NTP;
                     bf16* dst = a.oc + (size_t)tile * a.nb * D + f;
@@ -354,7 +427,8 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                 if (++slot == nslots) { slot = 0; ++round; }
             }
             slot0 = slot; round0 = round;
-            azptx::bar_sync_named(1, 256);                           // s_w / s_q are rewritten by the next tile
+            azptx::mbar_arrive(&sw_empty[buf]);                      // this thread no longer reads s_w[buf]
+            AZ_TR(3, 5);
         }
     }
     azptx::tc_fence_before();

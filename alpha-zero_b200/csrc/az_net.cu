@@ -560,7 +560,7 @@ extern "C" int az_net_finalize(az_net* n) {
             fa = AzFrontArgs{};
             fa.rows = n->rows; fa.cols = n->cols; fa.planes = C; fa.patch = P; fa.T = T; fa.kc = kc; fa.D = D; fa.H = H;
             fa.TS = (T + 7) / 8 * 8;
-            fa.nb = std::min(128 / fa.TS, 256 / H);
+            fa.nb = std::min(128 / fa.TS, 128 / H);
             fa.NTP = (fa.nb * fa.TS + 15) / 16 * 16;
             fa.NS = NS;
             fa.KB = KB;
@@ -568,7 +568,7 @@ extern "C" int az_net_finalize(az_net* n) {
             fa.nslots = std::min(std::min(4, D / 128), 384 / fa.NTP);
             fa.bias_v = n->f_bias_v;
             int tpp = 32;
-            while (tpp * fa.nb * H > 256) tpp >>= 1;
+            while (tpp * fa.nb * H > 128) tpp >>= 1;
             n->front = fa.nb >= 1 && fa.nslots >= 1 && tpp >= 1 && (fa.TS + tpp - 1) / tpp <= 8 && az_front_smem(fa) <= 227 * 1024;
         }
     }
@@ -1017,3 +1017,9 @@ extern "C" int az_net_profile_read(az_net* n, int max_kinds, const char** names_
     }
     return k;
 }
+
+#ifdef AZ_FRONT_TRACE
+extern "C" __attribute__((visibility("default"))) int az_debug_front_trace(unsigned long long* out_host) {
+    return (int)cudaMemcpyFromSymbol(out_host, g_front_trace, sizeof(g_front_trace));
+}
+#endif
