@@ -72,7 +72,7 @@ __device__ __forceinline__ void az_group_argmax(unsigned gmask, T& best, int& id
 #define AZ_LP 8
 
 template <int NW, int G>
-__global__ void __launch_bounds__(128) az_advance_kernel(AzForestDev f, int smem_per_group) {
+__global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int smem_per_group) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x % G;
     const int grp = threadIdx.x / G;

@@ -68,11 +68,12 @@ __device__ unsigned long long g_front_trace[4][64][8];   // [role: mma, builder,
 // Threads (16 warps):
 //   warps 0-3    S group: per-row statistic + scores from the stats accumulator, softmax -> weights in smem
 //   warps 4-11   V group: two warps per TMEM lane quarter, each owning every other value block
-//   warps 12-14  A-tile builders (96 threads, token rows r and r + 96)
-//   warp  15     TMA (weights, once) + MMA issue
+//   warps 12-13  A-tile builders (64 threads, token rows r and r + 64; next tile's boards prefetched)
+//   warp  15     TMA (weights, once) + MMA issue: stats and the even value blocks
+//   warp  14     MMA issue: the odd value blocks (one thread cannot issue tcgen05.mma fast enough alone)
 // The S group works on tile i + 1 while the V group consumes the weights of tile i (double-buffered).
 #define AZ_FRONT_THREADS 512
-#define AZ_FRONT_BUILDERS 96
+#define AZ_FRONT_BUILDERS 64
 
 template <int TS8>
 __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __grid_constant__ CUtensorMap tm_wst,
@@ -92,8 +93,8 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
     uint2* s_lut = reinterpret_cast<uint2*>(s_q + 2 * 128);      // 16 entries: nibble -> 4 bf16 (0 / 1.0)
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_lut + 16);
     uint64_t* w_full = bars;            // 1
-    uint64_t* a_full = bars + 1;        // 2   (96 builder arrivals)
-    uint64_t* a_empty = bars + 3;       // 2   (MMA commit: every MMA reading the stage is done)
+    uint64_t* a_full = bars + 1;        // 2   (64 builder arrivals)
+    uint64_t* a_empty = bars + 3;       // 2   (one commit per MMA warp: every MMA reading the stage is done)
     uint64_t* st_full = bars + 5;       // 1
     uint64_t* st_empty = bars + 6;      // 1   (128 S-group arrivals)
     uint64_t* v_full = bars + 7;        // 4
@@ -118,7 +119,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         azptx::mbar_init(w_full, 1);
         for (int i = 0; i < 2; ++i) {
             azptx::mbar_init(&a_full[i], AZ_FRONT_BUILDERS);
-            azptx::mbar_init(&a_empty[i], 1);
+            azptx::mbar_init(&a_empty[i], 2);
             azptx::mbar_init(&sw_full[i], 128);
             azptx::mbar_init(&sw_empty[i], 256);
         }
@@ -137,9 +138,10 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
     const uint32_t tmem_base = *tmem_slot;
     // TMEM columns: [0, 128) stats accumulator, value slots of NTP columns from 128 on.
 
-    if (warp == 15) {
-        // ------------------------------ weights in once, then MMA issue -----------------------------
-        if (lane == 0) {
+    if (warp >= 14) {
+        // ------------------------------ weights in once (warp 15), then MMA issue -----------------------
+        const bool lead = warp == 15;                                // stats + even value blocks; warp 14: odd value blocks
+        if (lead && lane == 0) {
             azptx::mbar_arrive_expect_tx(w_full, (uint32_t)(KB * NS * 128 + FB * KB * 16384));
             for (int kb = 0; kb < KB; ++kb) azptx::tma_load_2d(s_wst + (size_t)kb * NS * 128, &tm_wst, w_full, kb * 64, 0);
             for (int fb = 0; fb < FB; ++fb)
@@ -150,7 +152,8 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         const uint32_t idesc_st = azptx::umma_idesc_bf16(128, (uint32_t)NS);
         const uint32_t idesc_v = azptx::umma_idesc_bf16(128, (uint32_t)NTP);
         // The issuing thread is the pacemaker of the tensor pipe: every descriptor is formed once, outside
-        // the tile loop, and the K steps are fully unrolled -- nothing but tcgen05.mma in the hot sequence.
+        // the tile loop, and the K steps are fully unrolled and unpredicated (columns beyond the used K are
+        // zero in both operands) -- nothing but tcgen05.mma in the hot sequence.
         uint64_t d_wst[2], d_a[2][2], d_wv[4][2];
 #pragma unroll
         for (int kb = 0; kb < 2; ++kb) {
@@ -163,94 +166,145 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
             for (int fb = 0; fb < 4; ++fb)
                 d_wv[fb][kb] = azptx::umma_desc_k128(azptx::smem_u32(s_wv + ((size_t)(fb < FB ? fb : 0) * KB + kbe) * 16384));
         }
-#pragma unroll
-        for (int kb = 0; kb < 2; ++kb) {                             // keep the descriptors opaque 64-bit register values
-            asm volatile("" : "+l"(d_wst[kb]));
-            asm volatile("" : "+l"(d_a[0][kb]));
-            asm volatile("" : "+l"(d_a[1][kb]));
-#pragma unroll
-            for (int fb = 0; fb < 4; ++fb) asm volatile("" : "+l"(d_wv[fb][kb]));
-        }
+        const int mine = lead ? 0 : 1;                               // parity of the value blocks this warp issues
         int it = 0, slot = 0, round = 0;                           // value-block counter g = round * nslots + slot
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it & 1;
             AZ_TR1(0, 0);
             azptx::mbar_wait(&a_full[st], (it >> 1) & 1);
             AZ_TR1(0, 1);
-            azptx::mbar_wait(st_empty, (it & 1) ^ 1);
-            AZ_TR1(0, 2);
-            azptx::tc_fence_after();
             const uint64_t da0 = st ? d_a[1][0] : d_a[0][0], da1 = st ? d_a[1][1] : d_a[0][1];
-            if (lane == 0) {
-                // every K step is issued (columns beyond the used K are zero in both operands): no per-MMA predicate
+            if (lead) {
+                azptx::mbar_wait(st_empty, (it & 1) ^ 1);
+                AZ_TR1(0, 2);
+                azptx::tc_fence_after();
+                if (azptx::elect_one()) {
 #pragma unroll
-                for (int ks = 0; ks < 4; ++ks)
-                    azptx::umma_bf16(tmem_base, da0 + 2 * ks, d_wst[0] + 2 * ks, idesc_st, ks != 0);
-                if (KB == 2) {
+                    for (int ks = 0; ks < 4; ++ks)
+                        azptx::umma_bf16(tmem_base, da0 + 2 * ks, d_wst[0] + 2 * ks, idesc_st, ks != 0);
+                    if (KB == 2) {
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) azptx::umma_bf16(tmem_base, da1 + 2 * ks, d_wst[1] + 2 * ks, idesc_st, 1);
+                        for (int ks = 0; ks < 4; ++ks) azptx::umma_bf16(tmem_base, da1 + 2 * ks, d_wst[1] + 2 * ks, idesc_st, 1);
+                    }
+                    azptx::umma_commit(st_full);
                 }
-                azptx::umma_commit(st_full);
+                __syncwarp();
             }
-            __syncwarp();
 #pragma unroll
             for (int fb = 0; fb < 4; ++fb) {
                 if (fb < FB) {
-                    azptx::mbar_wait(&v_empty[slot], (round & 1) ^ 1);
-                    if (fb == 0) AZ_TR1(0, 3);
-                    if (fb == FB - 1) AZ_TR1(0, 4);
-                    azptx::tc_fence_after();
-                    if (lane == 0) {
-                        const uint32_t dcol = tmem_base + 128 + slot * NTP;
+                    if ((fb & 1) == mine) {
+                        azptx::mbar_wait(&v_empty[slot], (round & 1) ^ 1);
+                        if (fb == 0) AZ_TR1(0, 3);
+                        if (fb == 2) AZ_TR1(0, 4);
+                        azptx::tc_fence_after();
+                        if (azptx::elect_one()) {
+                            const uint32_t dcol = tmem_base + 128 + slot * NTP;
 #pragma unroll
-                        for (int ks = 0; ks < 4; ++ks) azptx::umma_bf16(dcol, d_wv[fb][0] + 2 * ks, da0 + 2 * ks, idesc_v, ks != 0);
-                        if (KB == 2) {
+                            for (int ks = 0; ks < 4; ++ks) azptx::umma_bf16(dcol, d_wv[fb][0] + 2 * ks, da0 + 2 * ks, idesc_v, ks != 0);
+                            if (KB == 2) {
 #pragma unroll
-                            for (int ks = 0; ks < 4; ++ks) azptx::umma_bf16(dcol, d_wv[fb][1] + 2 * ks, da1 + 2 * ks, idesc_v, 1);
+                                for (int ks = 0; ks < 4; ++ks) azptx::umma_bf16(dcol, d_wv[fb][1] + 2 * ks, da1 + 2 * ks, idesc_v, 1);
+                            }
+                            azptx::umma_commit(&v_full[slot]);
                         }
-                        azptx::umma_commit(&v_full[slot]);
-                        if (fb == FB - 1) azptx::umma_commit(&a_empty[st]);   // every MMA reading this A stage is done
+                        __syncwarp();
                     }
-                    __syncwarp();
                     if (++slot == nslots) { slot = 0; ++round; }
                 }
             }
+            if (azptx::elect_one()) azptx::umma_commit(&a_empty[st]);    // this warp's MMAs on the A stage are done
+            __syncwarp();
+            AZ_TR1(0, 5);
         }
     } else if (warp >= 12) {
-        // ------------------------------ A-tile builders: token rows bt and bt + 96 ---------------------
+        // ------------------------------ A-tile builders: token rows bt and bt + 64 ---------------------
         const int bt = threadIdx.x - 384;
         const int half = P >> 1, pp = P * P;
         const uint32_t colmask = (1u << a.cols) - 1u, pmask = (1u << P) - 1u;
+        // geometry of this thread's (at most two) rows does not depend on the board: hoisted out of the tile loop
+        int r_b[2], r_t[2], r_rs[2], r_ls[2], r_cr[2];
+        uint32_t r_inb[2];
+        bool r_on[2];
+#pragma unroll
+        for (int pass = 0; pass < 2; ++pass) {
+            const int r = bt + pass * AZ_FRONT_BUILDERS;
+            const int bb = r / TS, t = r - bb * TS;
+            r_b[pass] = bb;
+            r_t[pass] = t;
+            r_on[pass] = r < NTP && bb < a.nb && t < T;
+            int cr = 0, cc = 0;
+            if (t > 0) { cr = (t - 1) / a.cols; cc = (t - 1) - cr * a.cols; }
+            r_cr[pass] = cr;
+            r_rs[pass] = cc >= half ? cc - half : 0;
+            r_ls[pass] = cc >= half ? 0 : half - cc;
+            uint32_t inb = 0;                                        // in-bounds taps of the window (plane 2 is all ones)
+            for (int kr = 0; kr < P; ++kr) {
+                const int rr = cr + kr - half;
+                if (rr >= 0 && rr < a.rows) inb |= (((colmask >> r_rs[pass]) << r_ls[pass]) & pmask) << (kr * P);
+            }
+            r_inb[pass] = inb;
+        }
+        // boards of the tile (side bitboards + side to move), fetched one tile ahead
+        ulonglong2 w_cur[2], w_nxt[2];
+        uint32_t s_cur[2], s_nxt[2];
+        auto fetch = [&](int tile, ulonglong2 (&w)[2], uint32_t (&sm)[2]) {
+#pragma unroll
+            for (int pass = 0; pass < 2; ++pass) {
+                const int item = tile * a.nb + r_b[pass];
+                w[pass] = make_ulonglong2(0ull, 0ull);
+                sm[pass] = 2u;                                       // 2 = row unused / board beyond the batch
+                if (tile < tiles && r_on[pass] && item < items) {
+                    w[pass] = *reinterpret_cast<const ulonglong2*>(a.leaf_words + (size_t)(a.batch.offset + item) * 2);
+                    sm[pass] = (a.planes == 3 && a.leaf_player[a.batch.offset + item] != 0) ? 1u : 0u;
+                }
+            }
+        };
+        fetch(blockIdx.x, w_cur, s_cur);
+        // The one-hot columns of a row never change and pad rows stay zero: both stages are initialised once;
+        // per tile only the chunks (8 K columns = 16 bytes) that hold tap columns are rewritten.
+        const int nch = (a.kc + 7) >> 3;
+#pragma unroll
+        for (int pass = 0; pass < 2; ++pass) {
+            const int r = bt + pass * AZ_FRONT_BUILDERS;
+            if (r >= NTP) continue;
+            const unsigned __int128 km = r_on[pass] ? (unsigned __int128)1 << (a.kc + r_t[pass]) : (unsigned __int128)0;
+            for (int st = 0; st < 2; ++st)
+                for (int kb = 0; kb < KB; ++kb) {
+                    const uint64_t kw = kb == 0 ? (uint64_t)km : (uint64_t)(km >> 64);
+                    unsigned char* arow = s_a + (size_t)st * KB * tile_bytes + (size_t)kb * tile_bytes + (size_t)r * 128;
+                    for (int c = 0; c < 8; ++c) {
+                        const uint32_t by = (uint32_t)(kw >> (c * 8)) & 0xFFu;
+                        const uint2 lo = s_lut[by & 15u], hi = s_lut[by >> 4];
+                        *reinterpret_cast<uint4*>(arow + ((c ^ (r & 7)) << 4)) = make_uint4(lo.x, lo.y, hi.x, hi.y);
+                    }
+                }
+        }
         int it = 0;
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it & 1;
-            unsigned __int128 kms[2] = {0, 0};
+            fetch(tile + gridDim.x, w_nxt, s_nxt);                   // in flight while this tile is encoded
+            unsigned __int128 kms[2];
 #pragma unroll
             for (int pass = 0; pass < 2; ++pass) {
-                const int r = bt + pass * AZ_FRONT_BUILDERS;
-                if (r >= NTP) continue;
-                const int b_in_tile = r / TS, t = r - b_in_tile * TS;
-                const int item = tile * a.nb + b_in_tile;
-                if (!(b_in_tile < a.nb && t < T && item < items)) continue;
-                unsigned __int128 km = (unsigned __int128)1 << (a.kc + t);     // one-hot token index -> pos-emb / bias row
-                if (t > 0) {
-                    const int cr = (t - 1) / a.cols, cc = (t - 1) - cr * a.cols;
-                    const int rshift = cc >= half ? cc - half : 0, lshift = cc >= half ? 0 : half - cc;
-                    const ulonglong2 w = *reinterpret_cast<const ulonglong2*>(a.leaf_words + (size_t)(a.batch.offset + item) * 2);
-                    const bool stm = a.planes == 3 && a.leaf_player[a.batch.offset + item] != 0;
-                    uint32_t p0 = 0, p1 = 0, p2 = 0;                 // taps of planes 0 / 1 / 2, bit kr*P + kcol  (P*P <= 32)
+                unsigned __int128 km = 0;
+                if (r_on[pass]) {
+                    const int t = r_t[pass];
+                    km = (unsigned __int128)1 << (a.kc + t);         // one-hot token index -> pos-emb / bias row
+                    if (t > 0 && s_cur[pass] != 2u) {                // (boards beyond the batch keep an empty window)
+                        uint32_t p0 = 0, p1 = 0;                     // taps of planes 0 / 1, bit kr*P + kcol  (P*P <= 32)
 #pragma unroll 5
-                    for (int kr = 0; kr < P; ++kr) {
-                        const int rr = cr + kr - half;
-                        if (rr < 0 || rr >= a.rows) continue;
-                        const int sh = rr * a.cols;
-                        const uint32_t b0 = (uint32_t)(w.x >> sh) & colmask, b1 = (uint32_t)(w.y >> sh) & colmask;
-                        p0 |= (((b0 >> rshift) << lshift) & pmask) << (kr * P);
-                        p1 |= (((b1 >> rshift) << lshift) & pmask) << (kr * P);
-                        p2 |= (((colmask >> rshift) << lshift) & pmask) << (kr * P);   // plane 2 is all ones inside the board
+                        for (int kr = 0; kr < P; ++kr) {
+                            const int rr = r_cr[pass] + kr - half;
+                            if (rr < 0 || rr >= a.rows) continue;
+                            const int sh = rr * a.cols;
+                            const uint32_t b0 = (uint32_t)(w_cur[pass].x >> sh) & colmask, b1 = (uint32_t)(w_cur[pass].y >> sh) & colmask;
+                            p0 |= (((b0 >> r_rs[pass]) << r_ls[pass]) & pmask) << (kr * P);
+                            p1 |= (((b1 >> r_rs[pass]) << r_ls[pass]) & pmask) << (kr * P);
+                        }
+                        km |= (unsigned __int128)p0 | ((unsigned __int128)p1 << pp);
+                        if (s_cur[pass] == 1u) km |= (unsigned __int128)r_inb[pass] << (2 * pp);
                     }
-                    km |= (unsigned __int128)p0 | ((unsigned __int128)p1 << pp);
-                    if (stm) km |= (unsigned __int128)p2 << (2 * pp);
                 }
                 kms[pass] = km;
             }
@@ -260,22 +314,22 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
 #pragma unroll
             for (int pass = 0; pass < 2; ++pass) {
                 const int r = bt + pass * AZ_FRONT_BUILDERS;
-                if (r >= NTP) continue;
+                if (r >= NTP || !r_on[pass] || r_t[pass] == 0) continue;     // pad rows and the cls row never change
                 unsigned char* arow = s_a + (size_t)st * KB * tile_bytes + (size_t)r * 128;
                 const int sw = r & 7;
-                for (int kb = 0; kb < KB; ++kb) {
+                for (int gc = 0; gc < nch; ++gc) {
+                    const int kb = gc >> 3, c = gc & 7;
                     const uint64_t kw = kb == 0 ? (uint64_t)kms[pass] : (uint64_t)(kms[pass] >> 64);
-#pragma unroll
-                    for (int c = 0; c < 8; ++c) {
-                        const uint32_t by = (uint32_t)(kw >> (c * 8)) & 0xFFu;
-                        const uint2 lo = s_lut[by & 15u], hi = s_lut[by >> 4];
-                        *reinterpret_cast<uint4*>(arow + (size_t)kb * tile_bytes + ((c ^ sw) << 4)) = make_uint4(lo.x, lo.y, hi.x, hi.y);
-                    }
+                    const uint32_t by = (uint32_t)(kw >> (c * 8)) & 0xFFu;
+                    const uint2 lo = s_lut[by & 15u], hi = s_lut[by >> 4];
+                    *reinterpret_cast<uint4*>(arow + (size_t)kb * tile_bytes + ((c ^ sw) << 4)) = make_uint4(lo.x, lo.y, hi.x, hi.y);
                 }
             }
             azptx::fence_proxy_async();                              // generic-proxy writes -> visible to the MMA
             azptx::mbar_arrive(&a_full[st]);
             AZ_TR(1, 2);
+#pragma unroll
+            for (int pass = 0; pass < 2; ++pass) { w_cur[pass] = w_nxt[pass]; s_cur[pass] = s_nxt[pass]; }
         }
     } else if (warp < 4) {
         // ------------------------------ S group: statistic, scores, softmax ----------------------------
