@@ -37,7 +37,25 @@ __device__ __forceinline__ float az_puct32(float q, float P, int n, float s) {
 __device__ __forceinline__ float az_q32(double W, int n) { return __double2float_rn(__ddiv_rn(W, (double)n)); }
 
 // node.py:69-72 for one node of the path: visit += 1; value += v; (+ refresh the cached quotient)
-__device__ __forceinline__ void az_backup_node(AzHot* hot, double* wsum, uint32_t nd, double v, bool release_vl) {
+// Views of the node array that keep the kernel text in terms of hot / meta / W.
+struct AzHotView {
+    AzNode* p;
+    __device__ __forceinline__ AzHot& operator[](size_t i) const { return p[i].hot; }
+};
+struct AzMetaView {
+    AzNode* p;
+    __device__ __forceinline__ AzMeta& operator[](size_t i) const { return p[i].meta; }
+};
+struct AzMeta64View {
+    AzNode* p;
+    __device__ __forceinline__ unsigned long long operator[](size_t i) const { return *reinterpret_cast<const unsigned long long*>(&p[i].meta); }
+};
+struct AzWView {
+    AzNode* p;
+    __device__ __forceinline__ double& operator[](size_t i) const { return p[i].W; }
+};
+
+__device__ __forceinline__ void az_backup_node(AzHotView hot, AzWView wsum, uint32_t nd, double v, bool release_vl) {
     AzHot h = hot[nd];
     const double W = __dadd_rn(wsum[nd], v);
     h.N += 1;
@@ -54,31 +72,63 @@ __device__ __forceinline__ double az_puct64(double W, double P, int n, double s)
     return __dadd_rn(__ddiv_rn(W, (double)n), u);
 }
 
-template <int G, typename T>
-__device__ __forceinline__ void az_group_argmax(unsigned gmask, T& best, int& idx) {
-#pragma unroll
-    for (int off = G / 2; off > 0; off >>= 1) {
-        const T o = __shfl_xor_sync(gmask, best, off, G);
-        const int oi = __shfl_xor_sync(gmask, idx, off, G);
-        if (o > best || (o == best && oi < idx)) {           // first maximum in child order
-            best = o;
-            idx = oi;
-        }
-    }
+// First maximum in child order over the lanes of a group with the warp-reduce unit (redux.sync):
+// scores become order-preserving unsigned keys (+0.0 canonicalises -0.0; a lane never holds NaN
+// because `sc > best` is false for NaN), the winner is the smallest child index among the lanes
+// that hold the maximum key.  2 (fp32) / 3 (fp64) reductions instead of 5 shuffle rounds.
+__device__ __forceinline__ unsigned az_ord32(float f) {
+    const unsigned u = __float_as_uint(f + 0.0f);
+    return u ^ ((unsigned)((int)u >> 31) | 0x80000000u);
+}
+__device__ __forceinline__ unsigned long long az_ord64(double d) {
+    const unsigned long long u = (unsigned long long)__double_as_longlong(d + 0.0);
+    return u ^ ((unsigned long long)((long long)u >> 63) | 0x8000000000000000ull);
+}
+__device__ __forceinline__ int az_group_argmax(unsigned gmask, float best, int idx) {
+    const unsigned k = az_ord32(best);
+    const unsigned m = __reduce_max_sync(gmask, k);
+    return (int)__reduce_min_sync(gmask, k == m ? (unsigned)idx : 0x7fffffffu);
+}
+__device__ __forceinline__ int az_group_argmax(unsigned gmask, double best, int idx) {
+    const unsigned long long k = az_ord64(best);
+    const unsigned hi = (unsigned)(k >> 32), lo = (unsigned)k;
+    const unsigned mh = __reduce_max_sync(gmask, hi);
+    const unsigned ml = __reduce_max_sync(gmask, hi == mh ? lo : 0u);
+    return (int)__reduce_min_sync(gmask, (hi == mh && lo == ml) ? (unsigned)idx : 0x7fffffffu);
 }
 
 // Expansion of up to AZ_LP pending leaves of a tree runs in parallel (one lane per leaf generates
 // that leaf's legal moves -- for Gomoku the sequential CPython-set emulation -- into its own scratch).
 #define AZ_LP 8
 
+#ifdef AZ_ADV_TRACE
+// Per-tree phase clocks, accumulated over launches (tools/adv_trace.py): [tree][16]
+__device__ unsigned long long g_adv_trace[8192][16];
+__device__ unsigned int g_adv_hist[66];      // warp lifetimes of the launches since the last read: 64 buckets of 32k cycles, [64] = max, [65] = first-to-last clock span / 64
+#define AZ_AT(k)                                                                    \
+    do {                                                                            \
+        const long long t__ = clock64();                                            \
+        if (lane == 0 && tree < 8192) g_adv_trace[tree][k] += (unsigned long long)(t__ - at_prev); \
+        at_prev = t__;                                                              \
+    } while (0)
+#define AZ_AT_COUNT(k, n) do { if (lane == 0 && tree < 8192) g_adv_trace[tree][k] += (n); } while (0)
+#else
+#define AZ_AT(k) do {} while (0)
+#define AZ_AT_COUNT(k, n) do {} while (0)
+#endif
+
 template <int NW, int G>
-__global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int smem_per_group) {
+__global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int smem_per_group) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x % G;
     const int grp = threadIdx.x / G;
     const int tree = blockIdx.x * (blockDim.x / G) + grp;
     const unsigned gmask = az_group_mask<G>();
     if (tree >= f.n_trees) return;
+#ifdef AZ_ADV_TRACE
+    long long at_prev = clock64();
+    const long long at_t0 = at_prev;
+#endif
     // independent loads first, decisions after: one memory round trip
     const uint8_t is_active = f.active[tree], is_done = f.done_flag[tree];
     int n_nodes = f.n_nodes[tree];
@@ -93,6 +143,8 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
         rootb.w[1][w] = f.root_words[(size_t)tree * 2 * NW + NW + w];
     }
     if (!is_active || is_done) return;
+    AZ_AT(0);                                                 // tree scalars + root words
+    AZ_AT_COUNT(15, 1);
 
     const AzGame& g = f.g;
     unsigned char* sm = smem_raw + (size_t)grp * smem_per_group;
@@ -101,10 +153,11 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
     const int lm_bytes = moves_pad + 2 * g.set_slots;           // legal-move scratch of one pending leaf
     uint8_t* s_lm = sm + 4 * f.max_depth;
 
-    AzHot* hot = f.hot + (size_t)tree * f.cap;
-    AzMeta* meta = f.meta + (size_t)tree * f.cap;
-    const unsigned long long* meta64 = reinterpret_cast<const unsigned long long*>(meta);
-    double* wsum = f.wsum + (size_t)tree * f.cap;
+    AzNode* const nodes = f.nodes + (size_t)tree * f.cap;
+    const AzHotView hot{nodes};
+    const AzMetaView meta{nodes};
+    const AzMeta64View meta64{nodes};
+    const AzWView wsum{nodes};
     const bool use_vl = f.vl > 1;
     const int A = g.action_dim;
     const int LP = f.lp;
@@ -134,6 +187,7 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
             my_nc = az_legal_moves<NW>(g, b, f.cell_hash, lm + moves_pad, lm + moves_pad + g.set_slots, lm);
         }
         __syncwarp(gmask);                                    // move lists visible to the group
+        AZ_AT(1);                                             // pending scalars + legal moves
         for (int j = 0; j < nj; ++j) {                        // in selection order: node numbering and f64 sums depend on it
             const size_t pj = (size_t)tree * f.vl + j0 + j;
             const int nc = __shfl_sync(gmask, my_nc, j, G);
@@ -180,10 +234,12 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
                 m.status = AZ_ST_EXPANDED;
                 meta[leaf] = m;
             }
+            AZ_AT(2);                                             // child block written
             const double result = -(double)val;                   // mcts.py:56
             for (int i = lane; i < len; i += G)                   // node.py:69-72
                 az_backup_node(hot, wsum, gpath[i], ((len - 1 - i) & 1) ? -result : result, use_vl);
             __syncwarp(gmask);
+            AZ_AT(3);                                             // backup
             ++st_exp;
             st_child += nc;
             ++st_sims;
@@ -194,12 +250,37 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
     // ---------------- phase B: descend until `vl` leaves are pending -----------------------
     int started = sims;
     int np = 0;
-    // A tree whose best line ends in a terminal node burns simulation after simulation without
-    // ever needing the evaluator; left unbounded, one such tree (up to `iters` descents) sets the
-    // duration of the whole launch.  While nothing is pending the launch may stop after a few of
-    // them -- the next launch resumes the very same sequence, so results do not change.
-    const unsigned kMaxTerminalPerLaunch = f.vl == 1 ? 1u : 4u;   // vl == 1: exactly one descent per launch
-    while (started < f.iters && np < f.vl && !(np == 0 && st_term >= kMaxTerminalPerLaunch)) {
+    // A tree whose best line ends in a terminal node burns simulation after simulation without ever
+    // needing the evaluator; left unbounded, one such tree (up to `iters` descents) sets the duration
+    // of the whole launch (measured: one tree 15x the 99th percentile).  The step machine therefore
+    // closes a step after `vl` terminal descents as well.  At vl == 1 nothing is pending when that
+    // happens, the next launch resumes the very same sequence and the reference's order is kept;
+    // at vl > 1 it is part of the build-defined batching rule (oracle: az_oracle.c azo_search).
+    const unsigned kMaxTerminalPerLaunch = (unsigned)f.vl;
+    AzBoard<NW> kept = rootb;
+    int kept_player = 0, flushed = 0;
+    auto hand_off = [&](int upto) {                           // evaluation slots of pending leaves [flushed, upto)
+        const int cnt = upto - flushed;
+        if (cnt <= 0) return;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(f.n_leaves, cnt);
+        base = __shfl_sync(gmask, base, 0, G);
+        if (lane < cnt) {
+            const int slot = base + lane;
+            const size_t pk = (size_t)tree * f.vl + flushed + lane;
+            f.leaf_slot[pk] = slot;
+            f.leaf_player[slot] = (uint8_t)kept_player;
+            f.leaf_tree[slot] = tree;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                f.pend_words[pk * 2 * NW + w] = kept.w[0][w];
+                f.pend_words[pk * 2 * NW + NW + w] = kept.w[1][w];
+                f.leaf_words[(size_t)slot * 2 * NW + w] = kept_player ? kept.w[1][w] : kept.w[0][w];        // canonical: mine
+                f.leaf_words[(size_t)slot * 2 * NW + NW + w] = kept_player ? kept.w[0][w] : kept.w[1][w];   // theirs
+            }
+        }
+    };
+    while (started < f.iters && np < f.vl && st_term < kMaxTerminalPerLaunch) {
         AzBoard<NW> b = rootb;
         int player = root_player, mc = root_mc, len = 1;
         uint32_t node = 0;
@@ -210,6 +291,7 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
             const AzHot hr = hot[0];
             pn = hr.N + (int)hr.V;
         }
+        AZ_AT(4);                                             // root record
         // One memory round trip per level: every lane fetches hot AND meta of its children, the
         // winner's meta / visit count arrive by shuffle (mcts.py:20-23, node.py:42-47).
         while (m.status == AZ_ST_EXPANDED) {
@@ -222,20 +304,22 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
                 double best = -1.0 / 0.0;
                 for (int c = lane; c < nc; c += G) {
                     const AzHot h = hot[cb + c];
-                    const unsigned long long mm = meta64[cb + c];
+                    const ulonglong2 mw = *reinterpret_cast<const ulonglong2*>(&nodes[cb + c].meta);   // meta | W: same sector
+                    const unsigned long long mm = mw.x;
                     const int n = h.N + (int)h.V;
-                    const double W = wsum[cb + c] - (double)h.V;
+                    const double W = __longlong_as_double((long long)mw.y) - (double)h.V;
                     const double sc = az_puct64(W, f.root_prior64[(size_t)tree * g.max_children + c], n, s);
                     if (sc > best) { best = sc; bi = c; bm = mm; bn = n; }
                 }
-                az_group_argmax<G, double>(gmask, best, bi);
+                bi = az_group_argmax(gmask, best, bi);
             } else {
                 const float s = __fsqrt_rn((float)pn);
                 float best = -1.0f / 0.0f;
                 for (int c = lane; c < nc; c += G) {
                     const AzHot h = hot[cb + c];
-                    const unsigned long long mm = meta64[cb + c];
-                    const double Wc = use_vl ? wsum[cb + c] : 0.0;    // independent of h: same round trip
+                    const ulonglong2 mw = *reinterpret_cast<const ulonglong2*>(&nodes[cb + c].meta);   // meta | W: same sector
+                    const unsigned long long mm = mw.x;
+                    const double Wc = __longlong_as_double((long long)mw.y);
                     int n = h.N;
                     float q = h.Q;
                     if (use_vl && h.V) {                              // virtual loss: n + v visits, v losses
@@ -245,7 +329,7 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
                     const float sc = az_puct32(q, h.P, n, s);
                     if (sc > best) { best = sc; bi = c; bm = mm; bn = n; }
                 }
-                az_group_argmax<G, float>(gmask, best, bi);
+                bi = az_group_argmax(gmask, best, bi);
             }
             st_reads += nc;
             ++st_sel;
@@ -266,6 +350,8 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
             b.put(player, m.action);                          // Game.make_move (mcts.py:23)
             player ^= 1;
             ++mc;
+            AZ_AT(5);                                         // one select level
+            AZ_AT_COUNT(14, 1);
         }
         if (m.status == AZ_ST_PENDING) {                      // leaf already waiting: close the batch
             ++st_coll;
@@ -289,12 +375,11 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
             ++st_sims;
             ++started;
             ++sims;
+            AZ_AT(7);                                         // terminal backup
             continue;
         }
-        // leaf needs the evaluator
-        int slot = 0;
-        if (lane == 0) slot = atomicAdd(f.n_leaves, 1);
-        slot = __shfl_sync(gmask, slot, 0, G);
+        // leaf needs the evaluator: lane (np - flushed) keeps its board until the tree's slots are
+        // reserved with ONE atomic for all leaves of this launch (hand_off below)
         const size_t pj = (size_t)tree * f.vl + np;
         uint32_t* gpath = f.path + pj * f.max_depth;
         for (int i = lane; i < len; i += G) {
@@ -302,29 +387,29 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
             gpath[i] = nd;
             if (use_vl) hot[nd].V += 1;
         }
+        if (lane == np - flushed) {
+            kept = b;
+            kept_player = player;
+        }
         if (lane == 0) {
             f.path_len[pj] = (uint16_t)len;
-            f.leaf_slot[pj] = slot;
             f.pend_action[pj] = m.action;
-            f.leaf_player[slot] = (uint8_t)player;
-            f.leaf_tree[slot] = tree;
             if (use_vl) {
                 m.status = AZ_ST_PENDING;
                 meta[node] = m;
             }
-#pragma unroll
-            for (int w = 0; w < NW; ++w) {
-                f.pend_words[pj * 2 * NW + w] = b.w[0][w];
-                f.pend_words[pj * 2 * NW + NW + w] = b.w[1][w];
-                f.leaf_words[(size_t)slot * 2 * NW + w] = b.w[player][w];           // canonical: mine
-                f.leaf_words[(size_t)slot * 2 * NW + NW + w] = b.w[player ^ 1][w];  // theirs
-            }
+        }
+        if (np + 1 - flushed == G) {
+            hand_off(np + 1);
+            flushed = np + 1;
         }
         __syncwarp(gmask);
+        AZ_AT(6);                                             // terminal test + leaf hand-off
         ++np;
         ++started;
     }
 
+    hand_off(np);
     if (lane == 0) {
         f.n_nodes[tree] = n_nodes;
         f.sims_done[tree] = sims;
@@ -341,6 +426,14 @@ __global__ void __launch_bounds__(128, 8) az_advance_kernel(AzForestDev f, int s
         for (int k = 0; k < 7; ++k) if (lane == k) v = vals[k];
         if (v) f.stats[(size_t)tree * AZ_STAT_COUNT + lane] += v;
     }
+    AZ_AT(8);                                                 // tail writes
+#ifdef AZ_ADV_TRACE
+    if (lane == 0) {
+        const unsigned life = (unsigned)(clock64() - at_t0);
+        atomicAdd(&g_adv_hist[min(life >> 15, 63u)], 1u);
+        atomicMax(&g_adv_hist[64], life);
+    }
+#endif
 }
 
 }  // namespace
@@ -358,14 +451,14 @@ __global__ void az_begin_move_kernel(AzForestDev f) {
     h.Q = 0.f;
     h.P = 0.f;
     h.V = 0;
-    f.hot[(size_t)tree * f.cap] = h;
-    f.wsum[(size_t)tree * f.cap] = 0.0;
+    f.nodes[(size_t)tree * f.cap].hot = h;
+    f.nodes[(size_t)tree * f.cap].W = 0.0;
     AzMeta m;
     m.child_base = 0;
     m.action = 0;
     m.nchild = 0;
     m.status = AZ_ST_LEAF;
-    f.meta[(size_t)tree * f.cap] = m;
+    f.nodes[(size_t)tree * f.cap].meta = m;
     f.n_nodes[tree] = 1;
     f.sims_done[tree] = 0;
     f.n_pending[tree] = 0;
@@ -466,13 +559,12 @@ __global__ void az_root_visits_kernel(AzForestDev f, int* visits, double* q) {
     const int A = f.g.action_dim;
     for (int a = threadIdx.x; a < A; a += blockDim.x) visits[(size_t)tree * A + a] = 0;
     __syncthreads();
-    const AzMeta m = f.meta[(size_t)tree * f.cap];
-    const AzHot* hot = f.hot + (size_t)tree * f.cap;
-    const AzMeta* meta = f.meta + (size_t)tree * f.cap;
+    const AzNode* nodes = f.nodes + (size_t)tree * f.cap;
+    const AzMeta m = nodes[0].meta;
     if (m.status == AZ_ST_EXPANDED)
         for (int c = threadIdx.x; c < m.nchild; c += blockDim.x)
-            visits[(size_t)tree * A + az_action_index(f.g, meta[m.child_base + c].action)] = hot[m.child_base + c].N;
-    if (threadIdx.x == 0 && q) q[tree] = hot[0].N ? f.wsum[(size_t)tree * f.cap] / (double)hot[0].N : 0.0;   // gomoku.py:141
+            visits[(size_t)tree * A + az_action_index(f.g, nodes[m.child_base + c].meta.action)] = nodes[m.child_base + c].hot.N;
+    if (threadIdx.x == 0 && q) q[tree] = nodes[0].hot.N ? nodes[0].W / (double)nodes[0].hot.N : 0.0;   // gomoku.py:141
 }
 
 }  // namespace
@@ -615,6 +707,25 @@ int az_launch_advance(az_forest* f, cudaStream_t s) {
 
 }  // namespace
 
+#ifdef AZ_ADV_TRACE
+extern "C" __attribute__((visibility("default"))) int az_debug_adv_trace(unsigned long long* out_host, int reset) {
+    cudaError_t e = cudaMemcpyFromSymbol(out_host, g_adv_trace, sizeof(g_adv_trace));
+    if (reset) {
+        void* p = nullptr;
+        cudaGetSymbolAddress(&p, g_adv_trace);
+        cudaMemset(p, 0, sizeof(g_adv_trace));
+    }
+    return (int)e;
+}
+extern "C" __attribute__((visibility("default"))) int az_debug_adv_hist(unsigned int* out_host) {
+    cudaError_t e = cudaMemcpyFromSymbol(out_host, g_adv_hist, sizeof(g_adv_hist));
+    void* p = nullptr;
+    cudaGetSymbolAddress(&p, g_adv_hist);
+    cudaMemset(p, 0, sizeof(g_adv_hist));
+    return (int)e;
+}
+#endif
+
 #define AZ_CUDA_OK(expr)                                                                       \
     do {                                                                                       \
         cudaError_t e__ = (expr);                                                              \
@@ -658,9 +769,7 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
         az_forest_destroy(f);                                 \
         return rc;                                            \
     }
-    AZ_ALLOC(d.hot, nodes);
-    AZ_ALLOC(d.meta, nodes);
-    AZ_ALLOC(d.wsum, nodes);
+    AZ_ALLOC(d.nodes, nodes);
     AZ_ALLOC(d.root_words, (size_t)n_trees * 2 * nw);
     AZ_ALLOC(d.root_player, (size_t)n_trees);
     AZ_ALLOC(d.root_mc, (size_t)n_trees);
@@ -893,29 +1002,23 @@ extern "C" int az_forest_root_children(az_forest* f, int tree, int max_children,
     if (!f || tree < 0 || tree >= f->d.n_trees) return az_fail(AZ_EINVAL, "root_children: bad tree");
     cudaStream_t s = (cudaStream_t)stream;
     AZ_CUDA_OK(cudaStreamSynchronize(s));
-    AzMeta m;
-    AzHot h;
-    double w0 = 0.0;
-    AZ_CUDA_OK(cudaMemcpy(&m, f->d.meta + (size_t)tree * f->d.cap, sizeof(m), cudaMemcpyDeviceToHost));
-    AZ_CUDA_OK(cudaMemcpy(&h, f->d.hot + (size_t)tree * f->d.cap, sizeof(h), cudaMemcpyDeviceToHost));
-    AZ_CUDA_OK(cudaMemcpy(&w0, f->d.wsum + (size_t)tree * f->d.cap, sizeof(w0), cudaMemcpyDeviceToHost));
-    if (root_visit) *root_visit = h.N;
-    if (root_value) *root_value = w0;
+    AzNode root;
+    AZ_CUDA_OK(cudaMemcpy(&root, f->d.nodes + (size_t)tree * f->d.cap, sizeof(root), cudaMemcpyDeviceToHost));
+    const AzMeta m = root.meta;
+    if (root_visit) *root_visit = root.hot.N;
+    if (root_value) *root_value = root.W;
     if (m.status != AZ_ST_EXPANDED) return 0;
     const int nc = std::min<int>(m.nchild, max_children);
-    std::vector<AzHot> hh(nc);
-    std::vector<AzMeta> mm(nc);
-    std::vector<double> ww(nc), p64(nc);
-    AZ_CUDA_OK(cudaMemcpy(hh.data(), f->d.hot + (size_t)tree * f->d.cap + m.child_base, nc * sizeof(AzHot), cudaMemcpyDeviceToHost));
-    AZ_CUDA_OK(cudaMemcpy(mm.data(), f->d.meta + (size_t)tree * f->d.cap + m.child_base, nc * sizeof(AzMeta), cudaMemcpyDeviceToHost));
-    AZ_CUDA_OK(cudaMemcpy(ww.data(), f->d.wsum + (size_t)tree * f->d.cap + m.child_base, nc * sizeof(double), cudaMemcpyDeviceToHost));
+    std::vector<AzNode> kids(nc);
+    std::vector<double> p64(nc);
+    AZ_CUDA_OK(cudaMemcpy(kids.data(), f->d.nodes + (size_t)tree * f->d.cap + m.child_base, nc * sizeof(AzNode), cudaMemcpyDeviceToHost));
     if (f->d.use_noise)
         AZ_CUDA_OK(cudaMemcpy(p64.data(), f->d.root_prior64 + (size_t)tree * f->d.g.max_children, nc * 8, cudaMemcpyDeviceToHost));
     for (int c = 0; c < nc; ++c) {
-        if (cells_host) cells_host[c] = mm[c].action;
-        if (visits_host) visits_host[c] = hh[c].N;
-        if (values_host) values_host[c] = ww[c];
-        if (priors_host) priors_host[c] = f->d.use_noise ? p64[c] : (double)hh[c].P;
+        if (cells_host) cells_host[c] = kids[c].meta.action;
+        if (visits_host) visits_host[c] = kids[c].hot.N;
+        if (values_host) values_host[c] = kids[c].W;
+        if (priors_host) priors_host[c] = f->d.use_noise ? p64[c] : (double)kids[c].hot.P;
     }
     return m.nchild;
 }

@@ -1,9 +1,8 @@
 // Device-side view of a forest of concurrent search trees (one per game) in HBM.
 //
 // Layout (SoA across node fields, grouped by access pattern):
-//   hot [tree*cap + i]   AzHot  {N i32, Q f32, P f32, V u32}  -- 16 B, one vector load per child in PUCT
-//   meta[tree*cap + i]   AzMeta {child_base, action, nchild, status} -- 8 B, fetched together with hot
-//   wsum[tree*cap + i]   f64 value sum W -- read-modify-written by backups only (Q caches (float)(W/N))
+//   nodes[tree*cap + i]  AzNode = {hot {N i32, Q f32, P f32, V u32} | meta {child_base, action, nchild, status} | W f64}
+//                        32 B = one sector: two 16-byte loads per child in PUCT, one sector per backup / expansion
 // Children of a node are contiguous (bump allocator per tree), in the reference's child
 // order (= order of Game.get_valid_moves, ai/node.py:55-59).  Node 0 is the root.
 #pragma once
@@ -31,9 +30,7 @@ struct AzForestDev {
     int use_noise;    // Dirichlet noise mixed into the root priors (utils.py:12-27)
     int lp;           // pending leaves of a tree expanded in parallel (<= AZ_LP, <= vl)
 
-    AzHot* hot;
-    AzMeta* meta;
-    double* wsum;     // W of every node (f64 running sum in visitation order)
+    AzNode* nodes;    // [n_trees][cap]
 
     // per tree
     uint64_t* root_words;    // [n_trees][2*nw]  side-0 words then side-1 words

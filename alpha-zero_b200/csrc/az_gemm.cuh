@@ -6,9 +6,16 @@
 //            STAGES-deep shared-memory ring, completion on mbarriers;
 //   warp 1   MMA issuer: one lane issues tcgen05.mma (M=128, N=BN, K=16) with the fp32
 //            accumulator in TMEM; tcgen05.commit releases ring slots / publishes the tile;
-//   warps 2-5 epilogue: tcgen05.ld the accumulator (each warp its 32-lane quarter), add
-//            bias (+ exact-erf GELU | + residual), convert to bf16, 64-byte row stores.
+//   warps 2-9 epilogue: tcgen05.ld the accumulator (each warp its 32-lane quarter and one half of the
+//            tile's columns), add bias (+ erf GELU | + residual), convert to bf16, 64-byte row stores.
 // Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
+//
+// LayerNorm around a GEMM never runs as its own kernel on the cls-row path.  The GEMM that PRODUCES a
+// row also emits partial (sum, sum of squares) of its bf16 outputs (stats_out); the GEMM that CONSUMES
+// LayerNorm(row) runs on the raw row with the gain folded into the weights and applies
+//     out = rstd * (acc - mean * colsum) + bias',   colsum[n] = sum_k W'[n][k],  bias' = bias + W beta
+// in its epilogue (stats_in).  AZ_EPI_HEAD (BN = 64, one thread owns all head outputs of a row)
+// finishes with the softmax over the policy logits and tanh of the value (ai/nn.py:78-83, ai/mcts.py:49).
 // M may come from a device-side counter (the evaluation batch of the forest is only known
 // on the device), so the kernel is CUDA-graph capturable with a fixed grid.
 #pragma once
@@ -19,6 +26,10 @@
 #define AZ_EPI_BIAS 0
 #define AZ_EPI_GELU 1
 #define AZ_EPI_RESID 2
+#define AZ_EPI_HEAD 3
+#define AZ_STATS_LD 64          // floats per row of a statistics buffer: up to 32 (sum, sum of squares) partials
+#define AZ_GEMM_THREADS 320
+#define AZ_HEAD_STAGE_BYTES (4 * 32 * 64 * 4)
 
 struct AzGemmArgs {
     const float* bias;          // [N] fp32
@@ -33,6 +44,15 @@ struct AzGemmArgs {
     int m_rows_per_item;        // rows per item (tokens per board, or 1)
     float* out_f32;             // optional: columns >= f32_col0 are written here as fp32 [M][64] instead
     int f32_col0;
+    // LayerNorm folded around the GEMM (see the header comment)
+    float* stats_out;           // [M][AZ_STATS_LD]: partial (sum, sum sq) per (N tile, column half) of the bf16 outputs
+    const float* stats_in;      // partials of the A rows, stats_parts pairs valid
+    const float* colsum;        // [N]
+    int stats_parts;
+    float ln_inv_k, ln_eps;
+    // AZ_EPI_HEAD: softmax over columns [0, head_A) -> priors, tanh(column head_A) -> values
+    int head_A;
+    float *priors, *values, *logits;
 };
 
 __device__ __forceinline__ int az_gemm_rows(const AzGemmArgs& a) {
@@ -53,12 +73,20 @@ struct AzGemmCfg {
     static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;   // + barriers + align slack
 };
 
-__device__ __forceinline__ float az_gelu_erf(float x) {      // nn.GELU() default: exact erf form
-    return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+// nn.GELU() default (erf form): 0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz & Stegun 7.1.25
+// (|error| <= 2.5e-5, far below the bf16 output resolution):  z = |x|/sqrt2, t = 1/(1 + 0.47047 z),
+// E = (a1 t + a2 t^2 + a3 t^3) exp(-z^2) = 1 - erf(z)  =>  gelu(x) = max(x, 0) - 0.5 |x| E.
+__device__ __forceinline__ float az_gelu_erf(float x) {
+    const float ax = fabsf(x);
+    float t, e;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(ax, 0.47047f * 0.70710678118654752440f, 1.0f)));
+    const float p = t * fmaf(t, fmaf(t, 0.5f * 0.7478556f, 0.5f * -0.0958798f), 0.5f * 0.3480242f);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * (-0.5f * 1.4426950408889634f)));
+    return fmaf(-ax, p * e, fmaxf(x, 0.0f));
 }
 
 template <int BN, int EPI>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(AZ_GEMM_THREADS, 1)
 az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, AzGemmArgs args) {
     using Cfg = AzGemmCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
@@ -88,7 +116,7 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         }
         for (int i = 0; i < 2; ++i) {
             azptx::mbar_init(&tfull[i], 1);
-            azptx::mbar_init(&tempty[i], 128);
+            azptx::mbar_init(&tempty[i], EPI == AZ_EPI_HEAD ? 128 : 256);
         }
         azptx::fence_barrier_init();
     }
@@ -138,8 +166,10 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             as ^= 1;
             if (as == 0) aphase ^= 1;
         }
-    } else {                                                  // ---- epilogue (warps 2..5)
+    } else if (EPI != AZ_EPI_HEAD || warp < 6) {              // ---- epilogue (warps 2..9; the head epilogue uses 2..5)
         const int q = warp & 3;                               // TMEM lane quarter this warp may read
+        const int half = (warp - 2) >> 2;                     // which half of the tile's columns
+        constexpr int CPW = EPI == AZ_EPI_HEAD ? BN / 32 : BN / 64;   // 32-column chunks per warp
         int as = 0;
         uint32_t aphase = 0;
         for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
@@ -148,57 +178,136 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             azptx::tc_fence_after();
             const int row = m_blk * Cfg::BM + q * 32 + lane;
             const bool live = row < M;
-#pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                uint32_t r[32];
-                azptx::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * Cfg::ACC_STRIDE + c * 32, r);
-                azptx::tmem_ld_wait();
-                const int col0 = n_blk * BN + c * 32;
-                if (live && args.out_f32 && col0 >= args.f32_col0) {      // fp32 side output (attention scores)
-                    const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
-                    float4* op = reinterpret_cast<float4*>(args.out_f32 + (size_t)row * 64 + (col0 - args.f32_col0));
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const float4 bb = __ldg(b4 + i);
-                        op[i] = make_float4(__uint_as_float(r[4 * i + 0]) + bb.x, __uint_as_float(r[4 * i + 1]) + bb.y,
-                                            __uint_as_float(r[4 * i + 2]) + bb.z, __uint_as_float(r[4 * i + 3]) + bb.w);
-                    }
-                } else if (live) {
-                    const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
-                    uint4 rv[4];
-                    if (EPI == AZ_EPI_RESID) {
-                        const uint4* rp = reinterpret_cast<const uint4*>(args.resid + (size_t)row * args.ldr + col0);
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) rv[i] = rp[i];
-                    }
-                    uint4 ov[4];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const float4 bb = __ldg(b4 + i);
-                        float v0 = __uint_as_float(r[4 * i + 0]) + bb.x;
-                        float v1 = __uint_as_float(r[4 * i + 1]) + bb.y;
-                        float v2 = __uint_as_float(r[4 * i + 2]) + bb.z;
-                        float v3 = __uint_as_float(r[4 * i + 3]) + bb.w;
-                        if (EPI == AZ_EPI_GELU) {
-                            v0 = az_gelu_erf(v0); v1 = az_gelu_erf(v1); v2 = az_gelu_erf(v2); v3 = az_gelu_erf(v3);
-                        }
-                        if (EPI == AZ_EPI_RESID) {
-                            const uint32_t* rw = reinterpret_cast<const uint32_t*>(&rv[i >> 1]) + (i & 1) * 2;
-                            const __nv_bfloat162 r01 = *reinterpret_cast<const __nv_bfloat162*>(&rw[0]);
-                            const __nv_bfloat162 r23 = *reinterpret_cast<const __nv_bfloat162*>(&rw[1]);
-                            v0 += __bfloat162float(r01.x); v1 += __bfloat162float(r01.y);
-                            v2 += __bfloat162float(r23.x); v3 += __bfloat162float(r23.y);
-                        }
-                        __nv_bfloat162 o01 = __floats2bfloat162_rn(v0, v1);
-                        __nv_bfloat162 o23 = __floats2bfloat162_rn(v2, v3);
-                        uint32_t* ow = reinterpret_cast<uint32_t*>(&ov[i >> 1]) + (i & 1) * 2;
-                        ow[0] = *reinterpret_cast<uint32_t*>(&o01);
-                        ow[1] = *reinterpret_cast<uint32_t*>(&o23);
-                    }
-                    uint4* op = reinterpret_cast<uint4*>(args.out + (size_t)row * args.ldo + col0);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) op[i] = ov[i];
+            float mean = 0.f, rstd = 1.f;
+            if (args.stats_in && live) {                      // LayerNorm statistics of this A row
+                const float2* sp = reinterpret_cast<const float2*>(args.stats_in + (size_t)row * AZ_STATS_LD);
+                float s1 = 0.f, s2 = 0.f;
+                for (int p = 0; p < args.stats_parts; ++p) {
+                    const float2 v = sp[p];
+                    s1 += v.x;
+                    s2 += v.y;
                 }
+                mean = s1 * args.ln_inv_k;
+                rstd = rsqrtf(fmaxf(s2 * args.ln_inv_k - mean * mean, 0.f) + args.ln_eps);
+            }
+            const float nmr = -mean * rstd;                   // out = rstd*acc + nmr*colsum + bias
+            const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * Cfg::ACC_STRIDE;
+            if constexpr (EPI == AZ_EPI_HEAD) {
+                static_assert(EPI != AZ_EPI_HEAD || BN == 64, "head epilogue: one 64-column tile per row");
+                float l[64];
+                {
+                    uint32_t r0[32], r1[32];
+                    azptx::tmem_ld32(tacc, r0);
+                    azptx::tmem_ld32(tacc + 32, r1);
+                    azptx::tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        l[i] = fmaf(rstd, __uint_as_float(r0[i]), fmaf(nmr, __ldg(args.colsum + i), __ldg(args.bias + i)));
+                        l[32 + i] = fmaf(rstd, __uint_as_float(r1[i]), fmaf(nmr, __ldg(args.colsum + 32 + i), __ldg(args.bias + 32 + i)));
+                    }
+                }
+                const int A = args.head_A;
+                float* hs = reinterpret_cast<float*>(smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES) + 256) + q * 32 * 64;
+                const int r0w = m_blk * Cfg::BM + q * 32;     // first row of this warp
+                const int nlive = min(max(M - r0w, 0), 32);
+                const size_t obase = (size_t)(args.m_item_offset + r0w);
+                float mx = -3.0e38f, val = 0.f;
+#pragma unroll
+                for (int o = 0; o < 64; ++o) {
+                    if (o < A) mx = fmaxf(mx, l[o]);
+                    if (o == A) val = l[o];
+                }
+                if (args.logits) {
+#pragma unroll
+                    for (int o = 0; o < 64; ++o) if (o < A && live) hs[lane * A + o] = l[o];
+                    __syncwarp();
+                    for (int i = lane; i < nlive * A; i += 32) args.logits[obase * A + i] = hs[i];
+                    __syncwarp();
+                }
+                float sum = 0.f;
+#pragma unroll
+                for (int o = 0; o < 64; ++o) {
+                    if (o < A) {
+                        l[o] = expf(l[o] - mx);
+                        sum += l[o];
+                    }
+                }
+                const float inv = 1.0f / sum;
+#pragma unroll
+                for (int o = 0; o < 64; ++o) if (o < A && live) hs[lane * A + o] = l[o] * inv;
+                __syncwarp();
+                for (int i = lane; i < nlive * A; i += 32) args.priors[obase * A + i] = hs[i];
+                __syncwarp();
+                if (live) args.values[obase + lane] = tanhf(val);
+            } else {
+                float st1 = 0.f, st2 = 0.f;
+#pragma unroll 1
+                for (int cc = 0; cc < CPW; ++cc) {
+                    const int c = half * CPW + cc;
+                    uint32_t r[32];
+                    azptx::tmem_ld32(tacc + c * 32, r);
+                    azptx::tmem_ld_wait();
+                    const int col0 = n_blk * BN + c * 32;
+                    if (live && args.out_f32 && col0 >= args.f32_col0) {      // fp32 side output (attention scores)
+                        const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
+                        float4* op = reinterpret_cast<float4*>(args.out_f32 + (size_t)row * 64 + (col0 - args.f32_col0));
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const float4 bb = __ldg(b4 + i);
+                            op[i] = make_float4(__uint_as_float(r[4 * i + 0]) + bb.x, __uint_as_float(r[4 * i + 1]) + bb.y,
+                                                __uint_as_float(r[4 * i + 2]) + bb.z, __uint_as_float(r[4 * i + 3]) + bb.w);
+                        }
+                    } else if (live) {
+                        const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
+                        const float4* c4 = reinterpret_cast<const float4*>(args.colsum + col0);
+                        uint4 rv[4];
+                        if (EPI == AZ_EPI_RESID) {
+                            const uint4* rp = reinterpret_cast<const uint4*>(args.resid + (size_t)row * args.ldr + col0);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) rv[i] = rp[i];
+                        }
+                        uint4 ov[4];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            float4 bb = __ldg(b4 + i);
+                            if (args.stats_in) {
+                                const float4 cs = __ldg(c4 + i);
+                                bb.x = fmaf(nmr, cs.x, bb.x); bb.y = fmaf(nmr, cs.y, bb.y);
+                                bb.z = fmaf(nmr, cs.z, bb.z); bb.w = fmaf(nmr, cs.w, bb.w);
+                            }
+                            float v0 = fmaf(rstd, __uint_as_float(r[4 * i + 0]), bb.x);
+                            float v1 = fmaf(rstd, __uint_as_float(r[4 * i + 1]), bb.y);
+                            float v2 = fmaf(rstd, __uint_as_float(r[4 * i + 2]), bb.z);
+                            float v3 = fmaf(rstd, __uint_as_float(r[4 * i + 3]), bb.w);
+                            if (EPI == AZ_EPI_GELU) {
+                                v0 = az_gelu_erf(v0); v1 = az_gelu_erf(v1); v2 = az_gelu_erf(v2); v3 = az_gelu_erf(v3);
+                            }
+                            if (EPI == AZ_EPI_RESID) {
+                                const uint32_t* rw = reinterpret_cast<const uint32_t*>(&rv[i >> 1]) + (i & 1) * 2;
+                                const __nv_bfloat162 r01 = *reinterpret_cast<const __nv_bfloat162*>(&rw[0]);
+                                const __nv_bfloat162 r23 = *reinterpret_cast<const __nv_bfloat162*>(&rw[1]);
+                                v0 += __bfloat162float(r01.x); v1 += __bfloat162float(r01.y);
+                                v2 += __bfloat162float(r23.x); v3 += __bfloat162float(r23.y);
+                            }
+                            __nv_bfloat162 o01 = __floats2bfloat162_rn(v0, v1);
+                            __nv_bfloat162 o23 = __floats2bfloat162_rn(v2, v3);
+                            if (args.stats_out) {             // statistics of the values the consumer will read
+                                const float f0 = __bfloat162float(o01.x), f1 = __bfloat162float(o01.y);
+                                const float f2 = __bfloat162float(o23.x), f3 = __bfloat162float(o23.y);
+                                st1 += (f0 + f1) + (f2 + f3);
+                                st2 = fmaf(f0, f0, fmaf(f1, f1, fmaf(f2, f2, fmaf(f3, f3, st2))));
+                            }
+                            uint32_t* ow = reinterpret_cast<uint32_t*>(&ov[i >> 1]) + (i & 1) * 2;
+                            ow[0] = *reinterpret_cast<uint32_t*>(&o01);
+                            ow[1] = *reinterpret_cast<uint32_t*>(&o23);
+                        }
+                        uint4* op = reinterpret_cast<uint4*>(args.out + (size_t)row * args.ldo + col0);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) op[i] = ov[i];
+                    }
+                }
+                if (args.stats_out && live)
+                    *reinterpret_cast<float2*>(args.stats_out + (size_t)row * AZ_STATS_LD + (n_blk * 2 + half) * 2) = make_float2(st1, st2);
             }
             azptx::tc_fence_before();
             azptx::mbar_arrive(&tempty[as]);

@@ -87,9 +87,10 @@ static int az_pick_bn_small_m(int N, int max_rows) {
 
 template <int BN, int EPI>
 static int az_launch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& a, int max_rows, cudaStream_t s) {
+    constexpr int smem = AzGemmCfg<BN>::SMEM + (EPI == AZ_EPI_HEAD ? AZ_HEAD_STAGE_BYTES : 0);
     static bool attr_done = false;
     if (!attr_done) {
-        AZ_CUDA_OK(cudaFuncSetAttribute(az_gemm_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, AzGemmCfg<BN>::SMEM));
+        AZ_CUDA_OK(cudaFuncSetAttribute(az_gemm_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_done = true;
     }
     if (!g_num_sms) {
@@ -99,7 +100,7 @@ static int az_launch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const 
     }
     const int tiles = ((max_rows + 127) / 128) * (a.N / BN);
     const int grid = tiles < g_num_sms ? (tiles > 0 ? tiles : 1) : g_num_sms;
-    az_gemm_kernel<BN, EPI><<<grid, 192, AzGemmCfg<BN>::SMEM, s>>>(ta, tb, a);
+    az_gemm_kernel<BN, EPI><<<grid, AZ_GEMM_THREADS, smem, s>>>(ta, tb, a);
     AZ_CUDA_OK(cudaGetLastError());
     return AZ_OK;
 }
@@ -109,6 +110,13 @@ static int az_launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const Az
                           cudaStream_t s, int bn_forced = 0) {
     const int bn = bn_forced ? bn_forced : az_pick_bn(a.N);
     if (!bn || a.K % 64) return az_fail(AZ_EINVAL, "gemm: N and K must be multiples of 64");
+    if (epi == AZ_EPI_HEAD) {
+        if (bn != 64 || a.N != 64 || !a.stats_in || !a.colsum || !a.priors || !a.values || a.head_A < 1 || a.head_A > 63)
+            return az_fail(AZ_EINVAL, "gemm: head epilogue needs N = 64, row statistics and output pointers");
+        return az_launch_gemm_t<64, AZ_EPI_HEAD>(ta, tb, a, max_rows, s);
+    }
+    if ((a.stats_in && (!a.colsum || a.stats_parts < 1 || a.stats_parts > AZ_STATS_LD / 2)) || (a.stats_out && 2 * (a.N / bn) > AZ_STATS_LD / 2))
+        return az_fail(AZ_EINVAL, "gemm: bad LayerNorm-fold arguments");
 #define AZ_G(BN_)                                                                              \
     if (bn == BN_) {                                                                           \
         if (epi == AZ_EPI_BIAS) return az_launch_gemm_t<BN_, AZ_EPI_BIAS>(ta, tb, a, max_rows, s);   \
@@ -158,6 +166,10 @@ struct AzBlockW {
     CUtensorMap tm_in, tm_q, tm_kv, tm_out, tm_w1, tm_w2;
     CUtensorMap tm_out_c, tm_w1_c, tm_w2_c;     // same weights, tile width chosen for the cls-row GEMMs
     int bn_out_c = 0, bn_w1_c = 0, bn_w2_c = 0;
+    // norm2 folded into mlp1 for the cls rows (az_gemm.cuh): w1 * diag(gain), bias + w1 beta, row sums
+    bf16* w1_ln = nullptr;
+    float *b1_ln = nullptr, *cs1 = nullptr;
+    CUtensorMap tm_w1_ln_c;
 };
 
 struct az_net {
@@ -195,6 +207,13 @@ struct az_net {
     bf16* w_head = nullptr;
     float *b_head = nullptr, *head_out = nullptr;
     CUtensorMap tm_whead;
+    // cls-row tail without LayerNorm kernels: row statistics travel between the GEMM epilogues,
+    // the final norm + heads + softmax are the epilogue of one N = 64 GEMM (A + 1 <= 64)
+    bool tail_fold = false, head_fold = false;
+    float *stats1 = nullptr, *stats2 = nullptr;
+    bf16* w_head_ln = nullptr;
+    float *b_head_ln = nullptr, *cs_head = nullptr;
+    CUtensorMap tm_whead_ln, tm_xc, tm_xc2;
     bool head_gemm = false;
     // activations (one chunk)
     bf16 *x = nullptr, *xn = nullptr, *qkv = nullptr, *ao = nullptr, *hbuf = nullptr;
@@ -416,6 +435,24 @@ extern "C" int az_net_finalize(az_net* n) {
             (rc = az_make_tmap(&w.tm_w1, w.w1, 4 * D, D, D, az_pick_bn(4 * D))) ||
             (rc = az_make_tmap(&w.tm_w2, w.w2, D, 4 * D, 4 * D, az_pick_bn(D))))
             return rc;
+        if (l == n->L - 1) {                                  // norm2 folded into mlp1 (cls rows of the last block)
+            auto r16 = [](float v) { return __bfloat162float(__float2bfloat16(v)); };
+            std::vector<float> wf((size_t)4 * D * D), bfold((size_t)4 * D), cs((size_t)4 * D);
+            for (int r = 0; r < 4 * D; ++r) {
+                double acc = (*bb1)[r], sum = 0.0;
+                for (int k = 0; k < D; ++k) {
+                    const float wv = (*w1)[(size_t)r * D + k] * (*g2)[k];
+                    wf[(size_t)r * D + k] = wv;
+                    sum += (double)r16(wv);                   // what the tensor cores will multiply by
+                    acc += (double)(*w1)[(size_t)r * D + k] * (*be2)[k];
+                }
+                bfold[r] = (float)acc;
+                cs[r] = (float)sum;
+            }
+            if ((rc = az_upload_bf16(n, &w.w1_ln, wf.data(), wf.size())) || (rc = az_upload_f32(n, &w.b1_ln, bfold)) ||
+                (rc = az_upload_f32(n, &w.cs1, cs)))
+                return rc;
+        }
     }
     // ---- depth 1: fold the (constant) cls query into the K projection
     n->folded = false;
@@ -618,8 +655,36 @@ extern "C" int az_net_finalize(az_net* n) {
             (rc = az_make_tmap(&w.tm_w2_c, w.w2, D, 4 * D, 4 * D, w.bn_w2_c)))
             return rc;
     }
+    n->tail_fold = !getenv("AZ_NO_TAIL_FOLD");
+    n->head_fold = n->tail_fold && A + 1 <= 64;
+    if (n->tail_fold) {
+        AzBlockW& w = n->blk[n->L - 1];
+        if ((rc = az_make_tmap(&w.tm_w1_ln_c, w.w1_ln, 4 * D, D, D, w.bn_w1_c)) ||
+            (rc = az_net_alloc(n, &n->stats1, B * AZ_STATS_LD)) || (rc = az_net_alloc(n, &n->stats2, B * AZ_STATS_LD)) ||
+            (rc = az_make_tmap(&n->tm_xc, n->xc, B, D, D, 128)) || (rc = az_make_tmap(&n->tm_xc2, n->xc2, B, D, D, 128)))
+            return rc;
+    }
+    if (n->head_fold) {                                       // final norm folded into [policy ; value] rows
+        auto r16 = [](float v) { return __bfloat162float(__float2bfloat16(v)); };
+        std::vector<float> wh((size_t)64 * D, 0.f), bh(64, 0.f), cs(64, 0.f);
+        for (int o = 0; o <= A; ++o) {
+            const float* src = o < A ? wp->data() + (size_t)o * D : wv->data();
+            double acc = o < A ? (*bp)[o] : (*bv)[0], sum = 0.0;
+            for (int d = 0; d < D; ++d) {
+                const float v = src[d] * (*gf)[d];
+                wh[(size_t)o * D + d] = v;
+                sum += (double)r16(v);
+                acc += (double)src[d] * (*bf)[d];
+            }
+            bh[o] = (float)acc;
+            cs[o] = (float)sum;
+        }
+        if ((rc = az_upload_bf16(n, &n->w_head_ln, wh.data(), wh.size())) || (rc = az_upload_f32(n, &n->b_head_ln, bh)) ||
+            (rc = az_upload_f32(n, &n->cs_head, cs)) || (rc = az_make_tmap(&n->tm_whead_ln, n->w_head_ln, 64, D, D, 64)))
+            return rc;
+    }
     n->head_gemm = false;
-    if (A + 1 > 32 && A + 1 <= 64 && !getenv("AZ_NO_HEAD_GEMM")) {   // heads as one N = 64 tensor-core GEMM
+    if (!n->head_fold && A + 1 > 32 && A + 1 <= 64 && !getenv("AZ_NO_HEAD_GEMM")) {   // heads as one N = 64 tensor-core GEMM
         std::vector<float> wh((size_t)64 * D, 0.f), bh(64, 0.f);
         for (int o = 0; o < A; ++o) {
             for (int d = 0; d < D; ++d) wh[(size_t)o * D + d] = (*wp)[(size_t)o * D + d];
@@ -693,6 +758,20 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         ha.batch = batch; ha.xc = xc_final; ha.D = D; ha.A = A; ha.ln_g = n->lnf_g; ha.ln_b = n->lnf_b;
         ha.w_pol = n->w_pol; ha.b_pol = n->b_pol; ha.w_val = n->w_val; ha.b_val = n->b_val;
         ha.priors = priors; ha.values = values; ha.logits = logits;
+        if (n->head_fold) {                                    // one GEMM: raw rows x folded head weights, norm + softmax in the epilogue
+            AzGemmArgs ga = az_gargs(batch, 1, n->b_head_ln, nullptr, 0, nullptr, 64, 64, D);
+            ga.stats_in = n->stats2;
+            ga.stats_parts = 2 * (D / n->blk[L - 1].bn_w2_c);
+            ga.colsum = n->cs_head;
+            ga.ln_inv_k = 1.0f / (float)D;
+            ga.ln_eps = 1e-5f;
+            ga.head_A = A;
+            ga.priors = priors; ga.values = values; ga.logits = logits;
+            int rc2 = gemm_bn(AZ_K_HEAD, xc_final == n->xc2 ? n->tm_xc2 : n->tm_xc, n->tm_whead_ln, ga, AZ_EPI_HEAD, cap, 64);
+            if (rc2) return rc2;
+            ++n->launches;
+            return AZ_OK;
+        }
         if (n->head_gemm) {                                    // LayerNorm -> [cap][D] x [64][D]^T on tensor cores -> softmax
             layernorm(1, xc_final, D, n->xcn, D, n->lnf_g, n->lnf_b);
             AzGemmArgs ga = az_gargs(batch, 1, n->b_head, nullptr, 0, n->xcn, 64, 64, D);
@@ -725,6 +804,34 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         ++n->launches;
         return AZ_OK;
     };
+    // out-proj -> norm2 -> mlp (ai/nn.py:44-50) on the cls rows: oc [cap][D] -> xc (residual stream) -> xc2.
+    // With tail_fold the out-proj epilogue emits the row statistics and mlp1 applies norm2 in its own
+    // epilogue (az_gemm.cuh); mlp2 emits the statistics the head GEMM needs.
+    auto cls_tail = [&](AzBlockW& w, AzGemmArgs out_args, int out_epi) -> int {
+        int rc2;
+        if (n->tail_fold) {
+            out_args.stats_out = n->stats1;
+            if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out_c, out_args, out_epi, cap, w.bn_out_c))) return rc2;
+            AzGemmArgs g1 = az_gargs(batch, 1, w.b1_ln, nullptr, 0, n->hc, 4 * D, 4 * D, D);
+            g1.stats_in = n->stats1;
+            g1.stats_parts = 2 * (D / w.bn_out_c);
+            g1.colsum = w.cs1;
+            g1.ln_inv_k = 1.0f / (float)D;
+            g1.ln_eps = 1e-5f;
+            if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, n->tm_xc, w.tm_w1_ln_c, g1, AZ_EPI_GELU, cap, w.bn_w1_c))) return rc2;
+            AzGemmArgs g2 = az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D);
+            if (n->head_fold) g2.stats_out = n->stats2;
+            if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2_c, g2, AZ_EPI_RESID, cap, w.bn_w2_c))) return rc2;
+            n->launches += 3;
+            return AZ_OK;
+        }
+        if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out_c, out_args, out_epi, cap, w.bn_out_c))) return rc2;
+        layernorm(1, n->xc, D, n->xcn, D, w.ln2_g, w.ln2_b);
+        if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, n->tm_xcn, w.tm_w1_c, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap, w.bn_w1_c))) return rc2;
+        if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2_c, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap, w.bn_w2_c))) return rc2;
+        n->launches += 3;
+        return AZ_OK;
+    };
     if (n->front) {
         // embedding + LN1 + V/score projection + cls attention, all on chip (az_front.cuh)
         AzBlockW& w = n->blk[0];
@@ -752,11 +859,7 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         }
         AZ_CUDA_OK(cudaGetLastError());
         ++n->launches;
-        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out_c, az_gargs(batch, 1, n->b_out_x0, nullptr, 0, n->xc, D, D, D), AZ_EPI_BIAS, cap, w.bn_out_c))) return rc;
-        layernorm(1, n->xc, D, n->xcn, D, w.ln2_g, w.ln2_b);
-        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_xcn, w.tm_w1_c, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap, w.bn_w1_c))) return rc;
-        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2_c, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap, w.bn_w2_c))) return rc;
-        n->launches += 3;
+        if ((rc = cls_tail(w, az_gargs(batch, 1, n->b_out_x0, nullptr, 0, n->xc, D, D, D), AZ_EPI_BIAS))) return rc;
         return heads(n->xc2);
     }
     // 1. boards -> tokens -> LN1 of block 0 (affine folded into block 0's in_proj at load time)
@@ -837,11 +940,8 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         }
         AZ_CUDA_OK(cudaGetLastError());
         }
-        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out_c, az_gargs(batch, 1, w.b_out, n->x, T * D, n->xc, D, D, D), AZ_EPI_RESID, cap, w.bn_out_c))) return rc;
-        layernorm(1, n->xc, D, n->xcn, D, w.ln2_g, w.ln2_b);
-        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_xcn, w.tm_w1_c, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap, w.bn_w1_c))) return rc;
-        if ((rc = gemm_bn(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2_c, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap, w.bn_w2_c))) return rc;
-        n->launches += 6;
+        if ((rc = cls_tail(w, az_gargs(batch, 1, w.b_out, n->x, T * D, n->xc, D, D, D), AZ_EPI_RESID))) return rc;
+        n->launches += 3;
     }
     return heads(n->xc2);
 }

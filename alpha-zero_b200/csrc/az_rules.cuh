@@ -108,40 +108,67 @@ __host__ __device__ inline int az_legal_moves(const AzGame& g, const AzBoard<NW>
         }
         return n;
     }
-    // Gomoku: empty 8-neighbours of every stone, inserted in the reference's scan order.
-    uint8_t* tab = tab_a;
-    uint8_t* spare = tab_b;
-    uint32_t mask = 7;
-    int fill = 0;
-    for (int i = 0; i < 8; ++i) tab[i] = 0xFF;
+    // Gomoku: empty 8-neighbours of every stone, inserted in the reference's scan order.  Adding a
+    // key the set already holds changes nothing (no fill, no resize), so only the FIRST occurrence
+    // of a cell reaches the table: `blocked` = stones | cells already inserted is a bit test.
+    // Pass 1 lists the first occurrences in scan order (into `out`, reused below), pass 2 replays
+    // them through the table.
+    uint64_t blocked[NW];
+#pragma unroll
+    for (int wi = 0; wi < NW; ++wi) blocked[wi] = b.w[0][wi] | b.w[1][wi];
+    int ncand = 0;
     const int ddr[4] = {0, 1, 1, 1}, ddc[4] = {1, 0, 1, -1};
+#pragma unroll
     for (int wi = 0; wi < NW; ++wi) {
         uint64_t occ = b.w[0][wi] | b.w[1][wi];
         while (occ) {
             const int cell = wi * 64 + AZ_CTZ64(occ);
             occ &= occ - 1;
             const int r = cell / g.cols, c = cell - r * g.cols;
+#pragma unroll
             for (int d = 0; d < 4; ++d) {
+#pragma unroll
                 for (int s = 1; s >= -1; s -= 2) {
                     const int rr = r + s * ddr[d], cc = c + s * ddc[d];
                     if (rr < 0 || rr >= g.rows || cc < 0 || cc >= g.cols) continue;
                     const int x = rr * g.cols + cc;
-                    if (!b.empty(x)) continue;
-                    if (!az_set_insert(tab, mask, (uint8_t)x, cell_hash[x], true)) continue;
-                    ++fill;
-                    if ((uint32_t)fill * 5 >= mask * 3) {   // grow: smallest 2^k > 4*used
-                        uint32_t newsize = 8;
-                        while (newsize <= (uint32_t)fill * 4) newsize <<= 1;
-                        for (uint32_t i = 0; i < newsize; ++i) spare[i] = 0xFF;
-                        for (uint32_t i = 0; i <= mask; ++i)
-                            if (tab[i] != 0xFF) az_set_insert(spare, newsize - 1, tab[i], cell_hash[tab[i]], false);
-                        uint8_t* t = tab;
-                        tab = spare;
-                        spare = t;
-                        mask = newsize - 1;
+                    bool taken = false;
+                    if (NW == 1) {
+                        taken = (blocked[0] >> x) & 1;
+                        blocked[0] |= 1ull << x;
+                    } else {
+#pragma unroll
+                        for (int wj = 0; wj < NW; ++wj) {
+                            if (wj == (x >> 6)) {
+                                taken = (blocked[wj] >> (x & 63)) & 1;
+                                blocked[wj] |= 1ull << (x & 63);
+                            }
+                        }
                     }
+                    if (!taken) out[ncand++] = (uint8_t)x;
                 }
             }
+        }
+    }
+    uint8_t* tab = tab_a;
+    uint8_t* spare = tab_b;
+    uint32_t mask = 7;
+    int fill = 0;
+    for (int i = 0; i < 8; ++i) tab[i] = 0xFF;
+    for (int k = 0; k < ncand; ++k) {
+        const uint8_t x = out[k];
+        az_set_insert(tab, mask, x, cell_hash[x], false);
+        ++fill;
+        if ((uint32_t)fill * 5 >= mask * 3) {               // grow: smallest 2^k > 4*used
+            uint32_t newsize = 8;
+            while (newsize <= (uint32_t)fill * 4) newsize <<= 1;
+            for (uint32_t i = 0; i < newsize; ++i) spare[i] = 0xFF;
+            for (uint32_t i = 0; i <= mask; ++i)
+                if (tab[i] != 0xFF) az_set_insert(spare, newsize - 1, tab[i], cell_hash[tab[i]], false);
+            uint8_t* t = tab;
+            tab = spare;
+            spare = t;
+            mask = newsize - 1;
         }
     }
     if (fill == 0) {                                        // empty board: centre (gomoku.py:104-105)

@@ -37,8 +37,6 @@ struct __attribute__((aligned(16))) AzHot {
     float P;          // ai/node.py:36  prior (fp32, gathered from the unmasked softmax)
     uint32_t V;       // virtual-loss count (vl > 1 only)
 };
-// ai/node.py:34 value sum W (viewpoint of the player who moved in) lives in its own f64 array
-// (AzForestDev::wsum): only backups touch it.
 
 // Cold per-node record, read only for the selected child.
 struct __attribute__((aligned(8))) AzMeta {
@@ -46,6 +44,14 @@ struct __attribute__((aligned(8))) AzMeta {
     uint16_t action;      // cell index r*cols+c of the move that led here (prevAction)
     uint8_t nchild;
     uint8_t status;       // AZ_ST_*
+};
+
+// One node = one 32-byte sector: a child scan, a backup and an expansion each touch exactly one
+// sector per node and one address stream per tree (one TLB entry instead of three).
+struct __attribute__((aligned(32))) AzNode {
+    AzHot hot;        // offset 0:  what PUCT scores
+    AzMeta meta;      // offset 16: where the children are
+    double W;         // offset 24: ai/node.py:34 value sum (viewpoint of the player who moved in), f64 in visitation order
 };
 
 // One leaf handed to the evaluator: canonical side bitboards (mine = side to move).

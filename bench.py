@@ -115,6 +115,17 @@ def peaks():
         return dict(tflops=1400.0, hbm=6650.0, src="fallback (B200_PROFILING.md: ~1.4 PF sustained, 6.65 TB/s)")
 
 
+def ncu_traffic(kind, wl):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this
+    kernel on this workload (profiles/ncu_traffic.json names the capture file), else None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            t = json.load(f)
+        return t[kind][wl["name"]]["bytes"]
+    except Exception:
+        return None
+
+
 def roofline(wl, r, prof, pk, kind=None):
     """Roofline entry of one kernel kind (default: the kind with the largest share of the step).
     Algorithmic work per launch = per-leaf (or per-simulation) figure of DESIGN.md section 4 x the units of
@@ -126,9 +137,10 @@ def roofline(wl, r, prof, pk, kind=None):
     leaves = r["leaves_per_step"]
     per_step = {k: v["ms"] * (v["launches"] / max(prof["forest_advance"]["launches"], 1) if k != "forest_advance" else 1.0)
                 for k, v in prof.items()}
-    if kind is None:
-        kind = max(per_step, key=per_step.get)
+    if kind is None:                # dominant KERNEL: longest single launch (the three cls-row GEMMs are separate kernels)
+        kind = max(prof, key=lambda k: prof[k]["ms"])
     ms = prof[kind]["ms"]
+    traffic = ncu_traffic(kind, wl)
     st = r["stats"]
     flops = None
     if kind == "front_fused":       # one contraction over the K binary inputs per token: D value + H score + K Gram columns
@@ -142,14 +154,14 @@ def roofline(wl, r, prof, pk, kind=None):
     if flops is not None:
         ach = flops / (ms / 1e3) / 1e12
         return dict(kernel=name, bound="tensor", achieved=ach, peak=pk["tflops"], unit="TFLOP/s", frac=ach / pk["tflops"],
-                    traffic=None, peak_source=pk["src"], flops_per_launch=flops, ms_per_launch=ms, share_of_step=per_step[kind] / sum(per_step.values()))
+                    traffic=traffic, peak_source=pk["src"], flops_per_launch=flops, ms_per_launch=ms, share_of_step=per_step[kind] / sum(per_step.values()))
     if kind == "forest_advance":    # 16 B per child scored + 8 B header per select + 24 B RMW per path node + 26 B per child written
         sims = max(st["sims"], 1)
         per_sim = (16.0 * st["child_reads"] + 8.0 * st["selects"] + 24.0 * (st["selects"] + st["sims"]) + 26.0 * st["children"]) / sims
         nbytes = per_sim * wl["trees"] * wl["vl"]
         ach = nbytes / (ms / 1e3) / 1e9
         return dict(kernel="az_advance_kernel (PUCT select + expand + backup, one warp per tree)", bound="hbm", achieved=ach, peak=pk["hbm"],
-                    unit="GB/s", frac=ach / pk["hbm"], traffic=None, peak_source=pk["src"], bytes_per_sim=per_sim, bytes_per_launch=nbytes,
+                    unit="GB/s", frac=ach / pk["hbm"], traffic=traffic, peak_source=pk["src"], bytes_per_sim=per_sim, bytes_per_launch=nbytes,
                     ms_per_launch=ms, share_of_step=per_step[kind] / sum(per_step.values()))
     return None
 
@@ -196,15 +208,22 @@ def run_b200(args, wl, rank, world):
             dist.barrier()
             torch.cuda.synchronize()
 
+    e2e_parts = []
+
     def one_step(i, e2e):
         planes, players, mcs = roots[i]
+        ta = time.perf_counter()
         if e2e:
             np.copyto(pin_np, planes)                                 # the step's inputs start in pinned host memory
             forest.set_roots_planes(pin_np, players, mcs)             # H2D inside the timed region
         forest.set_noise(noise[i])
+        tb = time.perf_counter()
         forest.search_net(eng, iters)
+        tc = time.perf_counter()
         if e2e:
-            return forest.root_visits()                               # D2H of the step's result
+            out = forest.root_visits()                                # D2H of the step's result
+            e2e_parts.append((round((tb - ta) * 1e3, 2), round((tc - tb) * 1e3, 2), round((time.perf_counter() - tc) * 1e3, 2)))
+            return out
 
     clocks = ClockSampler(local)
     # ---- value: device time, inputs resident --------------------------------------------------
@@ -245,7 +264,8 @@ def run_b200(args, wl, rank, world):
         dev_ms, e2e_s = tm.tolist()
     sims_per_step = n * iters * world
     out = dict(dev_ms=dev_ms, e2e_s=e2e_s, sims_per_step=sims_per_step, gpu_launches=int(gpu_launches),
-               h2d=int(pinned.numel() * 4 + n * 8 + n * A * 8), d2h=int(n * A * 4 + n * 8), stats=stats)
+               h2d=int(pinned.numel() * 4 + n * 8 + n * A * 8), d2h=int(n * A * 4 + n * 8), stats=stats,
+               e2e_steps_ms=[dict(upload=a, search=b, readback=c) for a, b, c in e2e_parts[args.warmup:]])
     # ---- per-kernel profile (rank 0): eager steps of one search with CUDA events ------------------
     if rank == 0:
         planes, players, mcs = roots[-1]
@@ -316,7 +336,8 @@ def main():
     value = r["sims_per_step"] * args.steps / (r["dev_ms"] / 1e3)
     e2e = r["sims_per_step"] * args.steps / r["e2e_s"]
     line = dict(base, impl="b200", value=value, ms_per_step=r["dev_ms"] / args.steps, clocks=r["clocks"],
-                e2e=dict(value=e2e, unit="simulations/s", h2d_bytes_per_step=r["h2d"], d2h_bytes_per_step=r["d2h"]),
+                e2e=dict(value=e2e, unit="simulations/s", h2d_bytes_per_step=r["h2d"], d2h_bytes_per_step=r["d2h"],
+                         steps_ms=r["e2e_steps_ms"]),
                 gpu_launches=r["gpu_launches"], search_stats=r["stats"])
     prof = r.get("profile", {})
     if prof:

@@ -311,8 +311,10 @@ int azo_search(int gid, int rows, int cols, const uint8_t* cells_in, int player0
     const int stride = g.cells + 2;
     while (sims < iters) {
         /* phase B first (nothing is pending at loop entry): select up to vl leaves */
-        int np = 0, started = sims;
-        while (started < iters && np < vl) {
+        /* a step also closes after vl terminal descents (bounds the work of one step; at vl == 1 the
+         * order of simulations is unchanged because nothing is pending at that point) */
+        int np = 0, started = sims, nterm = 0;
+        while (started < iters && np < vl && nterm < vl) {
             int node = 0, len = 1;
             int* pth = path + np * stride;
             pth[0] = 0;
@@ -338,7 +340,7 @@ int azo_search(int gid, int rows, int cols, const uint8_t* cells_in, int player0
                     nd[pth[i]].visit++; nd[pth[i]].W += v; v = -v;
                     if (i >= 1) board[nd[pth[i]].cell] = 0;
                 }
-                st[0]++; st[1]++; started++; sims++;
+                st[0]++; st[1]++; started++; sims++; nterm++;
                 continue;
             }
             plen[np] = len;

@@ -66,8 +66,8 @@ def py_vl_search(g, ev, board, player, mc, iters, vl):
 
     sims = 0
     while sims < iters:
-        pend, started = [], sims
-        while started < iters and len(pend) < vl:
+        pend, started, nterm = [], sims, 0
+        while started < iters and len(pend) < vl and nterm < vl:       # a step closes after vl terminal descents too
             node, trace = root, [root]
             while node.children:
                 s32 = np.float32(np.sqrt(np.float64(node.visit + st(node)[0])))
@@ -94,6 +94,7 @@ def py_vl_search(g, ev, board, player, mc, iters, vl):
                 orc.backup(g, trace, term, board)
                 sims += 1
                 started += 1
+                nterm += 1
                 continue
             pri, val = ev(orc.canonical_board(g, board, node.player))
             moves = orc.valid_moves(g, board)
