@@ -142,6 +142,14 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
         rootb.w[0][w] = f.root_words[(size_t)tree * 2 * NW + w];
         rootb.w[1][w] = f.root_words[(size_t)tree * 2 * NW + NW + w];
     }
+    // the root's record is tracked in registers for the whole launch: every backup and every virtual
+    // loss passes through it, and a reload after the backup stores would cost a round trip per descent
+    AzMeta root_m = f.nodes[(size_t)tree * f.cap].meta;
+    int root_nv;
+    {
+        const AzHot hr = f.nodes[(size_t)tree * f.cap].hot;
+        root_nv = hr.N + (int)hr.V;
+    }
     if (!is_active || is_done) return;
     AZ_AT(0);                                                 // tree scalars + root words
     AZ_AT_COUNT(15, 1);
@@ -165,31 +173,52 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     unsigned st_sims = 0, st_term = 0, st_exp = 0, st_child = 0, st_sel = 0, st_reads = 0, st_coll = 0;
 
     // ---------------- phase A: expand + backup the evaluated leaves -----------------------
+    // Priors (lane a keeps prior a and a + 32) and the stored path (lane i keeps entries i and i + 32)
+    // of leaf j + 1 are fetched while leaf j is processed: one exposed round trip per leaf (the
+    // read-modify-write of the path nodes) instead of three.
+    const bool pre = (G == 32) && A <= 64 && f.max_depth <= 64;
     for (int j0 = 0; j0 < npend; j0 += LP) {
         const int nj = min(LP, npend - j0);
         int my_nc = 0, my_slot = 0, my_len = 0, my_action = 0;
         uint32_t my_leaf = 0;
         float my_val = 0.f;
-        if (lane < nj) {                                      // lane j: scalars + legal moves of leaf j0 + j
+        AzBoard<NW> pb_;
+        if (lane < nj) {                                      // lane j: scalars of leaf j0 + j
             const size_t pj = (size_t)tree * f.vl + j0 + lane;
-            AzBoard<NW> b;
 #pragma unroll
             for (int w = 0; w < NW; ++w) {
-                b.w[0][w] = f.pend_words[pj * 2 * NW + w];
-                b.w[1][w] = f.pend_words[pj * 2 * NW + NW + w];
+                pb_.w[0][w] = f.pend_words[pj * 2 * NW + w];
+                pb_.w[1][w] = f.pend_words[pj * 2 * NW + NW + w];
             }
             my_slot = f.leaf_slot[pj];
             my_len = f.path_len[pj];
             my_action = f.pend_action[pj];
+            my_leaf = f.pend_leaf[pj];
             my_val = f.values[my_slot];
-            my_leaf = f.path[pj * f.max_depth + my_len - 1];
+        }
+        float pa = 0.f, pb = 0.f;
+        uint32_t q0 = 0, q1 = 0;
+        auto fetch = [&](int j, float& xa, float& xb, uint32_t& y0, uint32_t& y1) {
+            const int slotx = __shfl_sync(gmask, my_slot, j, G);
+            const float* prx = f.priors + (size_t)slotx * A;
+            const uint32_t* gp = f.path + ((size_t)tree * f.vl + j0 + j) * f.max_depth;
+            xa = lane < A ? prx[lane] : 0.f;
+            xb = lane + 32 < A ? prx[lane + 32] : 0.f;
+            y0 = lane < f.max_depth ? gp[lane] : 0u;
+            y1 = lane + 32 < f.max_depth ? gp[lane + 32] : 0u;
+        };
+        if (pre) fetch(0, pa, pb, q0, q1);
+        if (lane < nj) {                                      // legal moves of leaf j0 + j (Gomoku: sequential set emulation)
             uint8_t* lm = s_lm + (size_t)lane * lm_bytes;
-            my_nc = az_legal_moves<NW>(g, b, f.cell_hash, lm + moves_pad, lm + moves_pad + g.set_slots, lm);
+            my_nc = az_legal_moves<NW>(g, pb_, f.cell_hash, lm + moves_pad, lm + moves_pad + g.set_slots, lm);
         }
         __syncwarp(gmask);                                    // move lists visible to the group
         AZ_AT(1);                                             // pending scalars + legal moves
         for (int j = 0; j < nj; ++j) {                        // in selection order: node numbering and f64 sums depend on it
             const size_t pj = (size_t)tree * f.vl + j0 + j;
+            float na = 0.f, nb = 0.f;
+            uint32_t r0 = 0, r1 = 0;
+            if (pre && j + 1 < nj) fetch(j + 1, na, nb, r0, r1);
             const int nc = __shfl_sync(gmask, my_nc, j, G);
             const int slot = __shfl_sync(gmask, my_slot, j, G);
             const int len = __shfl_sync(gmask, my_len, j, G);
@@ -202,48 +231,63 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             n_nodes += nc;
             const float* pri = f.priors + (size_t)slot * A;
             const bool noisy_root = (leaf == 0) && f.use_noise;
-            for (int c = lane; c < nc; c += G) {
-                const int cell = s_moves[c];
+            for (int c0 = 0; c0 < nc; c0 += G) {
+                const int c = c0 + lane;
+                const bool valid = c < nc;
+                const int cell = valid ? s_moves[c] : 0;
                 const int ai = az_action_index(g, cell);
-                float p = pri[ai];                               // node.py:57 gather, unmasked softmax
+                float p;                                         // node.py:57 gather, unmasked softmax
+                if (pre) {
+                    const float xa = __shfl_sync(gmask, pa, ai & 31, G);
+                    const float xb = A > 32 ? __shfl_sync(gmask, pb, ai & 31, G) : 0.f;
+                    p = ai < 32 ? xa : xb;
+                } else {
+                    p = valid ? pri[ai] : 0.f;
+                }
+                if (!valid) continue;
                 if (noisy_root) {                                // utils.py:24: f32*0.75 + f64 noise*0.25
                     const double p64 = __dadd_rn((double)__fmul_rn(0.75f, p),
                                                  __dmul_rn(0.25, f.root_noise[(size_t)tree * A + ai]));
                     f.root_prior64[(size_t)tree * g.max_children + c] = p64;
                     p = __double2float_rn(p64);                  // kept for reporting only
                 }
-                AzHot h;
-                h.N = 0;
-                h.Q = 0.f;
-                h.P = p;
-                h.V = 0;
-                hot[base + c] = h;
-                wsum[base + c] = 0.0;
-                AzMeta m;
-                m.child_base = 0;
-                m.action = (uint16_t)cell;
-                m.nchild = 0;
-                m.status = AZ_ST_LEAF;
-                meta[base + c] = m;
+                AzNode nn;
+                nn.hot.N = 0;
+                nn.hot.Q = 0.f;
+                nn.hot.P = p;
+                nn.hot.V = 0;
+                nn.meta.child_base = 0;
+                nn.meta.action = (uint16_t)cell;
+                nn.meta.nchild = 0;
+                nn.meta.status = AZ_ST_LEAF;
+                nn.W = 0.0;
+                uint4* dst = reinterpret_cast<uint4*>(&nodes[base + c]);   // one sector, two 16-byte stores
+                dst[0] = reinterpret_cast<const uint4*>(&nn)[0];
+                dst[1] = reinterpret_cast<const uint4*>(&nn)[1];
             }
-            if (lane == 0) {
+            {
                 AzMeta m;
                 m.child_base = base;
                 m.action = (uint16_t)action;
                 m.nchild = (uint8_t)nc;
                 m.status = AZ_ST_EXPANDED;
-                meta[leaf] = m;
+                if (lane == 0) meta[leaf] = m;
+                if (leaf == 0) root_m = m;
             }
             AZ_AT(2);                                             // child block written
             const double result = -(double)val;                   // mcts.py:56
-            for (int i = lane; i < len; i += G)                   // node.py:69-72
-                az_backup_node(hot, wsum, gpath[i], ((len - 1 - i) & 1) ? -result : result, use_vl);
+            for (int i = lane; i < len; i += G) {                 // node.py:69-72
+                const uint32_t nd = pre ? (i < 32 ? q0 : q1) : gpath[i];
+                az_backup_node(hot, wsum, nd, ((len - 1 - i) & 1) ? -result : result, use_vl);
+            }
+            root_nv += use_vl ? 0 : 1;                            // the root: N + 1, V - 1 under virtual loss
             __syncwarp(gmask);
             AZ_AT(3);                                             // backup
             ++st_exp;
             st_child += nc;
             ++st_sims;
             ++sims;
+            pa = na; pb = nb; q0 = r0; q1 = r1;
         }
     }
 
@@ -285,13 +329,9 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
         int player = root_player, mc = root_mc, len = 1;
         uint32_t node = 0;
         if (lane == 0) s_path[0] = 0;
-        AzMeta m = meta[0];
-        int pn;
-        {
-            const AzHot hr = hot[0];
-            pn = hr.N + (int)hr.V;
-        }
-        AZ_AT(4);                                             // root record
+        AzMeta m = root_m;
+        int pn = root_nv;
+        AZ_AT(4);                                             // root record (registers)
         // One memory round trip per level: every lane fetches hot AND meta of its children, the
         // winner's meta / visit count arrive by shuffle (mcts.py:20-23, node.py:42-47).
         while (m.status == AZ_ST_EXPANDED) {
@@ -371,6 +411,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             const double v = status == AZ_ST_WIN ? 1.0 : 0.0;
             for (int i = lane; i < len; i += G) az_backup_node(hot, wsum, s_path[i], ((len - 1 - i) & 1) ? -v : v, false);
             __syncwarp(gmask);
+            root_nv += 1;
             ++st_term;
             ++st_sims;
             ++started;
@@ -385,19 +426,20 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
         for (int i = lane; i < len; i += G) {
             const uint32_t nd = s_path[i];
             gpath[i] = nd;
-            if (use_vl) hot[nd].V += 1;
+            if (use_vl) atomicAdd(&nodes[nd].hot.V, 1u);      // fire-and-forget: nobody waits for the old count
         }
+        if (use_vl) root_nv += 1;
         if (lane == np - flushed) {
             kept = b;
             kept_player = player;
         }
+        if (use_vl) m.status = AZ_ST_PENDING;
+        if (node == 0) root_m = m;
         if (lane == 0) {
             f.path_len[pj] = (uint16_t)len;
             f.pend_action[pj] = m.action;
-            if (use_vl) {
-                m.status = AZ_ST_PENDING;
-                meta[node] = m;
-            }
+            f.pend_leaf[pj] = node;
+            if (use_vl) meta[node] = m;
         }
         if (np + 1 - flushed == G) {
             hand_off(np + 1);
@@ -424,7 +466,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
         unsigned v = 0;
 #pragma unroll
         for (int k = 0; k < 7; ++k) if (lane == k) v = vals[k];
-        if (v) f.stats[(size_t)tree * AZ_STAT_COUNT + lane] += v;
+        if (v) atomicAdd(&f.stats[(size_t)tree * AZ_STAT_COUNT + lane], (unsigned long long)v);   // no reply needed
     }
     AZ_AT(8);                                                 // tail writes
 #ifdef AZ_ADV_TRACE
@@ -643,6 +685,8 @@ struct az_forest {
     int smem_per_group = 0;
     std::vector<void*> allocs;
     double* noise_dev = nullptr;
+    int* vis_dev = nullptr;       // root_visits scratch [n_trees][A] + root Q [n_trees]
+    double* q_dev = nullptr;
     int* h_counts = nullptr;      // pinned: n_leaves, n_done
     void* h_stage = nullptr;      // pinned staging for roots
     size_t h_stage_bytes = 0;
@@ -785,6 +829,7 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     AZ_ALLOC(d.pend_player, (size_t)d.max_leaves);
     AZ_ALLOC(d.pend_mc, (size_t)d.max_leaves);
     AZ_ALLOC(d.pend_action, (size_t)d.max_leaves);
+    AZ_ALLOC(d.pend_leaf, (size_t)d.max_leaves);
     AZ_ALLOC(d.n_leaves, 4);
     d.n_done = d.n_leaves + 1;
     AZ_ALLOC(d.leaf_words, (size_t)d.max_leaves * 2 * nw);
@@ -795,6 +840,8 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     AZ_ALLOC(d.root_prior64, (size_t)n_trees * g.max_children);
     AZ_ALLOC(d.stats, (size_t)n_trees * AZ_STAT_COUNT);
     AZ_ALLOC(f->noise_dev, (size_t)n_trees * g.action_dim);
+    AZ_ALLOC(f->vis_dev, (size_t)n_trees * g.action_dim);
+    AZ_ALLOC(f->q_dev, (size_t)n_trees);
     AZ_ALLOC(f->planes_stage_dev, (size_t)n_trees * g.planes * g.state_dim);
     AZ_ALLOC(f->i32_stage_dev, (size_t)n_trees * 2);
     uint64_t* hash_dev = nullptr;
@@ -812,7 +859,7 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     cudaMemset(d.root_words, 0, (size_t)n_trees * 2 * nw * 8);
     cudaMemset(d.root_player, 0, n_trees);
     cudaMemset(d.root_mc, 0, (size_t)n_trees * 2);
-    f->h_stage_bytes = (size_t)n_trees * (size_t)std::max<size_t>((size_t)g.planes * g.state_dim * 4, (size_t)g.action_dim * 8) + 64;
+    f->h_stage_bytes = (size_t)n_trees * (size_t)std::max<size_t>((size_t)g.planes * g.state_dim * 4, (size_t)g.action_dim * 8 + 8) + 64;
     if (cudaMallocHost(&f->h_counts, 64) != cudaSuccess || cudaMallocHost(&f->h_stage, f->h_stage_bytes) != cudaSuccess) {
         az_forest_destroy(f);
         return az_fail(AZ_ENOMEM, "cudaMallocHost failed");
@@ -983,16 +1030,16 @@ extern "C" int az_forest_root_visits(az_forest* f, int32_t* visits_host, double*
     if (!f || !visits_host) return az_fail(AZ_EINVAL, "root_visits: null");
     cudaStream_t s = (cudaStream_t)stream;
     const int n = f->d.n_trees, A = f->d.g.action_dim;
-    int* vis_dev = nullptr;
-    double* q_dev = nullptr;
-    AZ_CUDA_OK(cudaMallocAsync(&vis_dev, (size_t)n * A * 4, s));
-    AZ_CUDA_OK(cudaMallocAsync(&q_dev, (size_t)n * 8, s));
-    az_root_visits_kernel<<<n, 64, 0, s>>>(f->d, vis_dev, q_dev);
-    AZ_CUDA_OK(cudaMemcpyAsync(visits_host, vis_dev, (size_t)n * A * 4, cudaMemcpyDeviceToHost, s));
-    if (q_host) AZ_CUDA_OK(cudaMemcpyAsync(q_host, q_dev, (size_t)n * 8, cudaMemcpyDeviceToHost, s));
-    AZ_CUDA_OK(cudaFreeAsync(vis_dev, s));
-    AZ_CUDA_OK(cudaFreeAsync(q_dev, s));
+    // device scratch and the pinned staging buffer are owned by the forest: a stream-ordered allocation
+    // per call let the pool trim and re-map memory at the synchronize (spikes of 20-300 ms per call)
+    int* h_vis = reinterpret_cast<int*>(f->h_stage);
+    double* h_q = reinterpret_cast<double*>(reinterpret_cast<char*>(f->h_stage) + (((size_t)n * A * 4 + 15) & ~(size_t)15));
+    az_root_visits_kernel<<<n, 64, 0, s>>>(f->d, f->vis_dev, f->q_dev);
+    AZ_CUDA_OK(cudaMemcpyAsync(h_vis, f->vis_dev, (size_t)n * A * 4, cudaMemcpyDeviceToHost, s));
+    if (q_host) AZ_CUDA_OK(cudaMemcpyAsync(h_q, f->q_dev, (size_t)n * 8, cudaMemcpyDeviceToHost, s));
     AZ_CUDA_OK(cudaStreamSynchronize(s));
+    memcpy(visits_host, h_vis, (size_t)n * A * 4);
+    if (q_host) memcpy(q_host, h_q, (size_t)n * 8);
     return AZ_OK;
 }
 

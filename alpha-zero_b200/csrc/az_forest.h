@@ -49,6 +49,7 @@ struct AzForestDev {
     uint64_t* pend_words;    // [n_trees][vl][2*nw]  leaf position (side 0, side 1)
     uint8_t* pend_player;
     uint16_t* pend_mc;
+    uint32_t* pend_leaf;     // node index of the pending leaf (= last path entry)
     uint16_t* pend_action;   // cell of the move that led to the leaf (meta.action, rewritten at expansion)
 
     // evaluation batch (compacted)

@@ -20,18 +20,43 @@ template <int NW>
 struct AzBoard {
     uint64_t w[2][NW];   // w[player][word]
 
+    // Player and word indices are data dependent; selecting with predicates instead of indexing keeps
+    // the board in registers (a dynamically indexed array is demoted to local memory).
+    __host__ __device__ __forceinline__ uint64_t word(int p, int i) const {
+        uint64_t v = 0;
+#pragma unroll
+        for (int k = 0; k < NW; ++k)
+            if (NW == 1 || k == i) v = p ? w[1][k] : w[0][k];
+        return v;
+    }
     __host__ __device__ __forceinline__ bool has(int p, int cell) const {
-        return (w[p][NW == 1 ? 0 : (cell >> 6)] >> (cell & 63)) & 1ull;
+        return (word(p, NW == 1 ? 0 : (cell >> 6)) >> (cell & 63)) & 1ull;
     }
     __host__ __device__ __forceinline__ bool empty(int cell) const {
         const int i = NW == 1 ? 0 : (cell >> 6);
-        return !(((w[0][i] | w[1][i]) >> (cell & 63)) & 1ull);
+        return !(((word(0, i) | word(1, i)) >> (cell & 63)) & 1ull);
     }
     __host__ __device__ __forceinline__ void put(int p, int cell) {
-        w[p][NW == 1 ? 0 : (cell >> 6)] |= 1ull << (cell & 63);
+        const uint64_t bit = 1ull << (cell & 63);
+        const int i = NW == 1 ? 0 : (cell >> 6);
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            if (NW == 1 || k == i) {
+                w[0][k] |= p ? 0ull : bit;
+                w[1][k] |= p ? bit : 0ull;
+            }
+        }
     }
     __host__ __device__ __forceinline__ void clear(int p, int cell) {
-        w[p][NW == 1 ? 0 : (cell >> 6)] &= ~(1ull << (cell & 63));
+        const uint64_t bit = 1ull << (cell & 63);
+        const int i = NW == 1 ? 0 : (cell >> 6);
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            if (NW == 1 || k == i) {
+                w[0][k] &= p ? ~0ull : ~bit;
+                w[1][k] &= p ? ~bit : ~0ull;
+            }
+        }
     }
 };
 

@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(PKG, "libaz_b200.so")
+SO_PATH = os.environ.get("AZ_B200_LIB") or os.path.join(PKG, "libaz_b200.so")   # AZ_B200_LIB: experiment builds (tools/)
 
 AZ_OK = 0
 GAME_IDS = {"tictactoe": 0, "connect4": 1, "gomoku": 2}
