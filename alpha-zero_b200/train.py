@@ -55,40 +55,92 @@ def save_data_to_buffer(Game, buffer, data):
                 buffer.add(*flip_data(b_rot, p_rot, "tb"), z)
 
 
-def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, return_visits=False):
-    """n_games concurrent self-play games; returns the reference's 5-tuple per game (and, on request,
-    the raw root visit counts per ply -- the compact form parallel.pack_games ships between ranks)."""
-    boards = np.stack([Game().board for _ in range(n_games)])
-    players = np.zeros(n_games, np.int32)
-    plies = np.zeros(n_games, np.int32)
-    alive = np.ones(n_games, np.uint8)
+def _moves_from_actions(Game, boards, acts):
+    """(row, col) of action index `acts[i]` on boards[i]: get_action_idx inverted for a whole batch
+    (games/connect4.py:27-41: the stone drops to the lowest empty row of the column)."""
+    if Game.name == "connect4":
+        n = np.arange(len(acts))
+        empty = (boards[:, 0] + boards[:, 1]) == 0                    # [n, rows, cols]
+        return empty[n, :, acts].sum(axis=1).astype(np.int64) - 1, acts.astype(np.int64)
+    return (acts // Game.cols).astype(np.int64), (acts % Game.cols).astype(np.int64)
+
+
+def _wins(Game, boards, movers, r, c):
+    """check_winner for a batch: a run of >= win_length of the mover's stones through (r, c)
+    (games/*: check_winner looks along the four lines through the last move only)."""
+    n = np.arange(len(r))
+    mine = boards[n, movers] == 1                                      # [n, rows, cols]
+    won = np.zeros(len(r), bool)
+    for dr, dc in ((0, 1), (1, 0), (1, 1), (1, -1)):
+        run = np.ones(len(r), np.int64)
+        for s in (1, -1):
+            going = np.ones(len(r), bool)
+            for k in range(1, Game.win_length):
+                rr, cc = r + s * k * dr, c + s * k * dc
+                ok = going & (rr >= 0) & (rr < Game.rows) & (cc >= 0) & (cc < Game.cols)
+                ok[ok] = mine[n[ok], rr[ok], cc[ok]]
+                run += ok
+                going = ok
+        won |= run >= Game.win_length
+    return won
+
+
+def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, return_visits=False, concurrent=None):
+    """n_games self-play games, `concurrent` of them in flight at once on the GPU forest (default: all);
+    a finished game's slot is refilled with the next game until n_games have been started.  Returns the
+    reference's 5-tuple per game in game order (and, on request, the raw root visit counts per ply --
+    the compact form parallel.pack_games ships between ranks).  Per ply the host does only batched NumPy
+    work: pi = visits / sum (utils.py:46-55), a move drawn from pi while ply < sample_until else the
+    most visited action (gomoku.py:143-147 / connect4.py:133), make_move, check_winner."""
+    C, R, W_, A = Game.feature_dim, Game.rows, Game.cols, Game.action_dim
+    slots = min(n_games, concurrent or n_games)
+    boards = np.zeros((slots, C, R, W_), np.float32)
+    players = np.zeros(slots, np.int32)
+    plies = np.zeros(slots, np.int32)
+    alive = np.ones(slots, np.uint8)
+    gid = np.arange(slots)                                             # game played in each slot
+    started = slots
     rec = [dict(boards=[], actions=[(-1, -1)], policies=[], qs=[], winner=-1, visits=[]) for _ in range(n_games)]
     sample_until = 8 if Game.name == "gomoku" else Game.state_dim + 1          # gomoku.py:143 / connect4.py:133
-    A = Game.action_dim
     while alive.any():
-        noise = np.random.dirichlet([0.03] * A, size=n_games) if dirichlet else None
+        noise = np.random.dirichlet([0.03] * A, size=slots) if dirichlet else None
         visits, q = MCTS.mcts_batch(model, boards, players, plies, Game, mcts_iter, noise=noise, vl=vl, active=alive)
-        for g in np.nonzero(alive)[0]:
-            pi = visits[g] / visits[g].sum()
-            r = rec[g]
-            r["policies"].append(pi)
-            r["visits"].append(visits[g].copy())
-            r["boards"].append(boards[g].copy())
-            r["qs"].append(q[g])
-            legal = {Game.get_action_idx(m): m for m in Game.get_valid_moves(boards[g])}
-            if plies[g] < sample_until:
-                a = int(np.random.choice(A, p=pi))
-            else:
-                a = int(np.argmax(visits[g]))           # ties: lowest action index (node.py:81 keeps child order)
-            move = legal[a]
-            mover = int(players[g])
-            players[g] = Game.make_move(boards[g], mover, move)
-            plies[g] += 1
-            r["actions"].append(move)
-            w = Game.check_winner(boards[g], mover, move)
-            if w != -1 or plies[g] == Game.state_dim:
-                r["winner"] = w
-                alive[g] = 0
+        live = np.nonzero(alive)[0]
+        vis = visits[live].astype(np.float64)
+        pi = vis / vis.sum(axis=1, keepdims=True)
+        # one uniform per game -> inverse-CDF draw from pi (np.random.choice's own method, vectorised)
+        u = np.random.random_sample(len(live))
+        cdf = np.cumsum(pi, axis=1)
+        cdf /= cdf[:, -1:]
+        drawn = (cdf < u[:, None]).sum(axis=1)
+        acts = np.where(plies[live] < sample_until, drawn, np.argmax(visits[live], axis=1))   # ties: lowest action index
+        snap = boards[live].copy()
+        r, c = _moves_from_actions(Game, snap, acts)
+        movers = players[live].astype(np.int64)
+        boards[live, movers, r, c] = 1
+        if C == 3:
+            boards[live, 2] = (1 - movers)[:, None, None]             # plane 2 = side to move next (connect4.py:55-70)
+        players[live] = 1 - movers
+        plies[live] += 1
+        won = _wins(Game, boards[live], movers, r, c)
+        over = won | (plies[live] == Game.state_dim)
+        for i, s in enumerate(live):
+            rg = rec[gid[s]]
+            rg["policies"].append(pi[i])
+            rg["visits"].append(visits[s].copy())
+            rg["boards"].append(snap[i])
+            rg["qs"].append(q[s])
+            rg["actions"].append((int(r[i]), int(c[i])))
+            if over[i]:
+                rg["winner"] = int(movers[i]) if won[i] else -1
+                if started < n_games:                                 # refill the slot with the next game
+                    gid[s] = started
+                    started += 1
+                    boards[s] = 0
+                    players[s] = 0
+                    plies[s] = 0
+                else:
+                    alive[s] = 0
     games = [(r["boards"], r["actions"], r["policies"], r["qs"], r["winner"]) for r in rec]
     if return_visits:
         return games, [np.stack(r["visits"]) for r in rec]

@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--cpu-procs", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-selfplay", action="store_true", help="skip the whole-game self-play leg (games/s)")
     return ap.parse_args()
 
 
@@ -295,6 +296,19 @@ def run_b200(args, wl, rank, world):
     out["clocks"] = clocks.summary(t_clock0, t_clock1)
     forest.close()
     eng.close()
+    # ---- whole games through the public API (train.play_games): games/s, SURVEY 8d ------------------
+    if rank == 0 and world == 1 and not args.no_selfplay:
+        from alpha_zero_b200 import train as az_train
+        np.random.seed(4321)
+        az_train.play_games(G, model, min(n, 256), min(iters, 32), vl=vl, concurrent=min(n, 256))   # warm-up: engine + forest of the small size
+        t0 = time.perf_counter()
+        games = az_train.play_games(G, model, n, iters, vl=vl, dirichlet=True, concurrent=n)
+        dt = time.perf_counter() - t0
+        plies = sum(len(g[0]) for g in games)
+        out["selfplay"] = dict(games=len(games), plies=plies, seconds=dt, games_per_s=len(games) / dt, positions_per_s=plies / dt,
+                               simulations_per_s=plies * iters / dt, sims_per_move=iters, concurrent=n,
+                               how="train.play_games: every game from the empty board to its end, Dirichlet noise on, moves "
+                                   "sampled / argmax as the reference, no refill (the batch thins out as games finish)")
     if world > 1:
         dist.destroy_process_group()
     return out
@@ -344,6 +358,8 @@ def main():
         line["kernel_ms"] = {k: round(v["ms"], 4) for k, v in prof.items()}
         line["roofline"] = roofline(wl, r, prof, pk)
         line["rooflines_all"] = {k: rl for k, rl in ((k, roofline(wl, r, prof, pk, k)) for k in prof) if rl}
+    if "selfplay" in r:
+        line["selfplay"] = r["selfplay"]
     if cb:
         line["cpu_baseline"] = cb
     print(json.dumps(line))

@@ -96,3 +96,34 @@ def test_collect_data_and_train_step_run_end_to_end():
         net.to("cpu")
         res2 = train.collect_data(G, net, buf, iterations=4, mcts_iter=16)      # weights changed: re-upload path
         assert sum(res2) == 4
+
+
+def test_play_games_batched_with_refill_is_self_consistent():
+    """train.play_games keeps `concurrent` games in flight and refills finished slots.  Every recorded
+    game must replay under the scalar rules of the Game class: boards follow from the actions, the winner is
+    what check_winner says, policies are visit counts / (iters - 1), moves are legal."""
+    import torch
+    from alpha_zero_b200.ai import Net
+    from alpha_zero_b200.games import TicTacToe, Connect4, Gomoku
+    from alpha_zero_b200 import train
+    game_cls(orc.GOMOKU)
+    torch.manual_seed(1)
+    np.random.seed(1)
+    for G, iters, n, conc in ((TicTacToe, 24, 40, 12), (Connect4, 24, 24, 24), (Gomoku, 16, 20, 8)):
+        net = Net((G.rows, G.cols), 3, 64, G.action_dim, 8, 1, G.feature_dim, dropout=0.1)
+        games, visits = train.play_games(G, net, n, iters, dirichlet=True, return_visits=True, concurrent=conc)
+        assert len(games) == n
+        for (boards, actions, policies, qs, winner), vis in zip(games, visits):
+            assert len(boards) == len(policies) == len(qs) == len(actions) - 1 == len(vis) >= 1
+            b = G().board.copy()
+            player, w = 0, -1
+            for i, mv in enumerate(actions[1:]):
+                assert np.array_equal(boards[i], b)
+                assert tuple(mv) in [tuple(m) for m in G.get_valid_moves(b)]
+                assert vis[i].sum() == iters - 1 and np.allclose(policies[i], vis[i] / vis[i].sum())
+                assert vis[i][G.get_action_idx(mv)] > 0
+                mover = player
+                player = G.make_move(b, mover, mv)
+                w = G.check_winner(b, mover, mv)
+                assert (w != -1 or i + 1 == G.state_dim) == (i == len(boards) - 1)
+            assert winner == w
