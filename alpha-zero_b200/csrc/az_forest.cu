@@ -124,6 +124,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     const int grp = threadIdx.x / G;
     const int tree = blockIdx.x * (blockDim.x / G) + grp;
     const unsigned gmask = az_group_mask<G>();
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the evaluator's first kernel may queue behind this grid
     if (tree >= f.n_trees) return;
 #ifdef AZ_ADV_TRACE
     long long at_prev = clock64();

@@ -104,8 +104,14 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int items = az_batch_items(a.batch);
-    const int tiles = (items + a.nb - 1) / a.nb;
+    // The batch size lives in device memory and is written by the predecessor (the forest's advance
+    // kernel): each role runs its own prologue, then waits for the predecessor grid and reads it.
+    int items = 0, tiles = 0;
+    auto wait_upstream = [&]() {
+        azptx::griddep_wait();
+        items = az_batch_items(a.batch);
+        tiles = (items + a.nb - 1) / a.nb;
+    };
     const int nslots = a.nslots;
 
     if (threadIdx.x < 16) {
@@ -137,6 +143,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
     azptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     // TMEM columns: [0, 128) stats accumulator, value slots of NTP columns from 128 on.
+    azptx::griddep_launch();                                         // the successor's CTAs may queue behind this grid
 
     if (warp >= 14) {
         // ------------------------------ weights in once (warp 15), then MMA issue -----------------------
@@ -148,7 +155,6 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                 for (int kb = 0; kb < KB; ++kb)
                     azptx::tma_load_2d(s_wv + ((size_t)fb * KB + kb) * 16384, &tm_wv, w_full, kb * 64, fb * 128);
         }
-        azptx::mbar_wait(w_full, 0);
         const uint32_t idesc_st = azptx::umma_idesc_bf16(128, (uint32_t)NS);
         const uint32_t idesc_v = azptx::umma_idesc_bf16(128, (uint32_t)NTP);
         // The issuing thread is the pacemaker of the tensor pipe: every descriptor is formed once, outside
@@ -168,6 +174,8 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         }
         const int mine = lead ? 0 : 1;                               // parity of the value blocks this warp issues
         int it = 0, slot = 0, round = 0;                           // value-block counter g = round * nslots + slot
+        azptx::mbar_wait(w_full, 0);
+        wait_upstream();
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it & 1;
             AZ_TR1(0, 0);
@@ -260,7 +268,6 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                 }
             }
         };
-        fetch(blockIdx.x, w_cur, s_cur);
         // The one-hot columns of a row never change and pad rows stay zero: both stages are initialised once;
         // per tile only the chunks (8 K columns = 16 bytes) that hold tap columns are rewritten.
         const int nch = (a.kc + 7) >> 3;
@@ -280,6 +287,8 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                     }
                 }
         }
+        wait_upstream();                                             // boards and batch size come from the predecessor
+        fetch(blockIdx.x, w_cur, s_cur);
         int it = 0;
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it & 1;
@@ -344,6 +353,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         const int pb = pair_on ? pair / H : 0, ph = pair_on ? pair - pb * H : 0;
         const float inv_d = 1.0f / (float)D;
         const int ne = (TS + tpp - 1) / tpp;                         // tokens per softmax thread (<= 8, checked on the host)
+        wait_upstream();
         int it = 0;
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int buf = it & 1;
@@ -428,6 +438,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         const uint32_t tq = tmem_base + ((uint32_t)((vw & 3) * 32) << 16);
         const int hd = D / a.H;
         int it = 0, slot0 = 0, round0 = 0;                           // block counter at fb = 0 of the current tile
+        wait_upstream();
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int buf = it & 1;
             const float* swb = s_w + buf * 8 * 128;

@@ -101,10 +101,7 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int M = az_gemm_rows(args);
-    const int m_tiles = (M + Cfg::BM - 1) / Cfg::BM;
     const int n_tiles = args.N / BN;
-    const int total = m_tiles * n_tiles;
     const int kblocks = args.K / Cfg::BK;
 
     if (warp == 0 && lane == 0) {
@@ -125,6 +122,13 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     __syncthreads();
     azptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // Programmatic dependent launch: everything above overlapped the predecessor's tail; its outputs
+    // (the A rows, the row statistics and the device-side row count) are read only from here on.
+    azptx::griddep_wait();
+    azptx::griddep_launch();
+    const int M = az_gemm_rows(args);
+    const int m_tiles = (M + Cfg::BM - 1) / Cfg::BM;
+    const int total = m_tiles * n_tiles;
 
     if (warp == 0) {
         if (lane == 0) {                                      // ---- TMA producer

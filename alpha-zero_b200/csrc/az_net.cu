@@ -85,6 +85,25 @@ static int az_pick_bn_small_m(int N, int max_rows) {
     return best ? best : az_pick_bn(N);
 }
 
+// Launch with programmatic stream serialization: the kernel may begin (prologue only -- it calls
+// griddepcontrol.wait before touching its inputs) while its predecessor in the stream drains.
+// AZ_NO_PDL=1 falls back to fully serialised launches.
+template <typename... KArgs, typename... Args>
+static cudaError_t az_launch_pdl(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t s, Args&&... args) {
+    static const bool pdl = !getenv("AZ_NO_PDL");
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3((unsigned)block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 template <int BN, int EPI>
 static int az_launch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& a, int max_rows, cudaStream_t s) {
     constexpr int smem = AzGemmCfg<BN>::SMEM + (EPI == AZ_EPI_HEAD ? AZ_HEAD_STAGE_BYTES : 0);
@@ -100,7 +119,7 @@ static int az_launch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const 
     }
     const int tiles = ((max_rows + 127) / 128) * (a.N / BN);
     const int grid = tiles < g_num_sms ? (tiles > 0 ? tiles : 1) : g_num_sms;
-    az_gemm_kernel<BN, EPI><<<grid, AZ_GEMM_THREADS, smem, s>>>(ta, tb, a);
+    AZ_CUDA_OK(az_launch_pdl(az_gemm_kernel<BN, EPI>, grid, AZ_GEMM_THREADS, smem, s, ta, tb, a));
     AZ_CUDA_OK(cudaGetLastError());
     return AZ_OK;
 }
@@ -849,7 +868,7 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
             AZ_CUDA_OK(cudaFuncSetAttribute(az_front_kernel<TS8_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
             done = true;                                                                                                   \
         }                                                                                                                  \
-        az_front_kernel<TS8_><<<grid, AZ_FRONT_THREADS, smem, s>>>(n->tm_fwst, n->tm_fwv, fa);                                          \
+        AZ_CUDA_OK(az_launch_pdl(az_front_kernel<TS8_>, grid, AZ_FRONT_THREADS, smem, s, n->tm_fwst, n->tm_fwv, fa));                   \
     } break;
             switch (fa.TS / 8) {
                 AZ_FRONT(1) AZ_FRONT(2) AZ_FRONT(3) AZ_FRONT(4) AZ_FRONT(5) AZ_FRONT(6) AZ_FRONT(7) AZ_FRONT(8)
