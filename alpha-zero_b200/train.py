@@ -8,6 +8,7 @@ reference's Adam + soft-target CE + MSE + explicit L2 step (train.py:85-123), wi
 NCCL gradient all-reduce when torch.distributed is initialised.
 """
 import time
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 import torch
@@ -100,10 +101,19 @@ def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, return_vis
     alive = np.ones(slots, np.uint8)
     gid = np.arange(slots)                                             # game played in each slot
     started = slots
-    rec = [dict(boards=[], actions=[(-1, -1)], policies=[], qs=[], winner=-1, visits=[]) for _ in range(n_games)]
+    winners = np.full(n_games, -1, np.int64)
+    log = dict(gid=[], snap=[], pi=[], vis=[], q=[], r=[], c=[])       # one entry per ply: arrays over the live games
     sample_until = 8 if Game.name == "gomoku" else Game.state_dim + 1          # gomoku.py:143 / connect4.py:133
+    # Dirichlet noise of the NEXT ply is drawn by a helper thread while the GPU searches (small-alpha gamma
+    # sampling is the most expensive host step); its generator is seeded from the global RNG, so runs repeat.
+    noise_rng = np.random.default_rng(np.random.randint(0, 2 ** 31 - 1, size=4))
+    pool = ThreadPoolExecutor(1) if dirichlet else None
+    draw = (lambda: noise_rng.dirichlet([0.03] * A, size=slots)) if dirichlet else None
+    pending = pool.submit(draw) if dirichlet else None
     while alive.any():
-        noise = np.random.dirichlet([0.03] * A, size=slots) if dirichlet else None
+        noise = pending.result() if dirichlet else None
+        if dirichlet:
+            pending = pool.submit(draw)
         visits, q = MCTS.mcts_batch(model, boards, players, plies, Game, mcts_iter, noise=noise, vl=vl, active=alive)
         live = np.nonzero(alive)[0]
         vis = visits[live].astype(np.float64)
@@ -112,7 +122,7 @@ def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, return_vis
         u = np.random.random_sample(len(live))
         cdf = np.cumsum(pi, axis=1)
         cdf /= cdf[:, -1:]
-        drawn = (cdf < u[:, None]).sum(axis=1)
+        drawn = np.minimum((cdf < u[:, None]).sum(axis=1), A - 1)
         acts = np.where(plies[live] < sample_until, drawn, np.argmax(visits[live], axis=1))   # ties: lowest action index
         snap = boards[live].copy()
         r, c = _moves_from_actions(Game, snap, acts)
@@ -124,26 +134,34 @@ def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, return_vis
         plies[live] += 1
         won = _wins(Game, boards[live], movers, r, c)
         over = won | (plies[live] == Game.state_dim)
-        for i, s in enumerate(live):
-            rg = rec[gid[s]]
-            rg["policies"].append(pi[i])
-            rg["visits"].append(visits[s].copy())
-            rg["boards"].append(snap[i])
-            rg["qs"].append(q[s])
-            rg["actions"].append((int(r[i]), int(c[i])))
-            if over[i]:
-                rg["winner"] = int(movers[i]) if won[i] else -1
-                if started < n_games:                                 # refill the slot with the next game
-                    gid[s] = started
-                    started += 1
-                    boards[s] = 0
-                    players[s] = 0
-                    plies[s] = 0
-                else:
-                    alive[s] = 0
-    games = [(r["boards"], r["actions"], r["policies"], r["qs"], r["winner"]) for r in rec]
+        for k, v in (("gid", gid[live].copy()), ("snap", snap), ("pi", pi), ("vis", visits[live]), ("q", q[live]), ("r", r), ("c", c)):
+            log[k].append(v)
+        done = live[over]
+        winners[gid[done]] = np.where(won[over], movers[over], -1)
+        for s in done:                                                # refill the slot with the next game, or retire it
+            if started < n_games:
+                gid[s] = started
+                started += 1
+                boards[s] = 0
+                players[s] = 0
+                plies[s] = 0
+            else:
+                alive[s] = 0
+    if pool is not None:
+        pending.cancel()
+        pool.shutdown(wait=True)
+    # per-game records: a game lives in one slot through consecutive plies, so a stable sort by game id keeps ply order
+    cat = {k: np.concatenate(v) for k, v in log.items()}
+    order = np.argsort(cat["gid"], kind="stable")
+    cuts = np.cumsum(np.bincount(cat["gid"], minlength=n_games))[:-1]
+    part = {k: np.split(v[order], cuts) for k, v in cat.items()}
+    games, all_visits = [], []
+    for g in range(n_games):
+        actions = [(-1, -1)] + list(zip(part["r"][g].tolist(), part["c"][g].tolist()))          # gomoku.py:128
+        games.append((list(part["snap"][g]), actions, list(part["pi"][g]), part["q"][g].tolist(), int(winners[g])))
+        all_visits.append(part["vis"][g])
     if return_visits:
-        return games, [np.stack(r["visits"]) for r in rec]
+        return games, all_visits
     return games
 
 

@@ -302,13 +302,14 @@ def run_b200(args, wl, rank, world):
         np.random.seed(4321)
         az_train.play_games(G, model, min(n, 256), min(iters, 32), vl=vl, concurrent=min(n, 256))   # warm-up: engine + forest of the small size
         t0 = time.perf_counter()
-        games = az_train.play_games(G, model, n, iters, vl=vl, dirichlet=True, concurrent=n)
+        games = az_train.play_games(G, model, 2 * n, iters, vl=vl, dirichlet=True, concurrent=n)
         dt = time.perf_counter() - t0
         plies = sum(len(g[0]) for g in games)
         out["selfplay"] = dict(games=len(games), plies=plies, seconds=dt, games_per_s=len(games) / dt, positions_per_s=plies / dt,
                                simulations_per_s=plies * iters / dt, sims_per_move=iters, concurrent=n,
                                how="train.play_games: every game from the empty board to its end, Dirichlet noise on, moves "
-                                   "sampled / argmax as the reference, no refill (the batch thins out as games finish)")
+                                   "sampled / argmax as the reference; 2 x concurrent games, a finished game's slot is refilled until all have "
+                                   "started (the batch thins out only at the end)")
     if world > 1:
         dist.destroy_process_group()
     return out
