@@ -251,20 +251,39 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                 const int rr = cr + kr - half;
                 if (rr >= 0 && rr < a.rows) inb |= (((colmask >> r_rs[pass]) << r_ls[pass]) & pmask) << (kr * P);
             }
-            r_inb[pass] = inb;
+            r_inb[pass] = (r_on[pass] && t > 0) ? inb : 0u;
+        }
+        // per (row, window row): where the board row starts in the bitboard and whether it exists; window rows
+        // beyond the patch or outside the board get an empty column mask, so the per-tile encode below has no
+        // branches and its 20 extractions are independent of each other
+        int g_sh[2][5];
+        uint32_t g_cm[2][5];
+        int g_ks[5];
+#pragma unroll
+        for (int kr = 0; kr < 5; ++kr) {
+            g_ks[kr] = kr < P ? kr * P : 0;
+#pragma unroll
+            for (int pass = 0; pass < 2; ++pass) {
+                const int rr = r_cr[pass] + kr - half;
+                const bool ok = kr < P && rr >= 0 && rr < a.rows && r_on[pass] && r_t[pass] > 0;
+                g_sh[pass][kr] = ok ? rr * a.cols : 0;
+                g_cm[pass][kr] = ok ? colmask : 0u;
+            }
         }
         // boards of the tile (side bitboards + side to move), fetched one tile ahead
+        // Only the loads are issued here; nothing consumes the loaded registers until the next tile is
+        // encoded (a compare right after the load would stall the warp for the whole memory latency).
         ulonglong2 w_cur[2], w_nxt[2];
-        uint32_t s_cur[2], s_nxt[2];
+        uint32_t s_cur[2], s_nxt[2];                                 // raw side-to-move byte, or 0xFFFFFFFF = row unused / board beyond the batch
         auto fetch = [&](int tile, ulonglong2 (&w)[2], uint32_t (&sm)[2]) {
 #pragma unroll
             for (int pass = 0; pass < 2; ++pass) {
                 const int item = tile * a.nb + r_b[pass];
                 w[pass] = make_ulonglong2(0ull, 0ull);
-                sm[pass] = 2u;                                       // 2 = row unused / board beyond the batch
+                sm[pass] = 0xFFFFFFFFu;
                 if (tile < tiles && r_on[pass] && item < items) {
                     w[pass] = *reinterpret_cast<const ulonglong2*>(a.leaf_words + (size_t)(a.batch.offset + item) * 2);
-                    sm[pass] = (a.planes == 3 && a.leaf_player[a.batch.offset + item] != 0) ? 1u : 0u;
+                    sm[pass] = a.leaf_player[a.batch.offset + item];
                 }
             }
         };
@@ -293,29 +312,32 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it & 1;
             fetch(tile + gridDim.x, w_nxt, s_nxt);                   // in flight while this tile is encoded
-            unsigned __int128 kms[2];
+            // K columns of a row as two 64-bit words: taps of plane 0 at bit 0, plane 1 at bit pp, plane 2
+            // (in-bounds taps when side 1 is to move) at bit 2*pp, one-hot token index at bit kc + t
+            uint64_t kw0[2], kw1[2];
 #pragma unroll
             for (int pass = 0; pass < 2; ++pass) {
-                unsigned __int128 km = 0;
-                if (r_on[pass]) {
-                    const int t = r_t[pass];
-                    km = (unsigned __int128)1 << (a.kc + t);         // one-hot token index -> pos-emb / bias row
-                    if (t > 0 && s_cur[pass] != 2u) {                // (boards beyond the batch keep an empty window)
-                        uint32_t p0 = 0, p1 = 0;                     // taps of planes 0 / 1, bit kr*P + kcol  (P*P <= 32)
-#pragma unroll 5
-                        for (int kr = 0; kr < P; ++kr) {
-                            const int rr = r_cr[pass] + kr - half;
-                            if (rr < 0 || rr >= a.rows) continue;
-                            const int sh = rr * a.cols;
-                            const uint32_t b0 = (uint32_t)(w_cur[pass].x >> sh) & colmask, b1 = (uint32_t)(w_cur[pass].y >> sh) & colmask;
-                            p0 |= (((b0 >> r_rs[pass]) << r_ls[pass]) & pmask) << (kr * P);
-                            p1 |= (((b1 >> r_rs[pass]) << r_ls[pass]) & pmask) << (kr * P);
-                        }
-                        km |= (unsigned __int128)p0 | ((unsigned __int128)p1 << pp);
-                        if (s_cur[pass] == 1u) km |= (unsigned __int128)r_inb[pass] << (2 * pp);
+                const int ob = a.kc + r_t[pass];
+                uint64_t k0 = ob < 64 ? 1ull << ob : 0ull, k1 = ob >= 64 ? 1ull << (ob - 64) : 0ull;
+                {
+                    // (boards beyond the batch were fetched as empty bitboards: their window stays empty)
+                    uint32_t p0 = 0, p1 = 0;                         // taps of planes 0 / 1, bit kr*P + kcol  (P*P <= 32)
+#pragma unroll
+                    for (int kr = 0; kr < 5; ++kr) {
+                        const uint32_t b0 = (uint32_t)(w_cur[pass].x >> g_sh[pass][kr]) & g_cm[pass][kr];
+                        const uint32_t b1 = (uint32_t)(w_cur[pass].y >> g_sh[pass][kr]) & g_cm[pass][kr];
+                        p0 |= (((b0 >> r_rs[pass]) << r_ls[pass]) & pmask) << g_ks[kr];
+                        p1 |= (((b1 >> r_rs[pass]) << r_ls[pass]) & pmask) << g_ks[kr];
+                    }
+                    k0 |= (uint64_t)p0 | ((uint64_t)p1 << pp);
+                    if (a.planes == 3 && s_cur[pass] != 0u && s_cur[pass] != 0xFFFFFFFFu) {   // side 1 to move; the taps may straddle bit 64
+                        const uint64_t inb = r_inb[pass];
+                        k0 |= inb << (2 * pp);
+                        if (3 * pp > 64) k1 |= inb >> (64 - 2 * pp);
                     }
                 }
-                kms[pass] = km;
+                kw0[pass] = k0;
+                kw1[pass] = k1;
             }
             AZ_TR(1, 0);
             azptx::mbar_wait(&a_empty[st], ((it >> 1) & 1) ^ 1);
@@ -326,12 +348,18 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                 if (r >= NTP || !r_on[pass] || r_t[pass] == 0) continue;     // pad rows and the cls row never change
                 unsigned char* arow = s_a + (size_t)st * KB * tile_bytes + (size_t)r * 128;
                 const int sw = r & 7;
-                for (int gc = 0; gc < nch; ++gc) {
-                    const int kb = gc >> 3, c = gc & 7;
-                    const uint64_t kw = kb == 0 ? (uint64_t)kms[pass] : (uint64_t)(kms[pass] >> 64);
-                    const uint32_t by = (uint32_t)(kw >> (c * 8)) & 0xFFu;
+                const int n0 = nch < 8 ? nch : 8;
+#pragma unroll 4
+                for (int c = 0; c < n0; ++c) {
+                    const uint32_t by = (uint32_t)(kw0[pass] >> (c * 8)) & 0xFFu;
                     const uint2 lo = s_lut[by & 15u], hi = s_lut[by >> 4];
-                    *reinterpret_cast<uint4*>(arow + (size_t)kb * tile_bytes + ((c ^ sw) << 4)) = make_uint4(lo.x, lo.y, hi.x, hi.y);
+                    *reinterpret_cast<uint4*>(arow + ((c ^ sw) << 4)) = make_uint4(lo.x, lo.y, hi.x, hi.y);
+                }
+#pragma unroll 2
+                for (int c = 0; c < nch - 8; ++c) {
+                    const uint32_t by = (uint32_t)(kw1[pass] >> (c * 8)) & 0xFFu;
+                    const uint2 lo = s_lut[by & 15u], hi = s_lut[by >> 4];
+                    *reinterpret_cast<uint4*>(arow + (size_t)tile_bytes + ((c ^ sw) << 4)) = make_uint4(lo.x, lo.y, hi.x, hi.y);
                 }
             }
             azptx::fence_proxy_async();                              // generic-proxy writes -> visible to the MMA
@@ -411,6 +439,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                     mx = fmaxf(mx, sc[i]);
                 }
                 for (int o = tpp >> 1; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                AZ_TR(2, 6);
                 float sum = 0.f;
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
@@ -418,6 +447,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                     sum += sc[i];
                 }
                 for (int o = tpp >> 1; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                AZ_TR(2, 7);
                 const float inv = 1.0f / sum;
                 if (pair_on) {
 #pragma unroll

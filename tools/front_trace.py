@@ -23,4 +23,4 @@ names = ["mma", "builder", "S", "V"]
 for it in range(0, 14):
     for r in range(4):
         ev = [int(v - t0) if v else -1 for v in out[r, it]]
-        print(f"it {it:2d} {names[r]:8s}", ev[:6])
+        print(f"it {it:2d} {names[r]:8s}", ev[:8])
