@@ -51,6 +51,11 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "r"(taddr));
 }
+// After tcgen05.wait::ld: ties the destination registers of an earlier tcgen05.ld to this point of the
+// volatile-asm order, so the compiler cannot schedule their consumers above the wait.
+__device__ __forceinline__ void tmem_regs_ready(uint32_t (&r)[8]) {
+    asm volatile("" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]));
+}
 __device__ __forceinline__ void bar_sync_named(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
@@ -425,30 +430,49 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
             {
                 float* sw = swb + ph * 128 + pb * TS;
                 const float* sq = sqb + pb * TS;
-                float sc[8], rs[8];
-                float mx = -1e30f;
+                // branch-free: every thread reads 8 (clamped) positions first, then runs 8 independent
+                // rsqrt / exp chains; invalid positions are masked by select, not skipped by a branch
+                float sc[8], rs[8], qv[8], wv[8];
+                bool ok[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const int t = sub + i * tpp;
-                    sc[i] = -1e30f;
-                    rs[i] = 0.f;
-                    if (i < ne && t < T) {
-                        rs[i] = rsqrtf(sq[t] * inv_d + 1e-5f);
-                        sc[i] = sw[t] * rs[i];
-                    }
+                    ok[i] = i < ne && t < T;
+                    const int tt = ok[i] ? t : 0;
+                    qv[i] = sq[tt];
+                    wv[i] = sw[tt];
+                }
+                float mx = -1e30f;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    float r;
+                    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaf(qv[i], inv_d, 1e-5f)));
+                    rs[i] = ok[i] ? r : 0.f;
+                    sc[i] = ok[i] ? wv[i] * r : -1e30f;
                     mx = fmaxf(mx, sc[i]);
                 }
-                for (int o = tpp >> 1; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+#pragma unroll
+                for (int o = 16; o; o >>= 1) {
+                    const float v = __shfl_xor_sync(0xffffffffu, mx, o);
+                    if (o < tpp) mx = fmaxf(mx, v);
+                }
                 AZ_TR(2, 6);
                 float sum = 0.f;
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    sc[i] = (i < ne && sub + i * tpp < T) ? __expf(sc[i] - mx) : 0.f;
+                    float e;
+                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"((sc[i] - mx) * 1.4426950408889634f));
+                    sc[i] = ok[i] ? e : 0.f;
                     sum += sc[i];
                 }
-                for (int o = tpp >> 1; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+#pragma unroll
+                for (int o = 16; o; o >>= 1) {
+                    const float v = __shfl_xor_sync(0xffffffffu, sum, o);
+                    if (o < tpp) sum += v;
+                }
                 AZ_TR(2, 7);
-                const float inv = 1.0f / sum;
+                float inv;
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(sum));
                 if (pair_on) {
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
@@ -486,7 +510,53 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                     const float bias = __ldg(a.bias_v + f);
                     const uint32_t tcol = tq + 128 + slot * NTP;
                     bf16* dst = a.oc + (size_t)tile * a.nb * D + f;
-                    constexpr int NBV = TS8 >= 5 ? 1 : (8 / TS8 > 4 ? 4 : 8 / TS8);   // boards fetched per TMEM round trip
+                    if constexpr (TS8 >= 5) {
+                        // Long token strides: a board is read in two halves, the second half (and then the next
+                        // board's first half) is in flight from TMEM while the previous one is accumulated.
+                        constexpr int H0 = (TS8 + 1) / 2, H1 = TS8 - H0;
+                        uint32_t va[H0][8], vb[H1][8];
+                        auto acc_half = [&](const float* wr, auto& v, auto nh, float& a0, float& a1, float& a2, float& a3) {
+                            constexpr int NH = decltype(nh)::value;
+#pragma unroll
+                            for (int j = 0; j < NH; ++j) {
+                                const float4 w0 = *reinterpret_cast<const float4*>(wr + j * 8);
+                                const float4 w1 = *reinterpret_cast<const float4*>(wr + j * 8 + 4);
+                                a0 = fmaf(w0.x, __uint_as_float(v[j][0]), fmaf(w1.x, __uint_as_float(v[j][4]), a0));
+                                a1 = fmaf(w0.y, __uint_as_float(v[j][1]), fmaf(w1.y, __uint_as_float(v[j][5]), a1));
+                                a2 = fmaf(w0.z, __uint_as_float(v[j][2]), fmaf(w1.z, __uint_as_float(v[j][6]), a2));
+                                a3 = fmaf(w0.w, __uint_as_float(v[j][3]), fmaf(w1.w, __uint_as_float(v[j][7]), a3));
+                            }
+                        };
+#pragma unroll
+                        for (int j = 0; j < H0; ++j) azptx::tmem_ld8(tcol + j * 8, va[j]);
+                        azptx::tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < H0; ++j) azptx::tmem_regs_ready(va[j]);
+                        for (int b = 0; b < a.nb; ++b) {
+#pragma unroll
+                            for (int j = 0; j < H1; ++j) azptx::tmem_ld8(tcol + b * TS + (H0 + j) * 8, vb[j]);
+                            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+                            acc_half(wrow + b * TS, va, std::integral_constant<int, H0>(), a0, a1, a2, a3);
+                            azptx::tmem_ld_wait();
+#pragma unroll
+                            for (int j = 0; j < H1; ++j) azptx::tmem_regs_ready(vb[j]);
+                            if (b + 1 < a.nb) {
+#pragma unroll
+                                for (int j = 0; j < H0; ++j) azptx::tmem_ld8(tcol + (b + 1) * TS + j * 8, va[j]);
+                            } else {                                 // slot fully read: hand it back to the MMA warp
+                                azptx::tc_fence_before();
+                                azptx::mbar_arrive(&v_empty[slot]);
+                            }
+                            acc_half(wrow + b * TS + H0 * 8, vb, std::integral_constant<int, H1>(), a0, a1, a2, a3);
+                            if (tile * a.nb + b < items) dst[(size_t)b * D] = __float2bfloat16((a0 + a1) + (a2 + a3) + bias);
+                            if (b + 1 < a.nb) {
+                                azptx::tmem_ld_wait();
+#pragma unroll
+                                for (int j = 0; j < H0; ++j) azptx::tmem_regs_ready(va[j]);
+                            }
+                        }
+                    } else {
+                    constexpr int NBV = 8 / TS8 > 4 ? 4 : 8 / TS8;   // boards fetched per TMEM round trip
                     for (int b0 = 0; b0 < a.nb; b0 += NBV) {
                         uint32_t v[NBV][TS8][8];
 #pragma unroll
@@ -517,6 +587,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                                 if (tile * a.nb + b < items) dst[(size_t)b * D] = __float2bfloat16((a0 + a1) + (a2 + a3) + bias);
                             }
                         }
+                    }
                     }
                 }
                 if (++slot == nslots) { slot = 0; ++round; }
