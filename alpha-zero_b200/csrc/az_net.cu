@@ -622,6 +622,9 @@ extern "C" int az_net_finalize(az_net* n) {
             fa.KB = KB;
             fa.ksteps = (kused + 15) / 16;
             fa.nslots = std::min(std::min(4, D / 128), 384 / fa.NTP);
+            // Slots must not rotate between the two value-issuing warps (a warp a whole use ahead of the other
+            // would alias the single parity bit of v_empty): even slot counts keep slot parity == block parity.
+            if (fa.nslots == 3 && !getenv("AZ_FRONT_SLOTS3")) fa.nslots = 2;
             fa.bias_v = n->f_bias_v;
             int tpp = 32;
             while (tpp * fa.nb * H > 128) tpp >>= 1;
