@@ -118,6 +118,10 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         tiles = (items + a.nb - 1) / a.nb;
     };
     const int nslots = a.nslots;
+    // Who issues the statistics MMAs: the lead value-issuing warp when every feature block owns a TMEM slot;
+    // builder warp 12 when slots are scarce (then the value issuers block on slots for long stretches and the S
+    // group, which paces the kernel, would wait behind them for its accumulator).
+    const bool bstats = a.nslots < (a.D >> 7);
 
     if (threadIdx.x < 16) {
         const uint32_t n = threadIdx.x;
@@ -130,7 +134,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
         azptx::mbar_init(w_full, 1);
         for (int i = 0; i < 2; ++i) {
             azptx::mbar_init(&a_full[i], AZ_FRONT_BUILDERS);
-            azptx::mbar_init(&a_empty[i], 2);
+            azptx::mbar_init(&a_empty[i], a.nslots < (a.D >> 7) ? 3 : 2);   // value-issuing warps (+ the statistics issuer, see below)
             azptx::mbar_init(&sw_full[i], 128);
             azptx::mbar_init(&sw_empty[i], 256);
         }
@@ -187,7 +191,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
             azptx::mbar_wait(&a_full[st], (it >> 1) & 1);
             AZ_TR1(0, 1);
             const uint64_t da0 = st ? d_a[1][0] : d_a[0][0], da1 = st ? d_a[1][1] : d_a[0][1];
-            if (lead) {
+            if (lead && !bstats) {
                 azptx::mbar_wait(st_empty, (it & 1) ^ 1);
                 AZ_TR1(0, 2);
                 azptx::tc_fence_after();
@@ -311,6 +315,18 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
                     }
                 }
         }
+        const bool stats_issuer = bstats && warp == 12;
+        const uint32_t idesc_st = azptx::umma_idesc_bf16(128, (uint32_t)NS);
+        uint64_t d_wst[2], d_as[2][2];
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+            const int kbe = kb < KB ? kb : 0;
+            d_wst[kb] = azptx::umma_desc_k128(azptx::smem_u32(s_wst + (size_t)kbe * NS * 128));
+#pragma unroll
+            for (int st = 0; st < 2; ++st)
+                d_as[st][kb] = azptx::umma_desc_k128(azptx::smem_u32(s_a + (size_t)st * KB * tile_bytes + (size_t)kbe * tile_bytes));
+        }
+        if (stats_issuer) azptx::mbar_wait(w_full, 0);               // statistic weights are in shared memory
         wait_upstream();                                             // boards and batch size come from the predecessor
         fetch(blockIdx.x, w_cur, s_cur);
         int it = 0;
@@ -370,6 +386,23 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front_kernel(const __g
             azptx::fence_proxy_async();                              // generic-proxy writes -> visible to the MMA
             azptx::mbar_arrive(&a_full[st]);
             AZ_TR(1, 2);
+            if (stats_issuer) {
+                azptx::mbar_wait(&a_full[st], (it >> 1) & 1);        // every builder thread has written its rows
+                azptx::mbar_wait(st_empty, (it & 1) ^ 1);            // the S group has read the previous tile's statistics
+                azptx::tc_fence_after();
+                if (azptx::elect_one()) {
+                    const uint64_t da0 = st ? d_as[1][0] : d_as[0][0], da1 = st ? d_as[1][1] : d_as[0][1];
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) azptx::umma_bf16(tmem_base, da0 + 2 * ks, d_wst[0] + 2 * ks, idesc_st, ks != 0);
+                    if (KB == 2) {
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) azptx::umma_bf16(tmem_base, da1 + 2 * ks, d_wst[1] + 2 * ks, idesc_st, 1);
+                    }
+                    azptx::umma_commit(st_full);
+                    azptx::umma_commit(&a_empty[st]);                // this thread's reads of the A stage are done
+                }
+                __syncwarp();
+            }
 #pragma unroll
             for (int pass = 0; pass < 2; ++pass) { w_cur[pass] = w_nxt[pass]; s_cur[pass] = s_nxt[pass]; }
         }

@@ -272,9 +272,10 @@ def run_b200(args, wl, rank, world):
         planes, players, mcs = roots[-1]
         forest.set_roots_planes(planes, players, mcs)
         forest.begin_move(iters)
-        adv, lv = [], []
+        adv, lv, per_step = [], [], {}
         eng.profile(True)
         eng.profile(False)                                            # zero the totals, timing off
+        prev = {}
         for s in range(iters // vl + 1 if vl > 1 else iters):         # the whole search, every 8th step timed
             timed = s % 8 == 4
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -286,11 +287,21 @@ def run_b200(args, wl, rank, world):
             if timed:
                 adv.append((a, b))
                 lv.append(forest.counts()[0])
-        prof = eng.profile_read()
+                cur = eng.profile_read()                              # per-step deltas: steps beyond 3x the median are dropped,
+                for k, (ms, cnt) in cur.items():                      # so one preempted launch cannot skew a kernel's figure
+                    pms, pcnt = prev.get(k, (0.0, 0))
+                    if cnt > pcnt:
+                        per_step.setdefault(k, []).append(((ms - pms) / (cnt - pcnt), cnt - pcnt))
+                prev = cur
         eng.profile(False)
         leaves = sum(lv) / max(len(lv), 1)
-        out["profile"] = {k: dict(ms=v[0] / max(v[1], 1), launches=v[1]) for k, v in prof.items() if v[1]}
-        out["profile"]["forest_advance"] = dict(ms=sum(a.elapsed_time(b) for a, b in adv) / len(adv), launches=len(adv))
+
+        def robust_mean(xs):                                          # mean over the steps within 3x the median
+            m = sorted(xs)[len(xs) // 2]
+            keep = [x for x in xs if x <= 3.0 * m]
+            return sum(keep) / len(keep)
+        out["profile"] = {k: dict(ms=robust_mean([m for m, _ in v]), launches=sum(c for _, c in v)) for k, v in per_step.items()}
+        out["profile"]["forest_advance"] = dict(ms=robust_mean([a.elapsed_time(b) for a, b in adv]), launches=len(adv))
         out["leaves_per_step"] = leaves
         out["proj_width"] = eng.proj_width()
     out["clocks"] = clocks.summary(t_clock0, t_clock1)
