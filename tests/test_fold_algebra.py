@@ -99,3 +99,52 @@ def test_folded_front_end_equals_the_module(rows, cols, C, A, D, P, H):
     scale = np.abs(ref).max()
     assert np.abs(exact - ref).max() <= 1e-9 * max(scale, 1.0)          # identity in real arithmetic
     assert np.abs(front(_bf16) - ref).max() <= 2e-2 * max(scale, 1.0)   # folded weights rounded once to bf16
+
+
+def test_layernorm_folded_into_the_consuming_gemm():
+    """csrc/az_gemm.cuh: LayerNorm(x) W^T + b == rstd * (x W'^T - mean * colsum) + b' with W' = W diag(g),
+    colsum[n] = sum_k W'[n][k], b' = b + W beta, mean / rstd from (sum, sum of squares) of the row.  Exact in
+    real arithmetic; with W' rounded to bf16 and colsum formed from the ROUNDED weights the subtraction still
+    cancels the mean term exactly (that is why az_net_finalize sums the rounded values)."""
+    rng = np.random.default_rng(5)
+    M, K, N = 64, 512, 96
+    x = _bf16(rng.normal(0.4, 1.3, (M, K)))                          # rows as the producing GEMM stored them (bf16)
+    W, b = rng.normal(0, 0.05, (N, K)), rng.normal(0, 0.1, N)
+    g, beta = rng.normal(1.0, 0.2, K), rng.normal(0, 0.1, K)
+    mean = x.mean(1, keepdims=True)
+    var = x.var(1, keepdims=True)
+    ref = ((x - mean) / np.sqrt(var + 1e-5) * g + beta) @ W.T + b
+
+    s1, s2 = x.sum(1, keepdims=True), (x * x).sum(1, keepdims=True)
+    m = s1 / K
+    rstd = 1 / np.sqrt(np.maximum(s2 / K - m * m, 0) + 1e-5)
+    Wf, bf = W * g[None, :], b + W @ beta
+    out = rstd * (x @ Wf.T - m * Wf.sum(1)[None, :]) + bf
+    assert np.abs(out - ref).max() <= 1e-9
+
+    Wr = _bf16(Wf)                                                   # device weights; colsum from the rounded values
+    out_r = rstd * (x @ Wr.T - m * Wr.sum(1)[None, :]) + bf
+    assert np.abs(out_r - ref).max() <= 2e-2 * np.abs(ref).max()
+    # colsum from UNROUNDED weights would leave mean * (rounding error of a whole row) behind: strictly worse
+    out_bad = rstd * (x @ Wr.T - m * Wf.sum(1)[None, :]) + bf
+    assert np.abs(out_r - ref).max() <= np.abs(out_bad - ref).max() + 1e-12
+
+
+def test_polynomial_erf_gelu_is_far_below_bf16_resolution():
+    """az_gelu_erf (csrc/az_gemm.cuh): gelu(x) = max(x, 0) - 0.5 |x| E(|x|/sqrt 2), E = 1 - erf from Abramowitz &
+    Stegun 7.1.25.  Against the exact erf form of nn.GELU() the absolute error stays below 3e-5 everywhere, below half a
+    bf16 ulp of the output wherever |gelu| >= 1e-2 (worst case: the shallow negative lobe near x = -2.5) and below
+    1/16 ulp for |gelu| >= 0.25 -- the epilogue rounds to bf16 right after."""
+    x = np.linspace(-9, 9, 200001)
+    z = np.abs(x) / np.sqrt(2)
+    t = 1 / (1 + 0.47047 * z)
+    E = t * (0.3480242 + t * (-0.0958798 + t * 0.7478556)) * np.exp(-z * z)
+    approx = np.maximum(x, 0) - 0.5 * np.abs(x) * E
+    exact = torch.nn.functional.gelu(torch.from_numpy(x)).numpy()
+    err = np.abs(approx - exact)
+    assert err.max() <= 3e-5
+    ulp = 2.0 ** (np.floor(np.log2(np.maximum(np.abs(exact), 2.0 ** -20))) - 7)
+    big = np.abs(exact) >= 1e-2
+    assert (err[big] <= ulp[big] / 2).all()
+    large = np.abs(exact) >= 0.25
+    assert (err[large] <= ulp[large] / 16).all()
