@@ -37,6 +37,9 @@ struct AzFrontArgs {
     int nslots;                   // TMEM accumulator slots for the value blocks
     const float* bias_v;          // [D]
     bf16* oc;                     // [cap][D] (chunk-local rows) attention output of the cls query (before out_proj)
+    // az_front2.cuh (reassociated value path): U[board][head][128] instead of oc
+    int NP;                       // (board, head) pairs per tile = nb*H rounded up to 16
+    bf16* uc;                     // [cap][H*128]
 };
 
 static inline size_t az_front_smem(const AzFrontArgs& a) {

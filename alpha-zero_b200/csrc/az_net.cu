@@ -177,6 +177,7 @@ extern "C" int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const
 #include "az_net_kernels.cuh"
 #include "az_embed_mma.cuh"
 #include "az_front.cuh"
+#include "az_front2.cuh"
 
 struct AzBlockW {
     float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
@@ -214,6 +215,11 @@ struct az_net {
     CUtensorMap tm_vs;
     // depth-1 nets on boards of <= 63 cells: embedding .. cls attention in one kernel (az_front.cuh)
     bool front = false;
+    bool front2 = false;                 // reassociated value path (az_front2.cuh): U vectors + out-proj over K = H*128
+    bf16 *w_out2 = nullptr, *uc = nullptr;
+    float* b_out2 = nullptr;
+    CUtensorMap tm_wout2, tm_uc;
+    int bn_out2 = 0;
     std::vector<double> host_wemb;       // [kpad][D] rows: conv taps, then pos-emb + bias rows (fp64 copy for the folds)
     int host_wemb_kpad = 0;
     bf16 *f_wst = nullptr, *f_wv = nullptr;
@@ -629,6 +635,38 @@ extern "C" int az_net_finalize(az_net* n) {
             int tpp = 32;
             while (tpp * fa.nb * H > 128) tpp >>= 1;
             n->front = fa.nb >= 1 && fa.nslots >= 1 && tpp >= 1 && (fa.TS + tpp - 1) / tpp <= 8 && az_front_smem(fa) <= 227 * 1024;
+            // Reassociated value path: out = sum_h (Wo_h Wv2_h) u_h + (Wo bv + bo + x0), u_h = A^T w_h (az_front2.cuh)
+            fa.NP = (fa.nb * H + 15) / 16 * 16;
+            n->front2 = n->front && KB == 2 && kc <= 80 && fa.NP <= 128 && az_front2_smem(fa) <= 227 * 1024 && !getenv("AZ_NO_FRONT2");
+            if (n->front2) {
+                const std::vector<float>* wo = az_param(n, "blocks.0.attn.out_proj.weight", (size_t)D * D, &err);
+                if (!wo) return az_fail(AZ_EINVAL, "az_net_finalize: " + err);
+                const int hd = D / H, K2 = H * 128;
+                // wv2 in fp64 (the bf16 rounding happens once, on the product)
+                std::vector<double> wv2d((size_t)D * 128, 0.0);
+                for (int f = 0; f < D; ++f) {
+                    const float* wr = &wi[(size_t)(2 * D + f) * D];
+                    for (int k = 0; k < kused; ++k) {
+                        double acc = 0;
+                        for (int d = 0; d < D; ++d) acc += (double)wr[d] * wc[(size_t)k * D + d];
+                        wv2d[(size_t)f * 128 + k] = acc;
+                    }
+                }
+                std::vector<float> w2((size_t)D * K2, 0.f), b2(D);
+                for (int d = 0; d < D; ++d) {
+                    const float* wor = &(*wo)[(size_t)d * D];
+                    for (int h = 0; h < H; ++h)
+                        for (int k = 0; k < kused; ++k) {
+                            double acc = 0;
+                            for (int j = 0; j < hd; ++j) acc += (double)wor[h * hd + j] * wv2d[(size_t)(h * hd + j) * 128 + k];
+                            w2[(size_t)d * K2 + h * 128 + k] = (float)acc;
+                        }
+                    double acc = box[d];
+                    for (int f = 0; f < D; ++f) acc += (double)wor[f] * bv[f];
+                    b2[d] = (float)acc;
+                }
+                if ((rc = az_upload_bf16(n, &n->w_out2, w2.data(), w2.size())) || (rc = az_upload_f32(n, &n->b_out2, b2))) return rc;
+            }
         }
     }
     // ---- heads
@@ -667,6 +705,13 @@ extern "C" int az_net_finalize(az_net* n) {
         return rc;
     if (deep && ((rc = az_make_tmap(&n->tm_ao, n->ao, M, D, D, 128)) || (rc = az_make_tmap(&n->tm_hbuf, n->hbuf, M, 4 * D, 4 * D, 128))))
         return rc;
+    if (n->front2) {
+        const int K2 = n->H * 128;
+        n->bn_out2 = az_pick_bn_small_m(D, n->chunk);
+        if ((rc = az_net_alloc(n, &n->uc, (B + 128) * K2)) || (rc = az_make_tmap(&n->tm_uc, n->uc, B, K2, K2, 128)) ||
+            (rc = az_make_tmap(&n->tm_wout2, n->w_out2, D, K2, K2, n->bn_out2)))
+            return rc;
+    }
     {   // cls-row GEMMs of the last block: M = boards of one chunk, tile width chosen for that M
         AzBlockW& w = n->blk[n->L - 1];
         w.bn_out_c = az_pick_bn_small_m(D, n->chunk);
@@ -829,14 +874,17 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
     // out-proj -> norm2 -> mlp (ai/nn.py:44-50) on the cls rows: oc [cap][D] -> xc (residual stream) -> xc2.
     // With tail_fold the out-proj epilogue emits the row statistics and mlp1 applies norm2 in its own
     // epilogue (az_gemm.cuh); mlp2 emits the statistics the head GEMM needs.
-    auto cls_tail = [&](AzBlockW& w, AzGemmArgs out_args, int out_epi) -> int {
+    auto cls_tail = [&](AzBlockW& w, AzGemmArgs out_args, int out_epi, bool from_u = false) -> int {
         int rc2;
+        const CUtensorMap& tm_oa = from_u ? n->tm_uc : n->tm_oc;         // out-proj input: U vectors (front2) or oc
+        const CUtensorMap& tm_ow = from_u ? n->tm_wout2 : w.tm_out_c;
+        const int bn_out = from_u ? n->bn_out2 : w.bn_out_c;
         if (n->tail_fold) {
             out_args.stats_out = n->stats1;
-            if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out_c, out_args, out_epi, cap, w.bn_out_c))) return rc2;
+            if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, tm_oa, tm_ow, out_args, out_epi, cap, bn_out))) return rc2;
             AzGemmArgs g1 = az_gargs(batch, 1, w.b1_ln, nullptr, 0, n->hc, 4 * D, 4 * D, D);
             g1.stats_in = n->stats1;
-            g1.stats_parts = 2 * (D / w.bn_out_c);
+            g1.stats_parts = 2 * (D / bn_out);
             g1.colsum = w.cs1;
             g1.ln_inv_k = 1.0f / (float)D;
             g1.ln_eps = 1e-5f;
@@ -847,7 +895,7 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
             n->launches += 3;
             return AZ_OK;
         }
-        if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, n->tm_oc, w.tm_out_c, out_args, out_epi, cap, w.bn_out_c))) return rc2;
+        if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, tm_oa, tm_ow, out_args, out_epi, cap, bn_out))) return rc2;
         layernorm(1, n->xc, D, n->xcn, D, w.ln2_g, w.ln2_b);
         if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, n->tm_xcn, w.tm_w1_c, az_gargs(batch, 1, w.b1, nullptr, 0, n->hc, 4 * D, 4 * D, D), AZ_EPI_GELU, cap, w.bn_w1_c))) return rc2;
         if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, n->tm_hc, w.tm_w2_c, az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D), AZ_EPI_RESID, cap, w.bn_w2_c))) return rc2;
@@ -858,8 +906,8 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         // embedding + LN1 + V/score projection + cls attention, all on chip (az_front.cuh)
         AzBlockW& w = n->blk[0];
         AzFrontArgs fa = n->fa;
-        fa.batch = batch; fa.leaf_words = words; fa.leaf_player = players; fa.oc = n->oc;
-        const size_t smem = az_front_smem(fa);
+        fa.batch = batch; fa.leaf_words = words; fa.leaf_player = players; fa.oc = n->oc; fa.uc = n->uc;
+        const size_t smem = n->front2 ? az_front2_smem(fa) : az_front_smem(fa);
         const int tiles = (cap + fa.nb - 1) / fa.nb;
         const int grid = tiles < g_num_sms ? (tiles > 0 ? tiles : 1) : g_num_sms;
         {
@@ -869,9 +917,11 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         static bool done = false;                                                                                          \
         if (!done) {                                                                                                       \
             AZ_CUDA_OK(cudaFuncSetAttribute(az_front_kernel<TS8_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
+            AZ_CUDA_OK(cudaFuncSetAttribute(az_front2_kernel<TS8_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); \
             done = true;                                                                                                   \
         }                                                                                                                  \
-        AZ_CUDA_OK(az_launch_pdl(az_front_kernel<TS8_>, grid, AZ_FRONT_THREADS, smem, s, n->tm_fwst, n->tm_fwv, fa));                   \
+        if (n->front2) AZ_CUDA_OK(az_launch_pdl(az_front2_kernel<TS8_>, grid, AZ_FRONT_THREADS, smem, s, n->tm_fwst, fa)); \
+        else AZ_CUDA_OK(az_launch_pdl(az_front_kernel<TS8_>, grid, AZ_FRONT_THREADS, smem, s, n->tm_fwst, n->tm_fwv, fa)); \
     } break;
             switch (fa.TS / 8) {
                 AZ_FRONT(1) AZ_FRONT(2) AZ_FRONT(3) AZ_FRONT(4) AZ_FRONT(5) AZ_FRONT(6) AZ_FRONT(7) AZ_FRONT(8)
@@ -881,6 +931,10 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         }
         AZ_CUDA_OK(cudaGetLastError());
         ++n->launches;
+        if (n->front2) {
+            if ((rc = cls_tail(w, az_gargs(batch, 1, n->b_out2, nullptr, 0, n->xc, D, D, n->H * 128), AZ_EPI_BIAS, true))) return rc;
+            return heads(n->xc2);
+        }
         if ((rc = cls_tail(w, az_gargs(batch, 1, n->b_out_x0, nullptr, 0, n->xc, D, D, D), AZ_EPI_BIAS))) return rc;
         return heads(n->xc2);
     }

@@ -19,7 +19,7 @@ out = np.zeros((4, 64, 8), np.uint64)
 L.az_debug_front_trace.argtypes = [C.c_void_p]
 print("rc", L.az_debug_front_trace(out.ctypes.data_as(C.c_void_p)))
 t0 = out[out > 0].min()
-names = ["mma", "builder", "S", "V"]
+names = ["mma", "builder", "S", "V|U"]
 for it in range(0, 14):
     for r in range(4):
         ev = [int(v - t0) if v else -1 for v in out[r, it]]
