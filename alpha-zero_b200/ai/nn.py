@@ -147,6 +147,10 @@ class B200Net:
     def proj_width(self):
         return int(self._L.az_net_proj_width(self.h))
 
+    def path_flags(self):
+        """bit 0 fused front end, 1 reassociated front end, 2 CTA-pair cls-row GEMMs, 3 LayerNorm fold, 4 head epilogue."""
+        return int(self._L.az_net_path_flags(self.h))
+
     def launch_count(self):
         return int(self._L.az_net_launch_count(self.h))
 

@@ -24,6 +24,7 @@
 
 #define AZ_FRONT2_STAGES 4
 #define AZ_FRONT2_LAG 2
+#define AZ_FRONT2_BUILDERS 96      // warps 12-14: one rewritten token row per thread (two when a tile has more than 96)
 
 static inline size_t az_front2_smem(const AzFrontArgs& a) {
     const size_t tile = (size_t)a.NTP * 128;
@@ -90,7 +91,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
         azptx::prefetch_tmap(&tm_wst);
         azptx::mbar_init(w_full, 1);
         for (int i = 0; i < NA; ++i) {
-            azptx::mbar_init(&a_full[i], AZ_FRONT_BUILDERS);
+            azptx::mbar_init(&a_full[i], AZ_FRONT2_BUILDERS);
             azptx::mbar_init(&a_empty[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
@@ -170,9 +171,13 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
                 __syncwarp();
             }
         }
-    } else if (warp >= 12 && warp < 14) {
-        // ------------------------------ A-tile builders: token rows bt and bt + 64 ---------------------
+    } else if (warp >= 12 && warp < 15) {
+        // ------------------------------ A-tile builders ------------------------------------------------
+        // Only the rows of real board cells change from tile to tile (the cls row, pad rows and the one-hot
+        // columns are constants): thread bt rewrites active rows bt and bt + 96, active row i = cell i % (T-1)
+        // of board i / (T-1).
         const int bt = threadIdx.x - 384;
+        const int nact = a.nb * (T - 1);
         const int half = P >> 1, pp = P * P;
         const uint32_t colmask = (1u << a.cols) - 1u, pmask = (1u << P) - 1u;
         int r_b[2], r_t[2], r_rs[2], r_ls[2], r_cr[2];
@@ -180,11 +185,11 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
         bool r_on[2];
 #pragma unroll
         for (int pass = 0; pass < 2; ++pass) {
-            const int r = bt + pass * AZ_FRONT_BUILDERS;
-            const int bb = r / TS, t = r - bb * TS;
+            const int ai = bt + pass * AZ_FRONT2_BUILDERS;
+            const int bb = ai / (T - 1), t = 1 + ai - bb * (T - 1);
             r_b[pass] = bb;
             r_t[pass] = t;
-            r_on[pass] = r < NTP && bb < a.nb && t < T;
+            r_on[pass] = ai < nact;
             int cr = 0, cc = 0;
             if (t > 0) { cr = (t - 1) / a.cols; cc = (t - 1) - cr * a.cols; }
             r_cr[pass] = cr;
@@ -229,11 +234,10 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
         const int nch = (a.kc + 7) >> 3;
         int it = 0;
         AZ_TR(1, 5);
-#pragma unroll
-        for (int pass = 0; pass < 2; ++pass) {                       // the stages were zero-filled before the CTA-wide sync
-            const int r = bt + pass * AZ_FRONT_BUILDERS;
-            if (r >= NTP || !r_on[pass]) continue;
-            const int ob = a.kc + r_t[pass];
+        for (int r = bt; r < a.nb * TS; r += AZ_FRONT2_BUILDERS) {   // the stages were zero-filled before the CTA-wide sync
+            const int t = r % TS;
+            if (t >= T) continue;
+            const int ob = a.kc + t;
             for (int st = 0; st < NA; ++st)
                 *reinterpret_cast<unsigned short*>(s_a + (size_t)st * 2 * tile_bytes + (size_t)(ob >> 6) * tile_bytes + (size_t)r * 128 +
                                                    (((((uint32_t)ob & 63u) >> 3) ^ ((uint32_t)r & 7u)) << 4) + (ob & 7) * 2) = 0x3F80;
@@ -248,6 +252,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
             uint64_t kw0[2], kw1[2];
 #pragma unroll
             for (int pass = 0; pass < 2; ++pass) {
+                if (pass == 1 && nact <= AZ_FRONT2_BUILDERS) { kw0[1] = kw1[1] = 0ull; continue; }   // uniform: no second row
                 const int ob = a.kc + r_t[pass];
                 uint64_t k0 = ob < 64 ? 1ull << ob : 0ull, k1 = ob >= 64 ? 1ull << (ob - 64) : 0ull;
                 uint32_t p0 = 0, p1 = 0;
@@ -272,8 +277,8 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
             AZ_TR(1, 1);
 #pragma unroll
             for (int pass = 0; pass < 2; ++pass) {
-                const int r = bt + pass * AZ_FRONT_BUILDERS;
-                if (r >= NTP || !r_on[pass] || r_t[pass] == 0) continue;     // pad rows and the cls row never change
+                if (!r_on[pass]) continue;
+                const int r = r_b[pass] * TS + r_t[pass];
                 unsigned char* arow = s_a + (size_t)st * 2 * tile_bytes + (size_t)r * 128;
                 const int sw = r & 7;
                 // every LUT read of the row first, then the stores: the compiler cannot prove that the LUT and the

@@ -85,6 +85,83 @@ __device__ __forceinline__ float az_gelu_erf(float x) {
     return fmaf(-ax, p * e, fmaxf(x, 0.0f));
 }
 
+// Epilogue of one accumulator tile for one thread (= one output row): BN/2 columns starting at
+// column half*BN/2 of the tile, bias (+ LayerNorm fold) (+ GELU | + residual), bf16 row stores,
+// optional row statistics.  Shared by the single-CTA and the CTA-pair kernels.
+template <int BN, int EPI>
+__device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uint32_t tacc, int row, bool live, int n_blk, int half,
+                                                     float rstd, float nmr) {
+    constexpr int CPW = BN / 64;                               // 32-column chunks per warp
+    float st1 = 0.f, st2 = 0.f;
+#pragma unroll 1
+    for (int cc = 0; cc < CPW; ++cc) {
+        const int c = half * CPW + cc;
+        uint32_t r[32];
+        azptx::tmem_ld32(tacc + c * 32, r);
+        azptx::tmem_ld_wait();
+        const int col0 = n_blk * BN + c * 32;
+        if (live && args.out_f32 && col0 >= args.f32_col0) {      // fp32 side output (attention scores)
+            const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
+            float4* op = reinterpret_cast<float4*>(args.out_f32 + (size_t)row * 64 + (col0 - args.f32_col0));
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float4 bb = __ldg(b4 + i);
+                op[i] = make_float4(__uint_as_float(r[4 * i + 0]) + bb.x, __uint_as_float(r[4 * i + 1]) + bb.y,
+                                    __uint_as_float(r[4 * i + 2]) + bb.z, __uint_as_float(r[4 * i + 3]) + bb.w);
+            }
+        } else if (live) {
+            const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
+            const float4* c4 = reinterpret_cast<const float4*>(args.colsum + col0);
+            uint4 rv[4];
+            if (EPI == AZ_EPI_RESID) {
+                const uint4* rp = reinterpret_cast<const uint4*>(args.resid + (size_t)row * args.ldr + col0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) rv[i] = rp[i];
+            }
+            uint4 ov[4];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float4 bb = __ldg(b4 + i);
+                if (args.stats_in) {
+                    const float4 cs = __ldg(c4 + i);
+                    bb.x = fmaf(nmr, cs.x, bb.x); bb.y = fmaf(nmr, cs.y, bb.y);
+                    bb.z = fmaf(nmr, cs.z, bb.z); bb.w = fmaf(nmr, cs.w, bb.w);
+                }
+                float v0 = fmaf(rstd, __uint_as_float(r[4 * i + 0]), bb.x);
+                float v1 = fmaf(rstd, __uint_as_float(r[4 * i + 1]), bb.y);
+                float v2 = fmaf(rstd, __uint_as_float(r[4 * i + 2]), bb.z);
+                float v3 = fmaf(rstd, __uint_as_float(r[4 * i + 3]), bb.w);
+                if (EPI == AZ_EPI_GELU) {
+                    v0 = az_gelu_erf(v0); v1 = az_gelu_erf(v1); v2 = az_gelu_erf(v2); v3 = az_gelu_erf(v3);
+                }
+                if (EPI == AZ_EPI_RESID) {
+                    const uint32_t* rw = reinterpret_cast<const uint32_t*>(&rv[i >> 1]) + (i & 1) * 2;
+                    const __nv_bfloat162 r01 = *reinterpret_cast<const __nv_bfloat162*>(&rw[0]);
+                    const __nv_bfloat162 r23 = *reinterpret_cast<const __nv_bfloat162*>(&rw[1]);
+                    v0 += __bfloat162float(r01.x); v1 += __bfloat162float(r01.y);
+                    v2 += __bfloat162float(r23.x); v3 += __bfloat162float(r23.y);
+                }
+                __nv_bfloat162 o01 = __floats2bfloat162_rn(v0, v1);
+                __nv_bfloat162 o23 = __floats2bfloat162_rn(v2, v3);
+                if (args.stats_out) {             // statistics of the values the consumer will read
+                    const float f0 = __bfloat162float(o01.x), f1 = __bfloat162float(o01.y);
+                    const float f2 = __bfloat162float(o23.x), f3 = __bfloat162float(o23.y);
+                    st1 += (f0 + f1) + (f2 + f3);
+                    st2 = fmaf(f0, f0, fmaf(f1, f1, fmaf(f2, f2, fmaf(f3, f3, st2))));
+                }
+                uint32_t* ow = reinterpret_cast<uint32_t*>(&ov[i >> 1]) + (i & 1) * 2;
+                ow[0] = *reinterpret_cast<uint32_t*>(&o01);
+                ow[1] = *reinterpret_cast<uint32_t*>(&o23);
+            }
+            uint4* op = reinterpret_cast<uint4*>(args.out + (size_t)row * args.ldo + col0);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) op[i] = ov[i];
+        }
+    }
+    if (args.stats_out && live)
+        *reinterpret_cast<float2*>(args.stats_out + (size_t)row * AZ_STATS_LD + (n_blk * 2 + half) * 2) = make_float2(st1, st2);
+}
+
 template <int BN, int EPI>
 __global__ void __launch_bounds__(AZ_GEMM_THREADS, 1)
 az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, AzGemmArgs args) {
@@ -244,74 +321,7 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 __syncwarp();
                 if (live) args.values[obase + lane] = tanhf(val);
             } else {
-                float st1 = 0.f, st2 = 0.f;
-#pragma unroll 1
-                for (int cc = 0; cc < CPW; ++cc) {
-                    const int c = half * CPW + cc;
-                    uint32_t r[32];
-                    azptx::tmem_ld32(tacc + c * 32, r);
-                    azptx::tmem_ld_wait();
-                    const int col0 = n_blk * BN + c * 32;
-                    if (live && args.out_f32 && col0 >= args.f32_col0) {      // fp32 side output (attention scores)
-                        const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
-                        float4* op = reinterpret_cast<float4*>(args.out_f32 + (size_t)row * 64 + (col0 - args.f32_col0));
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const float4 bb = __ldg(b4 + i);
-                            op[i] = make_float4(__uint_as_float(r[4 * i + 0]) + bb.x, __uint_as_float(r[4 * i + 1]) + bb.y,
-                                                __uint_as_float(r[4 * i + 2]) + bb.z, __uint_as_float(r[4 * i + 3]) + bb.w);
-                        }
-                    } else if (live) {
-                        const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
-                        const float4* c4 = reinterpret_cast<const float4*>(args.colsum + col0);
-                        uint4 rv[4];
-                        if (EPI == AZ_EPI_RESID) {
-                            const uint4* rp = reinterpret_cast<const uint4*>(args.resid + (size_t)row * args.ldr + col0);
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) rv[i] = rp[i];
-                        }
-                        uint4 ov[4];
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            float4 bb = __ldg(b4 + i);
-                            if (args.stats_in) {
-                                const float4 cs = __ldg(c4 + i);
-                                bb.x = fmaf(nmr, cs.x, bb.x); bb.y = fmaf(nmr, cs.y, bb.y);
-                                bb.z = fmaf(nmr, cs.z, bb.z); bb.w = fmaf(nmr, cs.w, bb.w);
-                            }
-                            float v0 = fmaf(rstd, __uint_as_float(r[4 * i + 0]), bb.x);
-                            float v1 = fmaf(rstd, __uint_as_float(r[4 * i + 1]), bb.y);
-                            float v2 = fmaf(rstd, __uint_as_float(r[4 * i + 2]), bb.z);
-                            float v3 = fmaf(rstd, __uint_as_float(r[4 * i + 3]), bb.w);
-                            if (EPI == AZ_EPI_GELU) {
-                                v0 = az_gelu_erf(v0); v1 = az_gelu_erf(v1); v2 = az_gelu_erf(v2); v3 = az_gelu_erf(v3);
-                            }
-                            if (EPI == AZ_EPI_RESID) {
-                                const uint32_t* rw = reinterpret_cast<const uint32_t*>(&rv[i >> 1]) + (i & 1) * 2;
-                                const __nv_bfloat162 r01 = *reinterpret_cast<const __nv_bfloat162*>(&rw[0]);
-                                const __nv_bfloat162 r23 = *reinterpret_cast<const __nv_bfloat162*>(&rw[1]);
-                                v0 += __bfloat162float(r01.x); v1 += __bfloat162float(r01.y);
-                                v2 += __bfloat162float(r23.x); v3 += __bfloat162float(r23.y);
-                            }
-                            __nv_bfloat162 o01 = __floats2bfloat162_rn(v0, v1);
-                            __nv_bfloat162 o23 = __floats2bfloat162_rn(v2, v3);
-                            if (args.stats_out) {             // statistics of the values the consumer will read
-                                const float f0 = __bfloat162float(o01.x), f1 = __bfloat162float(o01.y);
-                                const float f2 = __bfloat162float(o23.x), f3 = __bfloat162float(o23.y);
-                                st1 += (f0 + f1) + (f2 + f3);
-                                st2 = fmaf(f0, f0, fmaf(f1, f1, fmaf(f2, f2, fmaf(f3, f3, st2))));
-                            }
-                            uint32_t* ow = reinterpret_cast<uint32_t*>(&ov[i >> 1]) + (i & 1) * 2;
-                            ow[0] = *reinterpret_cast<uint32_t*>(&o01);
-                            ow[1] = *reinterpret_cast<uint32_t*>(&o23);
-                        }
-                        uint4* op = reinterpret_cast<uint4*>(args.out + (size_t)row * args.ldo + col0);
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) op[i] = ov[i];
-                    }
-                }
-                if (args.stats_out && live)
-                    *reinterpret_cast<float2*>(args.stats_out + (size_t)row * AZ_STATS_LD + (n_blk * 2 + half) * 2) = make_float2(st1, st2);
+                az_gemm_epilogue_row<BN, EPI>(args, tacc, row, live, n_blk, half, rstd, nmr);
             }
             azptx::tc_fence_before();
             azptx::mbar_arrive(&tempty[as]);

@@ -17,6 +17,7 @@
 #include <string>
 #include <vector>
 #include "az_gemm.cuh"
+#include "az_gemm2.cuh"
 #include "az_host.h"
 #include "../../include/az_b200.h"
 
@@ -85,6 +86,31 @@ static int az_pick_bn_small_m(int N, int max_rows) {
     return best ? best : az_pick_bn(N);
 }
 
+// CTA-pair tiles (az_gemm2.cuh): 256 x bn per pair of SMs, each CTA stages 128 A rows + bn/2 W rows per k-block.
+// Returned as bn + AZ_PAIR so that one integer describes the tile through the launch path.
+#define AZ_PAIR 1000
+static int az_pick_bn_pair(int N, int max_rows) {
+    if (!g_num_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int cands[2] = {256, 128};
+    int best = 0;
+    long long best_cost = 0;
+    for (int bn : cands) {
+        if (N % bn) continue;
+        const long long tiles = (long long)((max_rows + 255) / 256) * (N / bn);
+        const long long pairs = g_num_sms / 2;
+        const long long cost = ((tiles + pairs - 1) / pairs) * (128 + bn / 2);
+        if (!best || cost < best_cost) { best = bn; best_cost = cost; }
+    }
+    return best ? best + AZ_PAIR : 0;
+}
+static bool az_pair_enabled() { return !getenv("AZ_NO_PAIR"); }
+static uint32_t az_w_box_rows(int bn) { return bn >= AZ_PAIR ? (uint32_t)(bn - AZ_PAIR) / 2 : (uint32_t)bn; }
+static int az_bn_width(int bn) { return bn >= AZ_PAIR ? bn - AZ_PAIR : bn; }
+
 // Launch with programmatic stream serialization: the kernel may begin (prologue only -- it calls
 // griddepcontrol.wait before touching its inputs) while its predecessor in the stream drains.
 // AZ_NO_PDL=1 falls back to fully serialised launches.
@@ -124,9 +150,59 @@ static int az_launch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const 
     return AZ_OK;
 }
 
+template <int BN, int EPI>
+static int az_launch_gemm2_t(const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& a, int max_rows, cudaStream_t s) {
+    constexpr int smem = AzGemm2Cfg<BN>::SMEM;
+    static bool attr_done = false;
+    if (!attr_done) {
+        AZ_CUDA_OK(cudaFuncSetAttribute(az_gemm2_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_done = true;
+    }
+    if (!g_num_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int tiles = ((max_rows + 255) / 256) * (a.N / BN);
+    const int pairs = std::max(1, std::min(tiles, g_num_sms / 2));
+    static const bool pdl = !getenv("AZ_NO_PDL");
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * pairs));
+    cfg.blockDim = dim3(AZ_GEMM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 2 : 1;
+    AZ_CUDA_OK(cudaLaunchKernelEx(&cfg, az_gemm2_kernel<BN, EPI>, ta, tb, a));
+    AZ_CUDA_OK(cudaGetLastError());
+    return AZ_OK;
+}
+
 // A: bf16 [rows][K] (ld = lda), W: bf16 [N][K]; max_rows bounds the grid when M is device-side.
 static int az_launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& a, int epi, int max_rows,
                           cudaStream_t s, int bn_forced = 0) {
+    if (bn_forced >= AZ_PAIR) {                                // CTA-pair tile: the W tensor map has a box of bn/2 rows
+        const int bn2 = bn_forced - AZ_PAIR;
+        if ((bn2 != 128 && bn2 != 256) || a.N % bn2 || a.K % 64 || epi == AZ_EPI_HEAD || a.out_f32)
+            return az_fail(AZ_EINVAL, "gemm: unsupported CTA-pair tile");
+        if ((a.stats_in && (!a.colsum || a.stats_parts < 1 || a.stats_parts > AZ_STATS_LD / 2)) || (a.stats_out && 2 * (a.N / bn2) > AZ_STATS_LD / 2))
+            return az_fail(AZ_EINVAL, "gemm: bad LayerNorm-fold arguments");
+#define AZ_G2(BN_)                                                                             \
+    if (bn2 == BN_) {                                                                          \
+        if (epi == AZ_EPI_BIAS) return az_launch_gemm2_t<BN_, AZ_EPI_BIAS>(ta, tb, a, max_rows, s);  \
+        if (epi == AZ_EPI_GELU) return az_launch_gemm2_t<BN_, AZ_EPI_GELU>(ta, tb, a, max_rows, s);  \
+        return az_launch_gemm2_t<BN_, AZ_EPI_RESID>(ta, tb, a, max_rows, s);                   \
+    }
+        AZ_G2(256) AZ_G2(128)
+#undef AZ_G2
+    }
     const int bn = bn_forced ? bn_forced : az_pick_bn(a.N);
     if (!bn || a.K % 64) return az_fail(AZ_EINVAL, "gemm: N and K must be multiples of 64");
     if (epi == AZ_EPI_HEAD) {
@@ -152,12 +228,17 @@ extern "C" int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const
                             int ldr, void* out_dev, int ldo, int M, int N, int K, int epi, void* stream) {
     if (!a_dev || !w_dev || !bias_dev || !out_dev || M <= 0) return az_fail(AZ_EINVAL, "az_gemm_bf16: bad arguments");
     if (epi == AZ_EPI_RESID && !resid_dev) return az_fail(AZ_EINVAL, "az_gemm_bf16: residual missing");
-    const int bn = az_pick_bn(N);
+    int bn = az_pick_bn(N);
     if (!bn || K % 64 || lda % 8 || ldo % 8) return az_fail(AZ_EINVAL, "az_gemm_bf16: N,K multiples of 64; ld multiples of 8");
+    if (M >= 512 && N % 128 == 0 && az_pair_enabled()) bn = (N % 256 == 0 ? 256 : 128) + AZ_PAIR;   // CTA-pair kernel
+    if (const char* e = getenv("AZ_GEMM_BN")) {                 // experiments (tools/gemm_bench.py): force the tile width
+        const int f = atoi(e), w = f >= AZ_PAIR ? f - AZ_PAIR : f;
+        if (w > 0 && N % w == 0 && (f < AZ_PAIR ? (w == 64 || w == 128 || w == 192 || w == 256) : (w == 128 || w == 256))) bn = f;
+    }
     CUtensorMap ta, tb;
     int rc;
     if ((rc = az_make_tmap(&ta, a_dev, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 128))) return rc;
-    if ((rc = az_make_tmap(&tb, w_dev, (uint64_t)N, (uint64_t)K, (uint64_t)K, (uint32_t)bn))) return rc;
+    if ((rc = az_make_tmap(&tb, w_dev, (uint64_t)N, (uint64_t)K, (uint64_t)K, az_w_box_rows(bn)))) return rc;
     AzGemmArgs a{};
     a.bias = bias_dev;
     a.resid = reinterpret_cast<const bf16*>(resid_dev);
@@ -168,7 +249,7 @@ extern "C" int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const
     a.K = K;
     a.m_fixed = M;
     a.m_count = nullptr;
-    return az_launch_gemm(ta, tb, a, epi, M, (cudaStream_t)stream);
+    return az_launch_gemm(ta, tb, a, epi, M, (cudaStream_t)stream, bn);
 }
 
 // ======================================================================================
@@ -705,28 +786,32 @@ extern "C" int az_net_finalize(az_net* n) {
         return rc;
     if (deep && ((rc = az_make_tmap(&n->tm_ao, n->ao, M, D, D, 128)) || (rc = az_make_tmap(&n->tm_hbuf, n->hbuf, M, 4 * D, 4 * D, 128))))
         return rc;
+    // CTA-pair kernels for the cls-row GEMMs: measured (tools/gemm_bench.py) 7 % faster on the K = 4D GEMM at 65536 rows, not
+    // faster at 4096 rows (one tile per CTA: start-up latency, not L2 traffic, bounds those); AZ_PAIR_MIN_ROWS overrides
+    const int pair_min = getenv("AZ_PAIR_MIN_ROWS") ? atoi(getenv("AZ_PAIR_MIN_ROWS")) : 16384;
+    const bool pair_ok = az_pair_enabled() && n->chunk >= pair_min && D % 128 == 0;
     if (n->front2) {
         const int K2 = n->H * 128;
-        n->bn_out2 = az_pick_bn_small_m(D, n->chunk);
+        n->bn_out2 = pair_ok ? az_pick_bn_pair(D, n->chunk) : az_pick_bn_small_m(D, n->chunk);
         if ((rc = az_net_alloc(n, &n->uc, (B + 128) * K2)) || (rc = az_make_tmap(&n->tm_uc, n->uc, B, K2, K2, 128)) ||
-            (rc = az_make_tmap(&n->tm_wout2, n->w_out2, D, K2, K2, n->bn_out2)))
+            (rc = az_make_tmap(&n->tm_wout2, n->w_out2, D, K2, K2, az_w_box_rows(n->bn_out2))))
             return rc;
     }
     {   // cls-row GEMMs of the last block: M = boards of one chunk, tile width chosen for that M
         AzBlockW& w = n->blk[n->L - 1];
-        w.bn_out_c = az_pick_bn_small_m(D, n->chunk);
-        w.bn_w1_c = az_pick_bn_small_m(4 * D, n->chunk);
-        w.bn_w2_c = az_pick_bn_small_m(D, n->chunk);
-        if ((rc = az_make_tmap(&w.tm_out_c, w.w_out, D, D, D, w.bn_out_c)) ||
-            (rc = az_make_tmap(&w.tm_w1_c, w.w1, 4 * D, D, D, w.bn_w1_c)) ||
-            (rc = az_make_tmap(&w.tm_w2_c, w.w2, D, 4 * D, 4 * D, w.bn_w2_c)))
+        w.bn_out_c = pair_ok ? az_pick_bn_pair(D, n->chunk) : az_pick_bn_small_m(D, n->chunk);
+        w.bn_w1_c = pair_ok ? az_pick_bn_pair(4 * D, n->chunk) : az_pick_bn_small_m(4 * D, n->chunk);
+        w.bn_w2_c = pair_ok ? az_pick_bn_pair(D, n->chunk) : az_pick_bn_small_m(D, n->chunk);
+        if ((rc = az_make_tmap(&w.tm_out_c, w.w_out, D, D, D, az_w_box_rows(w.bn_out_c))) ||
+            (rc = az_make_tmap(&w.tm_w1_c, w.w1, 4 * D, D, D, az_w_box_rows(w.bn_w1_c))) ||
+            (rc = az_make_tmap(&w.tm_w2_c, w.w2, D, 4 * D, 4 * D, az_w_box_rows(w.bn_w2_c))))
             return rc;
     }
     n->tail_fold = !getenv("AZ_NO_TAIL_FOLD");
     n->head_fold = n->tail_fold && A + 1 <= 64;
     if (n->tail_fold) {
         AzBlockW& w = n->blk[n->L - 1];
-        if ((rc = az_make_tmap(&w.tm_w1_ln_c, w.w1_ln, 4 * D, D, D, w.bn_w1_c)) ||
+        if ((rc = az_make_tmap(&w.tm_w1_ln_c, w.w1_ln, 4 * D, D, D, az_w_box_rows(w.bn_w1_c))) ||
             (rc = az_net_alloc(n, &n->stats1, B * AZ_STATS_LD)) || (rc = az_net_alloc(n, &n->stats2, B * AZ_STATS_LD)) ||
             (rc = az_make_tmap(&n->tm_xc, n->xc, B, D, D, 128)) || (rc = az_make_tmap(&n->tm_xc2, n->xc2, B, D, D, 128)))
             return rc;
@@ -828,7 +913,7 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         if (n->head_fold) {                                    // one GEMM: raw rows x folded head weights, norm + softmax in the epilogue
             AzGemmArgs ga = az_gargs(batch, 1, n->b_head_ln, nullptr, 0, nullptr, 64, 64, D);
             ga.stats_in = n->stats2;
-            ga.stats_parts = 2 * (D / n->blk[L - 1].bn_w2_c);
+            ga.stats_parts = 2 * (D / az_bn_width(n->blk[L - 1].bn_w2_c));
             ga.colsum = n->cs_head;
             ga.ln_inv_k = 1.0f / (float)D;
             ga.ln_eps = 1e-5f;
@@ -884,7 +969,7 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
             if ((rc2 = gemm_bn(AZ_K_GEMM_CLS, tm_oa, tm_ow, out_args, out_epi, cap, bn_out))) return rc2;
             AzGemmArgs g1 = az_gargs(batch, 1, w.b1_ln, nullptr, 0, n->hc, 4 * D, 4 * D, D);
             g1.stats_in = n->stats1;
-            g1.stats_parts = 2 * (D / bn_out);
+            g1.stats_parts = 2 * (D / az_bn_width(bn_out));
             g1.colsum = w.cs1;
             g1.ln_inv_k = 1.0f / (float)D;
             g1.ln_eps = 1e-5f;
@@ -1082,6 +1167,11 @@ extern "C" int az_net_forward_planes(az_net* n, const float* planes_host, int B,
 // Output width of the all-token projection of the last block (the dominant GEMM): D + 64 when the
 // cls query is folded (depth 1), else 2D (K and V).
 extern "C" int az_net_proj_width(az_net* n) { return n ? (n->folded ? n->n2 : 2 * n->D) : 0; }
+
+extern "C" int az_net_path_flags(az_net* n) {
+    if (!n) return 0;
+    return (n->front ? 1 : 0) | (n->front2 ? 2 : 0) | (n->blk[n->L - 1].bn_w1_c >= AZ_PAIR ? 4 : 0) | (n->tail_fold ? 8 : 0) | (n->head_fold ? 16 : 0);
+}
 
 extern "C" long long az_net_launch_count(az_net* n) { return n ? (long long)n->launches : 0; }
 

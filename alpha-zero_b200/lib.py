@@ -42,6 +42,7 @@ _SIGS = {
     "az_net_forward_planes": (i32, [vp, vp, i32, vp, vp, vp, vp]),
     "az_net_launch_count": (C.c_longlong, [vp]),
     "az_net_proj_width": (i32, [vp]),
+    "az_net_path_flags": (i32, [vp]),
     "az_forest_search_net": (i32, [vp, vp, i32, vp]),
     "az_net_invalidate_graphs": (i32, [vp]),
     "az_forest_read_leaves": (i32, [vp, i32, vp, vp, vp, vp, vp, vp]),

@@ -144,12 +144,16 @@ def roofline(wl, r, prof, pk, kind=None):
     traffic = ncu_traffic(kind, wl)
     st = r["stats"]
     flops = None
-    if kind == "front_fused":       # one contraction over the K binary inputs per token: D value + H score + K Gram columns
+    front2 = bool(r.get("path_flags", 0) & 2)
+    if kind == "front_fused" and front2:   # statistics (H scores + K Cholesky columns) per token + U = A^T w: H columns per token
+        flops, name = 2.0 * leaves * T * kused * (H + kused + H), "az_front2_kernel (embedding+LN1+score projection+cls softmax+U=A^T w, tcgen05)"
+    elif kind == "front_fused":     # one contraction over the K binary inputs per token: D value + H score + K Gram columns
         flops, name = 2.0 * leaves * T * kused * (D + H + kused), "az_front_kernel (embedding+LN1+V/score projection+cls attention, tcgen05)"
     elif kind == "gemm_kv":
         flops, name = 2.0 * leaves * T * D * r["proj_width"], f"az_gemm_kernel (all-token projection, N={r['proj_width']}, tcgen05)"
-    elif kind == "gemm_cls_rows":   # out_proj D*D, mlp D*4D, 4D*D over 3 launches -> average launch
-        flops, name = 2.0 * leaves * 9 * D * D / 3.0, "az_gemm_kernel (cls-row out_proj / MLP GEMMs, tcgen05; average of the 3 launches)"
+    elif kind == "gemm_cls_rows":   # out_proj D*D (D x H*128 after the front-kernel reassociation), mlp D*4D, 4D*D over 3 launches -> average launch
+        kout = H * 128 if front2 else D
+        flops, name = 2.0 * leaves * (kout * D + 8 * D * D) / 3.0, "az_gemm_kernel (cls-row out_proj / MLP GEMMs, tcgen05; average of the 3 launches)"
     elif kind == "embed_ln":
         flops, name = 2.0 * leaves * T * 128 * D, "az_embed_mma_kernel (im2col embedding + LN, tcgen05)"
     if flops is not None:
@@ -304,6 +308,7 @@ def run_b200(args, wl, rank, world):
         out["profile"]["forest_advance"] = dict(ms=robust_mean([a.elapsed_time(b) for a, b in adv]), launches=len(adv))
         out["leaves_per_step"] = leaves
         out["proj_width"] = eng.proj_width()
+        out["path_flags"] = eng.path_flags()
     out["clocks"] = clocks.summary(t_clock0, t_clock1)
     forest.close()
     eng.close()
@@ -365,6 +370,9 @@ def main():
                 e2e=dict(value=e2e, unit="simulations/s", h2d_bytes_per_step=r["h2d"], d2h_bytes_per_step=r["d2h"],
                          steps_ms=r["e2e_steps_ms"]),
                 gpu_launches=r["gpu_launches"], search_stats=r["stats"])
+    pf = r.get("path_flags", 0)
+    line["evaluator_path"] = dict(flags=pf, front_kernel="az_front2_kernel" if pf & 2 else ("az_front_kernel" if pf & 1 else "generic"),
+                                  cls_row_gemm="cta_pair" if pf & 4 else "single_cta", layernorm_fold=bool(pf & 8), head_epilogue=bool(pf & 16))
     prof = r.get("profile", {})
     if prof:
         line["kernel_ms"] = {k: round(v["ms"], 4) for k, v in prof.items()}

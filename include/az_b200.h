@@ -126,6 +126,10 @@ AZ_API int az_net_forward_planes(az_net* n, const float* planes_host, int B, flo
                                  float* priors_host, void* stream);
 AZ_API long long az_net_launch_count(az_net* n);
 AZ_API int az_net_proj_width(az_net* n);   /* N of the all-token projection GEMM of the last block */
+/* Which kernels this net runs (for reports): bit 0 fused front end (az_front.cuh), bit 1 its reassociated form
+ * (az_front2.cuh: U vectors, out-proj over K = heads*128), bit 2 CTA-pair tiles for the cls-row GEMMs (az_gemm2.cuh),
+ * bit 3 LayerNorm folded around the cls-row GEMMs, bit 4 heads + softmax as a GEMM epilogue. */
+AZ_API int az_net_path_flags(az_net* n);
 /* MCTS.mcts with the built-in net for every tree of the forest: `iters` simulations per tree,
  * one CUDA graph per step (advance + net), no per-node host work. */
 AZ_API int az_forest_search_net(az_forest* f, az_net* n, int iters, void* stream);
