@@ -31,6 +31,11 @@ class HashEvaluator:
         self.seed, self.qbits = int(seed), int(qbits)
 
 
+class UCB1HashEvaluator(HashEvaluator):
+    """Parity runs of the vanilla selection rule (model=None, utils.py:36,43): UCB1 on the device with the
+    deterministic hash value in place of the random rollout (oracle: az_oracle.mcts_vanilla + hash_simulate)."""
+
+
 class MCTS:
     cache = {}          # kept for API compatibility (main.py:51-57); the GPU path needs no cache
     matched = 0
@@ -99,8 +104,21 @@ class MCTS:
     @staticmethod
     def _run(forest, model, iters):
         if not model:
-            raise NotImplementedError("vanilla MCTS (model=None: UCB1 + random rollouts, ai/mcts.py:57-79) is not "
-                                      "part of the GPU hot path; pass a Net / B200Net / callable evaluator")
+            # vanilla MCTS (ai/mcts.py:57-79): UCB1 + random rollouts on the device; the rollout streams are seeded
+            # from the global NumPy RNG the reference draws its rollout moves from
+            forest.set_mode(True)
+            try:
+                forest.search_rollout(iters, int(np.random.randint(0, 2 ** 31 - 1)) * 2654435761 + 12345)
+            finally:
+                forest.set_mode(False)
+            return
+        if isinstance(model, UCB1HashEvaluator):               # parity runs of the vanilla selection rule
+            forest.set_mode(True)
+            try:
+                forest.search_hash(iters, model.seed, model.qbits)
+            finally:
+                forest.set_mode(False)
+            return
         if isinstance(model, HashEvaluator):
             forest.search_hash(iters, model.seed, model.qbits)
             return
@@ -116,7 +134,8 @@ class MCTS:
         forest = MCTS._forest_for(Game, 1, mcts_iterations, 1)
         forest.set_roots_planes(np.asarray(board, dtype=np.float32)[None], [root.currentPlayer], [root.move_count])
         # the same draw, from the same global RNG, as utils.add_dirichlet_noise (utils.py:21)
-        forest.set_noise(np.random.dirichlet([0.03] * Game.action_dim)[None] if dirichlet else None)
+        # (vanilla mode, model=None, never mixes noise in: ai/mcts.py:42,52 sit inside `if model`)
+        forest.set_noise(np.random.dirichlet([0.03] * Game.action_dim)[None] if (dirichlet and model) else None)
         MCTS._run(forest, model, mcts_iterations)
         MCTS.mcts_count += mcts_iterations
         ch = forest.root_children(0)
@@ -125,10 +144,10 @@ class MCTS:
         for cell, n, w, p in zip(ch["cells"], ch["visits"], ch["W"], ch["P"]):
             action = (int(cell) // Game.cols, int(cell) % Game.cols)
             node = Node(root, action, 1 - root.currentPlayer, root.move_count + 1,
-                        np.float64(p) if dirichlet else np.float32(p))
+                        (np.float64(p) if dirichlet else np.float32(p)) if model else 0.0)
             node.visit, node.value = int(n), float(w)
             root.children.append(node)
-        root.refresh_ucb()
+        root.refresh_ucb("network" if model else "normal")
 
     # ---- many positions at once --------------------------------------------------------------------
     @staticmethod

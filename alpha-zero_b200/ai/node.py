@@ -35,10 +35,13 @@ class Node:
             by_action[Game.get_action_idx(ch.prevAction)] = ch
         return np.random.choice(by_action, p=p)
 
-    def refresh_ucb(self):
-        """PUCT of the children as the reference would show them (utils.py:29-44)."""
+    def refresh_ucb(self, mode="network"):
+        """PUCT ('network') or UCB1 ('normal') of the children as the reference would show them (utils.py:29-44)."""
         for ch in self.children:
-            u = ch.prior * math.sqrt(self.visit) / (ch.visit + 1)
+            if mode == "normal":
+                u = math.sqrt(2 * math.log(self.visit) / (ch.visit + 1)) if self.visit > 0 else 0.0
+            else:
+                u = ch.prior * math.sqrt(self.visit) / (ch.visit + 1)
             ch.ucb = u if ch.visit == 0 else (ch.value / ch.visit) + u
 
     def to_string(self, Game):

@@ -72,6 +72,15 @@ __device__ __forceinline__ double az_puct64(double W, double P, int n, double s)
     return __dadd_rn(__ddiv_rn(W, (double)n), u);
 }
 
+// Vanilla mode (model=None), utils.py:36,43 in Python floats: sqrt(2 ln Np / (n+1)) (+ W/n once visited); an
+// unvisited child is NOT +inf.  two_ln = 2 * ln(Np) with ln from the host's C library (log_tab), so the score is
+// the reference's bit for bit.
+__device__ __forceinline__ double az_ucb1(double W, int n, double two_ln) {
+    const double e = __dsqrt_rn(__ddiv_rn(two_ln, (double)(n + 1)));
+    if (n == 0) return e;
+    return __dadd_rn(__ddiv_rn(W, (double)n), e);
+}
+
 // First maximum in child order over the lanes of a group with the warp-reduce unit (redux.sync):
 // scores become order-preserving unsigned keys (+0.0 canonicalises -0.0; a lane never holds NaN
 // because `sc > best` is false for NaN), the winner is the smallest child index among the lanes
@@ -340,8 +349,8 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             const uint32_t cb = m.child_base;
             int bi = 0x7fffffff, bn = 0;
             unsigned long long bm = 0ull;
-            if (node == 0 && f.use_noise) {
-                const double s = __dsqrt_rn((double)pn);
+            if (f.ucb1 || (node == 0 && f.use_noise)) {
+                const double s = f.ucb1 ? __dmul_rn(2.0, f.log_tab[pn]) : __dsqrt_rn((double)pn);
                 double best = -1.0 / 0.0;
                 for (int c = lane; c < nc; c += G) {
                     const AzHot h = hot[cb + c];
@@ -349,7 +358,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
                     const unsigned long long mm = mw.x;
                     const int n = h.N + (int)h.V;
                     const double W = __longlong_as_double((long long)mw.y) - (double)h.V;
-                    const double sc = az_puct64(W, f.root_prior64[(size_t)tree * g.max_children + c], n, s);
+                    const double sc = f.ucb1 ? az_ucb1(W, n, s) : az_puct64(W, f.root_prior64[(size_t)tree * g.max_children + c], n, s);
                     if (sc > best) { best = sc; bi = c; bm = mm; bn = n; }
                 }
                 bi = az_group_argmax(gmask, best, bi);
@@ -543,6 +552,96 @@ __global__ void az_eval_hash_kernel(AzForestDev f, uint64_t seed, int qbits, flo
             const int q = (int)((x >> 40) & 0xFFFF) - 32768;
             f.values[slot] = __fmul_rn((float)q, 1.0f / 32768.0f);
         }
+    }
+}
+
+// MCTS.simulate (ai/mcts.py:62-79): uniformly random legal moves from the leaf to the end of the game, one thread
+// per pending leaf.  The leaf is canonical (side 0 = side to move), so the value written is +1 if the side to move
+// wins, -1 if it loses, 0 for a draw (the reference's `result` with the sign of mcts.py:56).  Legal SETS only --
+// the reference's move order does not matter under a uniform draw: TicTacToe empty cells, Connect4 the lowest
+// empty cell of every open column, Gomoku empty 8-neighbours of stones (centre on an empty board).
+template <int NW>
+__device__ int az_rollout(const AzGame& g, AzBoard<NW> b, uint64_t rng) {
+    int mc = 0;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) mc += __popcll(b.w[0][i]) + __popcll(b.w[1][i]);
+    int player = 0;
+    while (mc < g.state_dim) {
+        uint64_t legal[NW];
+#pragma unroll
+        for (int i = 0; i < NW; ++i) legal[i] = 0ull;
+        int n = 0;
+        for (int cell = 0; cell < g.state_dim; ++cell) {
+            if (!b.empty(cell)) continue;
+            bool ok;
+            if (g.gid == AZ_GAME_TICTACTOE) {
+                ok = true;
+            } else if (g.gid == AZ_GAME_CONNECT4) {
+                ok = cell + g.cols >= g.state_dim || !b.empty(cell + g.cols);
+            } else {
+                ok = false;
+                const int r = cell / g.cols, c = cell - r * g.cols;
+                for (int dr = -1; dr <= 1 && !ok; ++dr)
+                    for (int dc = -1; dc <= 1; ++dc) {
+                        const int rr = r + dr, cc = c + dc;
+                        if ((dr || dc) && rr >= 0 && rr < g.rows && cc >= 0 && cc < g.cols && !b.empty(rr * g.cols + cc)) { ok = true; break; }
+                    }
+                if (mc == 0) ok = cell == (g.rows / 2) * g.cols + g.cols / 2;
+            }
+            if (ok) {
+#pragma unroll
+                for (int i = 0; i < NW; ++i)
+                    if (NW == 1 || i == (cell >> 6)) legal[i] |= 1ull << (cell & 63);
+                ++n;
+            }
+        }
+        if (n == 0) return 0;
+        rng = az_sm64(rng);
+        int k = (int)((rng >> 11) % (uint64_t)n);
+        int cell = 0;
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            uint64_t w = legal[i];
+            const int pc = __popcll(w);
+            if (k >= 0 && k < pc) {
+                for (int j = 0; j < k; ++j) w &= w - 1;
+                cell = i * 64 + __ffsll((long long)w) - 1;
+                k = -1;
+            } else if (k >= 0) {
+                k -= pc;
+            }
+        }
+        b.put(player, cell);
+        ++mc;
+        if (az_is_win(g, b, player, cell)) return player == 0 ? 1 : -1;
+        player ^= 1;
+    }
+    return 0;
+}
+
+__global__ void az_eval_rollout_kernel(AzForestDev f, uint64_t seed, uint64_t counter) {
+    const int n = *f.n_leaves;
+    const int A = f.g.action_dim;
+    const int nw = f.g.nw;
+    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n; slot += gridDim.x * blockDim.x) {
+        const uint64_t* w = f.leaf_words + (size_t)slot * 2 * nw;
+        const uint64_t rng = az_sm64(az_sm64(seed ^ (counter * 0x9E3779B97F4A7C15ull)) + (uint64_t)f.leaf_tree[slot] * 0xD1B54A32D192ED03ull + (uint64_t)slot);
+        int r;
+        if (nw == 1) {
+            AzBoard<1> b;
+            b.w[0][0] = w[0];
+            b.w[1][0] = w[1];
+            r = az_rollout<1>(f.g, b, rng);
+        } else {
+            AzBoard<AZ_MAX_WORDS> b;
+            for (int i = 0; i < AZ_MAX_WORDS; ++i) {
+                b.w[0][i] = i < nw ? w[i] : 0ull;
+                b.w[1][i] = i < nw ? w[nw + i] : 0ull;
+            }
+            r = az_rollout<AZ_MAX_WORDS>(f.g, b, rng);
+        }
+        f.values[slot] = (float)r;
+        for (int a = 0; a < A; ++a) f.priors[(size_t)slot * A + a] = 0.f;     // node.py:58: children without priors
     }
 }
 
@@ -794,6 +893,8 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     d.max_depth = g.state_dim + 2;
     d.max_leaves = n_trees * vl_batch;
     d.use_noise = 0;
+    d.ucb1 = 0;
+    d.log_tab = nullptr;
     f->max_iters = max_iters;
     // One warp per tree: sub-warp groups (8 lanes for the <= 9-children games) share a warp between
     // four trees whose descents diverge and serialise; measured 4x slower on Connect4.  AZ_FOREST_GROUP=8
@@ -988,6 +1089,52 @@ extern "C" int az_eval_hash(az_forest* f, uint64_t seed, int qbits, void* stream
     const int grid = (int)std::min<long long>((work + 255) / 256, 148 * 16);
     az_eval_hash_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(f->d, seed, qbits, scale);
     AZ_CUDA_OK(cudaGetLastError());
+    return AZ_OK;
+}
+
+// Vanilla MCTS (model=None, ai/mcts.py:57-59): mode 1 = UCB1 selection, children without priors.
+extern "C" int az_forest_set_mode(az_forest* f, int mode) {
+    if (!f || (mode != 0 && mode != 1)) return az_fail(AZ_EINVAL, "forest_set_mode: mode 0 (PUCT) or 1 (UCB1)");
+    if (mode == 1 && !f->d.log_tab) {
+        const int n = f->max_iters + f->d.vl + 2;
+        std::vector<double> tab((size_t)n, 0.0);
+        for (int i = 1; i < n; ++i) tab[i] = std::log((double)i);          // the C library's log = Python's math.log
+        double* dev = nullptr;
+        int rc = az_dev_alloc(f, &dev, (size_t)n);
+        if (rc) return rc;
+        AZ_CUDA_OK(cudaMemcpy(dev, tab.data(), (size_t)n * sizeof(double), cudaMemcpyHostToDevice));
+        f->d.log_tab = dev;
+    }
+    f->d.ucb1 = mode;
+    return AZ_OK;
+}
+
+// MCTS.simulate for every pending leaf (random rollouts; `counter` separates the steps of one search).
+extern "C" int az_eval_rollout(az_forest* f, uint64_t seed, uint64_t counter, void* stream) {
+    if (!f) return az_fail(AZ_EINVAL, "eval_rollout: null forest");
+    const int grid = std::max(1, std::min((f->d.max_leaves + 63) / 64, 148 * 8));
+    az_eval_rollout_kernel<<<grid, 64, 0, (cudaStream_t)stream>>>(f->d, seed, counter);
+    AZ_CUDA_OK(cudaGetLastError());
+    return AZ_OK;
+}
+
+// Whole vanilla search: UCB1 + random rollouts, host loop inside the library (as az_forest_search_hash).
+extern "C" int az_forest_search_rollout(az_forest* f, int iters, uint64_t seed, void* stream) {
+    if (!f || !f->d.ucb1) return az_fail(AZ_ESTATE, "search_rollout: call az_forest_set_mode(f, 1) first");
+    int rc = az_forest_begin_move(f, iters, stream);
+    if (rc) return rc;
+    int done = 0, steps = 0;
+    for (;;) {
+        const int burst = steps == 0 ? (f->d.vl == 1 ? iters + 1 : std::max(8, iters / f->d.vl)) : 4;
+        for (int i = 0; i < burst; ++i) {
+            if ((rc = az_forest_advance(f, stream))) return rc;
+            if ((rc = az_eval_rollout(f, seed, (uint64_t)steps, stream))) return rc;
+            ++steps;
+        }
+        if ((rc = az_forest_counts(f, nullptr, &done, stream))) return rc;
+        if (done >= f->d.n_trees) break;
+        if (steps > 2 * iters + 16) return az_fail(AZ_ESTATE, "search_rollout: did not converge");
+    }
     return AZ_OK;
 }
 

@@ -29,6 +29,8 @@ struct AzForestDev {
     int max_leaves;   // n_trees * vl
     int use_noise;    // Dirichlet noise mixed into the root priors (utils.py:12-27)
     int lp;           // pending leaves of a tree expanded in parallel (<= AZ_LP, <= vl)
+    int ucb1;         // vanilla MCTS (model=None): UCB1 selection in f64 (utils.py:36,43), priors unused
+    const double* log_tab;   // [iters + vl + 2] ln(N) computed on the host with the C library (= math.log of the reference)
 
     AzNode* nodes;    // [n_trees][cap]
 

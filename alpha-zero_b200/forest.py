@@ -135,6 +135,17 @@ class Forest:
         _lib.check(self._L.az_forest_search_hash(self.h, int(iters), C.c_uint64(seed), int(qbits), self.stream),
                    "search_hash")
 
+    def set_mode(self, ucb1):
+        """True: vanilla MCTS (model=None) -- UCB1 selection, children without priors; False: PUCT."""
+        _lib.check(self._L.az_forest_set_mode(self.h, 1 if ucb1 else 0), "set_mode")
+
+    def eval_rollout(self, seed, counter=0):
+        _lib.check(self._L.az_eval_rollout(self.h, C.c_uint64(seed), C.c_uint64(counter), self.stream), "eval_rollout")
+
+    def search_rollout(self, iters, seed):
+        """Whole vanilla search (ai/mcts.py:57-79): UCB1 + uniformly random rollouts on the device."""
+        _lib.check(self._L.az_forest_search_rollout(self.h, int(iters), C.c_uint64(seed), self.stream), "search_rollout")
+
     def search_net(self, net, iters):
         """Whole search with the built-in net (ai.nn.B200Net): CUDA-graph replay per step."""
         _lib.check(self._L.az_forest_search_net(self.h, net.h, int(iters), self.stream), "search_net")

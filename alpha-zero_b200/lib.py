@@ -28,6 +28,9 @@ _SIGS = {
     "az_leaves_to_planes": (i32, [vp, vp, i32, vp]),
     "az_leaves_set_logits": (i32, [vp, vp, vp, i32, vp]),
     "az_forest_search_hash": (i32, [vp, i32, u64, i32, vp]),
+    "az_forest_set_mode": (i32, [vp, i32]),
+    "az_eval_rollout": (i32, [vp, u64, u64, vp]),
+    "az_forest_search_rollout": (i32, [vp, i32, u64, vp]),
     "az_forest_root_visits": (i32, [vp, vp, vp, vp]),
     "az_forest_root_children": (i32, [vp, i32, i32, vp, vp, vp, vp, C.POINTER(i32), C.POINTER(C.c_double), vp]),
     "az_forest_stats": (i32, [vp, vp, i32, vp]),

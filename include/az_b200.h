@@ -74,6 +74,14 @@ AZ_API int az_leaves_to_planes(az_forest* f, float* planes_dev, int max_b, void*
 AZ_API int az_leaves_set_logits(az_forest* f, const float* logits_dev, const float* values_dev, int max_b, void* stream);
 /* (c) the built-in policy/value net, az_net_* below. */
 
+/* Vanilla MCTS (MCTS.mcts(None, ...): ai/mcts.py:57-79, utils.py:36,43).  mode 1 = UCB1 selection in f64 with
+ * ln(N) from the host C library (bit-exact with math.log), children without priors; mode 0 = PUCT (default). */
+AZ_API int az_forest_set_mode(az_forest* f, int mode);
+/* MCTS.simulate for every pending leaf: uniformly random legal moves to the end of the game (bitboard rules on
+ * the device, splitmix64 streams keyed by seed / counter / tree); writes value = +1 / -1 / 0 for the side to move. */
+AZ_API int az_eval_rollout(az_forest* f, uint64_t seed, uint64_t counter, void* stream);
+/* Whole vanilla search (mode 1): advance + rollouts, host loop inside the library. */
+AZ_API int az_forest_search_rollout(az_forest* f, int iters, uint64_t seed, void* stream);
 /* Whole search with the hash evaluator, host loop inside the library. */
 AZ_API int az_forest_search_hash(az_forest* f, int iters, uint64_t seed, int qbits, void* stream);
 

@@ -261,11 +261,28 @@ static double puct64(double W, double P, int n, double s) {
     return W / (double)n + u;
 }
 
+/* utils.py:29-44 'normal' branch (model=None, vanilla MCTS): Python floats = f64; an unvisited child scores
+ * sqrt(2 ln Np / 1), not +inf.  Selected by azo_set_ucb1(1); the priors are then unused (node.py:58). */
+static int g_ucb1 = 0;
+void azo_set_ucb1(int on) { g_ucb1 = on; }
+static double ucb1(double W, int n, double two_ln_np) {
+    double e = sqrt(two_ln_np / (double)(n + 1));
+    if (n == 0) return e;
+    return W / (double)n + e;
+}
+
 /* node.py:42-47: first maximum in child order. */
 static int select_child(const ONode* nd, int node, int noisy_root) {
     const ONode* p = &nd[node];
     int pn = p->visit + p->vloss, best = p->first;
-    if (noisy_root) {
+    if (g_ucb1) {
+        double s = 2 * log((double)pn), bs = 0;
+        for (int c = 0; c < p->nchild; c++) {
+            const ONode* ch = &nd[p->first + c];
+            double sc = ucb1(ch->W - (double)ch->vloss, ch->visit + ch->vloss, s);
+            if (c == 0 || sc > bs) { bs = sc; best = p->first + c; }
+        }
+    } else if (noisy_root) {
         double s = sqrt((double)pn), bs = 0;
         for (int c = 0; c < p->nchild; c++) {
             const ONode* ch = &nd[p->first + c];

@@ -406,6 +406,76 @@ def select_child(node):
     return best
 
 
+def ucb1_scores(node):
+    """utils.py:29-44, 'normal' branch (model=None): Python floats (f64) throughout,
+    unvisited child: sqrt(2 ln N_p / 1) -- finite, not +inf; visited: W/n + sqrt(2 ln N_p / (n+1))."""
+    for ch in node.children:
+        if ch.visit == 0:
+            ch.ucb = math.sqrt(2 * math.log(node.visit) / (ch.visit + 1))
+        else:
+            ch.ucb = (ch.value / ch.visit) + math.sqrt(2 * math.log(node.visit) / (ch.visit + 1))
+
+
+def select_child_ucb1(node):
+    """node.py:42-47 with mode 'normal': first maximum in child order."""
+    ucb1_scores(node)
+    best = node.children[0]
+    for ch in node.children[1:]:
+        if ch.ucb > best.ucb:
+            best = ch
+    return best
+
+
+def rollout(g, board, node, rng=np.random):
+    """ai/mcts.py:62-79 (MCTS.simulate): uniformly random legal moves to the end of the game on a copy of the
+    board; +1 if the player who moved INTO `node` wins, -1 if the side to move at `node` wins, 0 for a draw."""
+    sim = board.copy()
+    player, mc, winner = node.player, node.move_count, -1
+    while winner == -1 and mc < g.state_dim:
+        moves = valid_moves(g, sim)
+        a = moves[rng.randint(len(moves))]
+        player = make_move(g, sim, player, a)
+        mc += 1
+        winner = check_winner(g, sim, 1 - player, a)
+    if winner != -1:
+        return 1 if winner == (1 - node.player) else -1
+    return 0
+
+
+def mcts_vanilla(g, board, root, iterations, simulate=None, rng=np.random):
+    """ai/mcts.py:11-60 with model=None: UCB1 selection, children without priors, result = simulate(...)
+    (default: the random rollout above; tests inject a deterministic function of the leaf position the way the
+    golden generator replaces MCTS.simulate in the reference)."""
+    for _ in range(iterations):
+        node = root
+        trace = [root]
+        while node.children:
+            node = select_child_ucb1(node)
+            trace.append(node)
+            make_move(g, board, 1 - node.player, node.action)
+        if node.parent is not None:
+            if check_winner(g, board, 1 - node.player, node.action) != -1:
+                backup(g, trace, 1, board)
+                continue
+            if node.move_count == g.state_dim:
+                backup(g, trace, 0, board)
+                continue
+        moves = valid_moves(g, board)
+        for mv in moves:                                   # node.py:58: no prior
+            node.children.append(Node(node, mv, 1 - node.player, node.move_count + 1))
+        result = simulate(g, board, node) if simulate is not None else rollout(g, board, node, rng)
+        backup(g, trace, result, board)
+
+
+def hash_simulate(seed, qbits=16):
+    """Deterministic stand-in for the rollout in parity runs: minus the hash evaluator's value of the leaf
+    (the same number the GPU's hash evaluator backs up, ai/mcts.py:56 sign convention)."""
+    def f(g, board, node):
+        _, value = hash_eval_from_key(g, hash_eval_key(g, canonical_board(g, board, node.player), seed), qbits)
+        return -float(value)
+    return f
+
+
 def expand(g, node, moves, priors):
     """node.py:50-59: one child per legal move in list order; prior gathered from the
     UNMASKED, un-renormalised policy vector by action index."""

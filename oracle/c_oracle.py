@@ -86,6 +86,11 @@ def search_batch(g, cells, players, mcs, iters, vl=1, seed=0, qbits=16, noise=No
     return dict(n_children=nc, cells=oc, visits=ov, W=oW, P=oP, root_visit=rv, root_value=rW, stats=stats)
 
 
+def set_ucb1(on):
+    """Vanilla-MCTS selection (utils.py:36,43) instead of PUCT for the following searches."""
+    lib().azo_set_ucb1(int(bool(on)))
+
+
 def legal(g, cells):
     out = np.zeros(g.rows * g.cols, np.int32)
     c = np.ascontiguousarray(cells, dtype=np.uint8)

@@ -161,6 +161,49 @@ def ref_search(R, g, opening, iters, seed, qbits, noise):
     }
 
 
+def ref_search_vanilla(R, g, opening, iters, seed, qbits=16):
+    """The reference's vanilla mode (model=None: UCB1 + expansion without priors, ai/mcts.py:57-59, utils.py:36,43)
+    with its loop unmodified; only the RNG-bound rollout MCTS.simulate is replaced by a deterministic function of
+    the leaf position (minus the hash evaluator's value), so the search is reproducible."""
+    G, board, player, mc = setup_position(R, g, opening)
+    MCTS, Node = R["ai"].MCTS, R["ai"].Node
+    saved = MCTS.simulate
+
+    def simulate(Game, b, node):
+        canon = orc.canonical_board(g, b, node.currentPlayer)
+        _, value = orc.hash_eval_from_key(g, orc.hash_eval_key(g, canon, seed), qbits)
+        return -float(value)
+    MCTS.simulate = staticmethod(simulate)
+    before = board.copy()
+    root = Node(None, None, player, mc)
+    try:
+        MCTS.mcts(None, board, root, G, iters)
+    finally:
+        MCTS.simulate = saved
+    assert np.array_equal(before, board), "reference must restore the board"
+    return {
+        "actions": [int(G.get_action_idx(ch.prevAction)) for ch in root.children],
+        "visits": [int(ch.visit) for ch in root.children],
+        "values": [float(ch.value).hex() for ch in root.children],
+        "root_visit": int(root.visit),
+        "root_value": float(root.value).hex(),
+    }
+
+
+def gen_vanilla(R, rng):
+    cases = []
+    plan = [(orc.TICTACTOE, [0, 2, 5], [1, 2, 50, 400]), (orc.CONNECT4, [0, 4, 15, 30], [8, 200, 800]),
+            (orc.GOMOKU, [0, 3, 12, 30], [2, 200, 800])]
+    for g, opens, iters_list in plan:
+        for n_open in opens:
+            opening = random_opening(R, g, n_open, rng)
+            for iters in iters_list:
+                seed = int(rng.integers(1 << 40))
+                cases.append({"game": g.name, "rows": g.rows, "opening": opening, "iters": iters, "seed": seed,
+                              "qbits": 16, "result": ref_search_vanilla(R, g, opening, iters, seed)})
+    return cases
+
+
 def gen_puct(R, rng, n_cases):
     """utils.calcUcbOfChildrenFromParent('network') on synthetic nodes -> exact score bits."""
     Node, utils = R["ai"].Node, R["utils"]
@@ -268,6 +311,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ref", default="/root/reference")
     ap.add_argument("--out", default=os.path.join(os.path.dirname(HERE), "tests", "golden"))
+    ap.add_argument("--only", default="", help="'vanilla': write only search_vanilla.json (own RNG stream)")
     args = ap.parse_args()
     os.makedirs(args.out, exist_ok=True)
     R = load_reference(args.ref)
@@ -278,6 +322,9 @@ def main():
             json.dump(obj, f, separators=(",", ":"))
         print("wrote", name, os.path.getsize(os.path.join(args.out, name)), "bytes")
 
+    if args.only == "vanilla":
+        dump("search_vanilla.json", gen_vanilla(R, np.random.default_rng(20261105)))
+        return
     g15 = orc.gomoku_spec(15)
     # 1. rules ------------------------------------------------------------------------
     dump("rules_tictactoe.json", gen_rules(R, orc.TICTACTOE, 40, rng))
@@ -304,6 +351,7 @@ def main():
                     cases.append({"game": g.name, "rows": g.rows, "opening": opening, "iters": iters,
                                   "seed": seed, "qbits": qbits, "noise": noise, "result": res})
     dump("search.json", cases)
+    dump("search_vanilla.json", gen_vanilla(R, np.random.default_rng(20261105)))
     # 3. PUCT arithmetic ----------------------------------------------------------------
     dump("puct.json", gen_puct(R, rng, 400))
     # 4. self-play trajectories + buffer transform ---------------------------------------

@@ -49,6 +49,25 @@ def test_search_golden():
         assert float(r["root_value"][0]) == fhex(ref["root_value"])
 
 
+def test_vanilla_search_golden():
+    """UCB1 selection (model=None) against searches of the reference itself (tests/golden/search_vanilla.json)."""
+    co.set_ucb1(True)
+    try:
+        for case in load_json("search_vanilla.json"):
+            g = spec_of(case)
+            board, player, mc = position_after(g, case["opening"])
+            r = co.search_batch(g, co.cells_from_planes(board)[None], [player], [mc], case["iters"], 1, case["seed"], case["qbits"])
+            ref = case["result"]
+            nc = int(r["n_children"][0])
+            assert nc == len(ref["actions"])
+            assert r["visits"][0, :nc].tolist() == ref["visits"]
+            assert r["W"][0, :nc].tolist() == [fhex(v) for v in ref["values"]]
+            assert int(r["root_visit"][0]) == ref["root_visit"]
+            assert float(r["root_value"][0]) == fhex(ref["root_value"])
+    finally:
+        co.set_ucb1(False)
+
+
 def py_vl_search(g, ev, board, player, mc, iters, vl):
     """Python statement of the virtual-loss step machine the C oracle and the CUDA path
     implement (build-defined; no reference behaviour).  vl=1 is orc.mcts exactly."""

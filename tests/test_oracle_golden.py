@@ -85,6 +85,39 @@ def test_search_cases():
         assert got["root_value"] == fhex(ref["root_value"])
 
 
+def test_vanilla_search_cases():
+    """model=None (UCB1, children without priors; ai/mcts.py:57-59, utils.py:36,43): the reference's loop with
+    MCTS.simulate replaced by a deterministic function of the leaf (oracle/gen_golden.py: ref_search_vanilla)."""
+    cases = load_json("search_vanilla.json")
+    assert len(cases) >= 30
+    for case in cases:
+        g = spec_of(case)
+        board, player, mc = position_after(g, case["opening"])
+        before = board.copy()
+        root = orc.Node(None, None, player, mc)
+        orc.mcts_vanilla(g, board, root, case["iters"], simulate=orc.hash_simulate(case["seed"], case["qbits"]))
+        assert np.array_equal(board, before)
+        ref = case["result"]
+        assert [orc.action_idx(g, ch.action) for ch in root.children] == ref["actions"]
+        assert [ch.visit for ch in root.children] == ref["visits"]
+        assert [float(ch.value) for ch in root.children] == [fhex(v) for v in ref["values"]]
+        assert root.visit == ref["root_visit"] == case["iters"]
+        assert float(root.value) == fhex(ref["root_value"])
+
+
+def test_rollout_statistics():
+    """The random rollout (ai/mcts.py:62-79) from the empty TicTacToe board: first-player win / draw / loss
+    frequencies of uniformly random play are known to be 58.5 % / 12.7 % / 28.8 %; 4000 rollouts must land
+    within 3 points."""
+    g = orc.TICTACTOE
+    rng = np.random.RandomState(7)
+    root = orc.Node(None, None, 0, 0)
+    res = [orc.rollout(g, orc.new_board(g), root, rng) for _ in range(4000)]
+    # root.player = 0 is to move, so +1 means player 1 (the one who "moved into" the root) wins
+    lose, draw, win = res.count(1) / 4000, res.count(0) / 4000, res.count(-1) / 4000
+    assert abs(win - 0.585) < 0.03 and abs(draw - 0.127) < 0.03 and abs(lose - 0.288) < 0.03, (win, draw, lose)
+
+
 def test_selfplay_and_buffer_transform():
     recs = load_json("selfplay.json")
     arrs = np.load(f"{GOLDEN}/selfplay.npz")
