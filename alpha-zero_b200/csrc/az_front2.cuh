@@ -42,6 +42,97 @@ __device__ __forceinline__ uint64_t umma_desc_mn128(uint32_t smem_addr, uint32_t
 }
 }  // namespace azptx
 
+// One rewritten token row of the A tile per thread.  Only the rows of real board cells change from tile to tile
+// (the cls row, pad rows and the one-hot columns are constants): active row i = cell i % (T-1) of board i / (T-1).
+struct AzRowBuilder {
+    bool on;
+    int b, t, r, rs, ls, ob;
+    uint32_t inb, pmask;
+    int sh[5], ks[5];
+    uint32_t cm[5];
+    ulonglong2 w_cur, w_nxt;
+    uint32_t s_cur, s_nxt;                                       // raw side-to-move byte, 0xFFFFFFFF = row unused / board beyond the batch
+    uint64_t kw0, kw1;
+
+    __device__ __forceinline__ void init(const AzFrontArgs& a, int ai, int TS) {
+        const int T = a.T, P = a.patch, half = P >> 1;
+        const uint32_t colmask = (1u << a.cols) - 1u;
+        pmask = (1u << P) - 1u;
+        b = ai / (T - 1);
+        t = 1 + ai - b * (T - 1);
+        on = ai < a.nb * (T - 1);
+        r = b * TS + t;
+        ob = a.kc + t;
+        const int cr = (t - 1) / a.cols, cc = (t - 1) - cr * a.cols;
+        rs = cc >= half ? cc - half : 0;
+        ls = cc >= half ? 0 : half - cc;
+        inb = 0;                                                 // in-bounds taps of the window (plane 2 is all ones)
+        for (int kr = 0; kr < P; ++kr) {
+            const int rr = cr + kr - half;
+            if (rr >= 0 && rr < a.rows) inb |= (((colmask >> rs) << ls) & pmask) << (kr * P);
+        }
+        if (!on) inb = 0u;
+#pragma unroll
+        for (int kr = 0; kr < 5; ++kr) {                         // window rows outside the board / beyond the patch: empty mask
+            const int rr = cr + kr - half;
+            const bool ok = kr < P && rr >= 0 && rr < a.rows && on;
+            ks[kr] = kr < P ? kr * P : 0;
+            sh[kr] = ok ? rr * a.cols : 0;
+            cm[kr] = ok ? colmask : 0u;
+        }
+    }
+    // loads only: nothing consumes the registers until the next tile is encoded
+    __device__ __forceinline__ void fetch(const AzFrontArgs& a, int tile, int tiles, int items, ulonglong2& w, uint32_t& sm) const {
+        const int item = tile * a.nb + b;
+        w = make_ulonglong2(0ull, 0ull);
+        sm = 0xFFFFFFFFu;
+        if (tile < tiles && on && item < items) {
+            w = *reinterpret_cast<const ulonglong2*>(a.leaf_words + (size_t)(a.batch.offset + item) * 2);
+            sm = a.leaf_player[a.batch.offset + item];
+        }
+    }
+    // K columns of the row as two 64-bit words: taps of plane 0 at bit 0, plane 1 at bit pp, plane 2 (in-bounds taps
+    // when side 1 is to move) at bit 2*pp, one-hot token index at bit kc + t
+    __device__ __forceinline__ void encode(const AzFrontArgs& a) {
+        const int pp = a.patch * a.patch;
+        uint64_t k0 = ob < 64 ? 1ull << ob : 0ull, k1 = ob >= 64 ? 1ull << (ob - 64) : 0ull;
+        uint32_t p0 = 0, p1 = 0;
+#pragma unroll
+        for (int kr = 0; kr < 5; ++kr) {
+            const uint32_t b0 = (uint32_t)(w_cur.x >> sh[kr]) & cm[kr];
+            const uint32_t b1 = (uint32_t)(w_cur.y >> sh[kr]) & cm[kr];
+            p0 |= (((b0 >> rs) << ls) & pmask) << ks[kr];
+            p1 |= (((b1 >> rs) << ls) & pmask) << ks[kr];
+        }
+        k0 |= (uint64_t)p0 | ((uint64_t)p1 << pp);
+        if (a.planes == 3 && s_cur != 0u && s_cur != 0xFFFFFFFFu) {      // side 1 to move; the taps may straddle bit 64
+            const uint64_t ib = inb;
+            k0 |= ib << (2 * pp);
+            if (3 * pp > 64) k1 |= ib >> (64 - 2 * pp);
+        }
+        kw0 = k0;
+        kw1 = k1;
+    }
+    // every LUT read of the row first, then the stores: the compiler cannot prove that the LUT and the tile do not
+    // alias, so interleaved they run as one serial load -> store chain (85 cycles per chunk)
+    __device__ __forceinline__ void store(unsigned char* stage, uint32_t tile_bytes, const uint2* s_lut, int nch) const {
+        if (!on) return;
+        unsigned char* arow = stage + (size_t)r * 128;
+        const int sw = r & 7;
+        uint2 lo[10], hi[10];
+#pragma unroll
+        for (int c = 0; c < 10; ++c) {
+            const uint32_t by = (uint32_t)((c < 8 ? kw0 : kw1) >> ((c & 7) * 8)) & 0xFFu;
+            lo[c] = s_lut[by & 15u];
+            hi[c] = s_lut[by >> 4];
+        }
+#pragma unroll
+        for (int c = 0; c < 10; ++c)
+            if (c < nch)
+                *reinterpret_cast<uint4*>(arow + (c < 8 ? 0u : tile_bytes) + (((c & 7) ^ sw) << 4)) = make_uint4(lo[c].x, lo[c].y, hi[c].x, hi[c].y);
+    }
+};
+
 template <int TS8>
 __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __grid_constant__ CUtensorMap tm_wst, AzFrontArgs a) {
     extern __shared__ unsigned char smem_dyn[];
@@ -91,7 +182,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
         azptx::prefetch_tmap(&tm_wst);
         azptx::mbar_init(w_full, 1);
         for (int i = 0; i < NA; ++i) {
-            azptx::mbar_init(&a_full[i], AZ_FRONT2_BUILDERS);
+            azptx::mbar_init(&a_full[i], a.nb * (a.T - 1) > AZ_FRONT2_BUILDERS ? AZ_FRONT2_BUILDERS + 32 : AZ_FRONT2_BUILDERS);
             azptx::mbar_init(&a_empty[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
@@ -172,69 +263,13 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
             }
         }
     } else if (warp >= 12 && warp < 15) {
-        // ------------------------------ A-tile builders ------------------------------------------------
-        // Only the rows of real board cells change from tile to tile (the cls row, pad rows and the one-hot
-        // columns are constants): thread bt rewrites active rows bt and bt + 96, active row i = cell i % (T-1)
-        // of board i / (T-1).
+        // ------------------------------ A-tile builders: active row bt of every tile -------------------
+        // (active rows 96.. of a tile, if any, are written by warp 8 between its U epilogues)
         const int bt = threadIdx.x - 384;
-        const int nact = a.nb * (T - 1);
-        const int half = P >> 1, pp = P * P;
-        const uint32_t colmask = (1u << a.cols) - 1u, pmask = (1u << P) - 1u;
-        int r_b[2], r_t[2], r_rs[2], r_ls[2], r_cr[2];
-        uint32_t r_inb[2];
-        bool r_on[2];
-#pragma unroll
-        for (int pass = 0; pass < 2; ++pass) {
-            const int ai = bt + pass * AZ_FRONT2_BUILDERS;
-            const int bb = ai / (T - 1), t = 1 + ai - bb * (T - 1);
-            r_b[pass] = bb;
-            r_t[pass] = t;
-            r_on[pass] = ai < nact;
-            int cr = 0, cc = 0;
-            if (t > 0) { cr = (t - 1) / a.cols; cc = (t - 1) - cr * a.cols; }
-            r_cr[pass] = cr;
-            r_rs[pass] = cc >= half ? cc - half : 0;
-            r_ls[pass] = cc >= half ? 0 : half - cc;
-            uint32_t inb = 0;                                        // in-bounds taps of the window (plane 2 is all ones)
-            for (int kr = 0; kr < P; ++kr) {
-                const int rr = cr + kr - half;
-                if (rr >= 0 && rr < a.rows) inb |= (((colmask >> r_rs[pass]) << r_ls[pass]) & pmask) << (kr * P);
-            }
-            r_inb[pass] = (r_on[pass] && t > 0) ? inb : 0u;
-        }
-        int g_sh[2][5];
-        uint32_t g_cm[2][5];
-        int g_ks[5];
-#pragma unroll
-        for (int kr = 0; kr < 5; ++kr) {
-            g_ks[kr] = kr < P ? kr * P : 0;
-#pragma unroll
-            for (int pass = 0; pass < 2; ++pass) {
-                const int rr = r_cr[pass] + kr - half;
-                const bool ok = kr < P && rr >= 0 && rr < a.rows && r_on[pass] && r_t[pass] > 0;
-                g_sh[pass][kr] = ok ? rr * a.cols : 0;
-                g_cm[pass][kr] = ok ? colmask : 0u;
-            }
-        }
-        ulonglong2 w_cur[2], w_nxt[2];
-        uint32_t s_cur[2], s_nxt[2];
-        auto fetch = [&](int tile, ulonglong2 (&w)[2], uint32_t (&sm)[2]) {
-#pragma unroll
-            for (int pass = 0; pass < 2; ++pass) {
-                const int item = tile * a.nb + r_b[pass];
-                w[pass] = make_ulonglong2(0ull, 0ull);
-                sm[pass] = 0xFFFFFFFFu;
-                if (tile < tiles && r_on[pass] && item < items) {
-                    w[pass] = *reinterpret_cast<const ulonglong2*>(a.leaf_words + (size_t)(a.batch.offset + item) * 2);
-                    sm[pass] = a.leaf_player[a.batch.offset + item];
-                }
-            }
-        };
-        // one-hot columns and pad rows never change: every stage is initialised once
         const int nch = (a.kc + 7) >> 3;
         int it = 0;
         AZ_TR(1, 5);
-        for (int r = bt; r < a.nb * TS; r += AZ_FRONT2_BUILDERS) {   // the stages were zero-filled before the CTA-wide sync
+        for (int r = bt; r < a.nb * TS; r += AZ_FRONT2_BUILDERS) {   // one-hot columns: the stages were zero-filled before the CTA-wide sync
             const int t = r % TS;
             if (t >= T) continue;
             const int ob = a.kc + t;
@@ -242,66 +277,27 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
                 *reinterpret_cast<unsigned short*>(s_a + (size_t)st * 2 * tile_bytes + (size_t)(ob >> 6) * tile_bytes + (size_t)r * 128 +
                                                    (((((uint32_t)ob & 63u) >> 3) ^ ((uint32_t)r & 7u)) << 4) + (ob & 7) * 2) = 0x3F80;
         }
+        AzRowBuilder rb;
+        rb.init(a, bt, TS);
         AZ_TR(1, 6);
         wait_upstream();
-        fetch(blockIdx.x, w_cur, s_cur);
+        rb.fetch(a, blockIdx.x, tiles, items, rb.w_cur, rb.s_cur);
         AZ_TR(1, 7);
         for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int st = it % NA;
-            fetch(tile + gridDim.x, w_nxt, s_nxt);
-            uint64_t kw0[2], kw1[2];
-#pragma unroll
-            for (int pass = 0; pass < 2; ++pass) {
-                if (pass == 1 && nact <= AZ_FRONT2_BUILDERS) { kw0[1] = kw1[1] = 0ull; continue; }   // uniform: no second row
-                const int ob = a.kc + r_t[pass];
-                uint64_t k0 = ob < 64 ? 1ull << ob : 0ull, k1 = ob >= 64 ? 1ull << (ob - 64) : 0ull;
-                uint32_t p0 = 0, p1 = 0;
-#pragma unroll
-                for (int kr = 0; kr < 5; ++kr) {
-                    const uint32_t b0 = (uint32_t)(w_cur[pass].x >> g_sh[pass][kr]) & g_cm[pass][kr];
-                    const uint32_t b1 = (uint32_t)(w_cur[pass].y >> g_sh[pass][kr]) & g_cm[pass][kr];
-                    p0 |= (((b0 >> r_rs[pass]) << r_ls[pass]) & pmask) << g_ks[kr];
-                    p1 |= (((b1 >> r_rs[pass]) << r_ls[pass]) & pmask) << g_ks[kr];
-                }
-                k0 |= (uint64_t)p0 | ((uint64_t)p1 << pp);
-                if (a.planes == 3 && s_cur[pass] != 0u && s_cur[pass] != 0xFFFFFFFFu) {
-                    const uint64_t inb = r_inb[pass];
-                    k0 |= inb << (2 * pp);
-                    if (3 * pp > 64) k1 |= inb >> (64 - 2 * pp);
-                }
-                kw0[pass] = k0;
-                kw1[pass] = k1;
-            }
+            rb.fetch(a, tile + gridDim.x, tiles, items, rb.w_nxt, rb.s_nxt);     // in flight while this tile is encoded
+            rb.encode(a);
             AZ_TR(1, 0);
             azptx::mbar_wait(&a_empty[st], ((it / NA) & 1) ^ 1);
             AZ_TR(1, 1);
-#pragma unroll
-            for (int pass = 0; pass < 2; ++pass) {
-                if (!r_on[pass]) continue;
-                const int r = r_b[pass] * TS + r_t[pass];
-                unsigned char* arow = s_a + (size_t)st * 2 * tile_bytes + (size_t)r * 128;
-                const int sw = r & 7;
-                // every LUT read of the row first, then the stores: the compiler cannot prove that the LUT and the
-                // tile do not alias, so interleaved they run as one serial load -> store chain (85 cycles per chunk)
-                uint2 lo[10], hi[10];
-#pragma unroll
-                for (int c = 0; c < 10; ++c) {
-                    const uint32_t by = (uint32_t)((c < 8 ? kw0[pass] : kw1[pass]) >> ((c & 7) * 8)) & 0xFFu;
-                    lo[c] = s_lut[by & 15u];
-                    hi[c] = s_lut[by >> 4];
-                }
-#pragma unroll
-                for (int c = 0; c < 10; ++c)
-                    if (c < nch)
-                        *reinterpret_cast<uint4*>(arow + (c < 8 ? 0u : tile_bytes) + (((c & 7) ^ sw) << 4)) = make_uint4(lo[c].x, lo[c].y, hi[c].x, hi[c].y);
-            }
+            rb.store(s_a + (size_t)st * 2 * tile_bytes, tile_bytes, s_lut, nch);
             AZ_TR(1, 3);
-            azptx::fence_proxy_async();
+            azptx::fence_proxy_async();                              // generic-proxy writes -> visible to the MMA
             AZ_TR(1, 4);
             azptx::mbar_arrive(&a_full[st]);
             AZ_TR(1, 2);
-#pragma unroll
-            for (int pass = 0; pass < 2; ++pass) { w_cur[pass] = w_nxt[pass]; s_cur[pass] = s_nxt[pass]; }
+            rb.w_cur = rb.w_nxt;
+            rb.s_cur = rb.s_nxt;
         }
     } else if (warp < 8) {
         // ------------------------------ S groups: statistic, scores, softmax -> Wblk --------------------
@@ -422,9 +418,34 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
         const int q = warp & 3;
         const int k = q * 32 + lane;                                 // TMEM lane = K index
         const int pairs = a.nb * a.H;
+        // warp 8 also writes the active rows 96.. of every tile (a tile of two 7x7 boards has 98).  It builds tile j
+        // and THEN drains the accumulator of tile j - NA: both wait for the same event (the U MMAs of tile j - NA),
+        // so the build never queues behind a recent MMA (with a lag of 2 the chain U MMA -> epilogue -> build ->
+        // statistics MMA serialised the whole pipeline: 3.4 k cycles per tile instead of 1.5 k).
+        const bool extra = a.nb * (T - 1) > AZ_FRONT2_BUILDERS;
+        const bool assist = warp == 8 && extra;
+        const int ulag = extra ? NA : 0;
+        const int nch = (a.kc + 7) >> 3;
+        AzRowBuilder rb;
+        rb.init(a, AZ_FRONT2_BUILDERS + lane, TS);
         wait_upstream();
-        int it = 0;
-        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+        if (assist) rb.fetch(a, blockIdx.x, tiles, items, rb.w_cur, rb.s_cur);
+        const int n_my = tiles > (int)blockIdx.x ? (tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+        for (int j = 0; j < n_my + ulag; ++j) {
+            if (assist && j < n_my) {
+                const int bst = j % NA, btile = blockIdx.x + j * gridDim.x;
+                rb.fetch(a, btile + gridDim.x, tiles, items, rb.w_nxt, rb.s_nxt);
+                rb.encode(a);
+                azptx::mbar_wait(&a_empty[bst], ((j / NA) & 1) ^ 1);
+                rb.store(s_a + (size_t)bst * 2 * tile_bytes, tile_bytes, s_lut, nch);
+                azptx::fence_proxy_async();
+                azptx::mbar_arrive(&a_full[bst]);
+                rb.w_cur = rb.w_nxt;
+                rb.s_cur = rb.s_nxt;
+            }
+            const int it = j - ulag;
+            if (it < 0) continue;
+            const int tile = blockIdx.x + it * gridDim.x;
             const int g = it & 1, u = it >> 1;
             AZ_TR(3, 0);
             azptx::mbar_wait(&u_full[g], u & 1);

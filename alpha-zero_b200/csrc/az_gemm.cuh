@@ -53,6 +53,7 @@ struct AzGemmArgs {
     // AZ_EPI_HEAD: softmax over columns [0, head_A) -> priors, tanh(column head_A) -> values
     int head_A;
     float *priors, *values, *logits;
+    int dbg;                    // experiments (tools/gemm_bench.py): bit 0 no MMA, bit 1 no W loads, bit 2 no A loads (results are garbage)
 };
 
 __device__ __forceinline__ int az_gemm_rows(const AzGemmArgs& a) {
@@ -215,6 +216,14 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 const int m_blk = tile / n_tiles, n_blk = tile - m_blk * n_tiles;
                 for (int kb = 0; kb < kblocks; ++kb) {
                     azptx::mbar_wait(&empty[stage], phase ^ 1);
+                    if (args.dbg & 6) {
+                        const uint32_t bytes = ((args.dbg & 4) ? 0 : Cfg::A_BYTES) + ((args.dbg & 2) ? 0 : Cfg::B_BYTES);
+                        if (bytes) azptx::mbar_arrive_expect_tx(&full[stage], bytes); else azptx::mbar_arrive(&full[stage]);
+                        if (!(args.dbg & 4)) azptx::tma_load_2d(s_a + stage * Cfg::A_BYTES, &tm_a, &full[stage], kb * Cfg::BK, m_blk * Cfg::BM);
+                        if (!(args.dbg & 2)) azptx::tma_load_2d(s_b + stage * Cfg::B_BYTES, &tm_b, &full[stage], kb * Cfg::BK, n_blk * BN);
+                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
                     azptx::mbar_arrive_expect_tx(&full[stage], Cfg::A_BYTES + Cfg::B_BYTES);
                     azptx::tma_load_2d(s_a + stage * Cfg::A_BYTES, &tm_a, &full[stage], kb * Cfg::BK, m_blk * Cfg::BM);
                     azptx::tma_load_2d(s_b + stage * Cfg::B_BYTES, &tm_b, &full[stage], kb * Cfg::BK, n_blk * BN);
@@ -232,7 +241,10 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             for (int kb = 0; kb < kblocks; ++kb) {
                 azptx::mbar_wait(&full[stage], phase);
                 azptx::tc_fence_after();
-                if (lane == 0) {
+                if (lane == 0 && (args.dbg & 1)) {
+                    azptx::mbar_arrive(&empty[stage]);
+                    if (kb == kblocks - 1) azptx::mbar_arrive(&tfull[as]);
+                } else if (lane == 0) {
                     const uint64_t da = azptx::umma_desc_k128(azptx::smem_u32(s_a + stage * Cfg::A_BYTES));
                     const uint64_t db = azptx::umma_desc_k128(azptx::smem_u32(s_b + stage * Cfg::B_BYTES));
 #pragma unroll

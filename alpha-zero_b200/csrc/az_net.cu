@@ -249,6 +249,7 @@ extern "C" int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const
     a.K = K;
     a.m_fixed = M;
     a.m_count = nullptr;
+    if (const char* e = getenv("AZ_GEMM_DBG")) a.dbg = atoi(e);
     return az_launch_gemm(ta, tb, a, epi, M, (cudaStream_t)stream, bn);
 }
 

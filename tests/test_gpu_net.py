@@ -86,6 +86,30 @@ def test_net_matches_torch_fp32(rows, cols, C, A, dim, depth, patch, B):
     eng.close()
 
 
+@pytest.mark.parametrize("env", [{"AZ_PAIR_MIN_ROWS": "512"}, {"AZ_NO_FRONT2": "1"}, {"AZ_NO_FRONT2": "1", "AZ_PAIR_MIN_ROWS": "512"}])
+def test_net_kernel_variants_match_torch(env, monkeypatch):
+    """The same tolerance on the other kernel choices of the cls-row path: CTA-pair GEMM tiles (az_gemm2.cuh, default
+    only from 16384 boards per pass) and the first fused front kernel (az_front.cuh) instead of the reassociated one."""
+    import torch
+    from alpha_zero_b200.ai.nn import B200Net
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    net = make_net(6, 7, 3, 7, 512, 1, 5)
+    rng = np.random.default_rng(2)
+    B = 3000
+    x = (rng.random((B, 3, 6, 7)) < 0.3).astype(np.float32)
+    x[:, 1] *= (1 - x[:, 0])
+    x[:, 2] = rng.integers(0, 2, B).astype(np.float32)[:, None, None]
+    eng = B200Net(net, max_batch=4096)
+    flags = eng.path_flags()
+    assert bool(flags & 4) == ("AZ_PAIR_MIN_ROWS" in env) and bool(flags & 2) == ("AZ_NO_FRONT2" not in env)
+    l, v, p = eng.forward_numpy(x)
+    with torch.no_grad():
+        rl, rv = net(torch.from_numpy(x[:600]))
+    check_close(l[:600], v[:600], p[:600], rl.numpy(), rv.numpy())
+    eng.close()
+
+
 @pytest.mark.parametrize("g,n,iters,vl,dim,depth", [(orc.CONNECT4, 256, 200, 1, 128, 1), (orc.GOMOKU, 128, 160, 1, 64, 2),
                                                     (orc.GOMOKU, 96, 200, 4, 64, 1), (orc.TICTACTOE, 64, 100, 1, 64, 1)])
 def test_search_with_net_replays_exactly_in_oracle(g, n, iters, vl, dim, depth):

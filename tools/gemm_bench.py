@@ -59,4 +59,4 @@ for name, M, N, K, epi in shapes:
         e1.record()
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) * 1000 / 200
-        print(f"{name:10s} M{M} N{N} K{K} bn={bn:5d}: {us:7.2f} us  {2.0 * M * N * K / us / 1e6:7.1f} TFLOP/s", flush=True)
+        print(f"{name:10s} M{M} N{N} K{K} bn={bn:5d} dbg={os.environ.get('AZ_GEMM_DBG', '0')}: {us:7.2f} us  {2.0 * M * N * K / us / 1e6:7.1f} TFLOP/s", flush=True)
