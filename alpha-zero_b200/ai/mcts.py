@@ -50,10 +50,16 @@ class MCTS:
         if isinstance(model, B200Net):
             return model
         if isinstance(model, Net):
+            import weakref
             stamp = tuple(p._version for p in model.parameters())
             ent = MCTS._engines.get(id(model))
+            if ent is not None and ent[3]() is not model:   # id() of a collected Net reused by another model
+                ent[0].close()
+                ent = None
             if ent is None or ent[2] < max_batch:
-                ent = [B200Net(model, max_batch=max_batch), stamp, max_batch]
+                for k in [k for k, e in MCTS._engines.items() if e[3]() is None]:   # engines of collected models
+                    MCTS._engines.pop(k)[0].close()
+                ent = [B200Net(model, max_batch=max_batch), stamp, max_batch, weakref.ref(model)]
                 MCTS._engines[id(model)] = ent
             elif ent[1] != stamp:                       # weights changed since the upload
                 ent[0].load_state_dict(model.state_dict())
