@@ -1182,7 +1182,8 @@ extern "C" long long az_net_launch_count(az_net* n) { return n ? (long long)n->l
 // leaves; the step is captured once into a CUDA graph and replayed (no per-node host work).
 // ======================================================================================
 struct AzStepGraph {
-    unsigned long long kernels = 0;     // kernels in one captured step
+    unsigned long long kernels = 0;     // kernels in one captured graph
+    int steps = 1;                      // search steps per graph
     az_forest* f = nullptr;
     int iters = -1, use_noise = -1;
     cudaGraphExec_t exec = nullptr;
@@ -1218,7 +1219,12 @@ extern "C" int az_forest_search_net(az_forest* f, az_net* n, int iters, void* st
         cudaGraph_t graph = nullptr;
         AZ_CUDA_OK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
         const unsigned long long before = n->launches;
-        rc = az_step_eager(n, f, s);
+        // AZ_GRAPH_STEPS > 1 captures several steps per graph (steps beyond the last simulation find every tree finished and
+        // an empty evaluation batch).  Measured on Connect4 4096 x 800: 39.5 / 39.4 / 39.4 / 39.2 M sims/s at 1 / 3 / 9 / 27
+        // steps per graph -- the gap between graph launches is not what the step waits for; the default stays 1.
+        g.steps = 1;
+        if (const char* e = getenv("AZ_GRAPH_STEPS")) g.steps = std::max(1, std::min(64, atoi(e)));
+        for (int i = 0; i < g.steps && !rc; ++i) rc = az_step_eager(n, f, s);
         g.kernels = n->launches - before;
         cudaError_t ce = cudaStreamEndCapture(s, &graph);
         if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
@@ -1230,11 +1236,12 @@ extern "C" int az_forest_search_net(az_forest* f, az_net* n, int iters, void* st
     }
     int done = 0;
     for (;;) {
-        const int burst = steps <= 1 ? (d->vl == 1 ? iters + 1 - steps : std::max(8, iters / d->vl)) : 4;
+        const int want = steps <= 1 ? (d->vl == 1 ? iters + 1 - steps : std::max(8, iters / d->vl)) : 4;
+        const int burst = (want + g.steps - 1) / g.steps;
         for (int i = 0; i < burst; ++i) {
             AZ_CUDA_OK(cudaGraphLaunch(g.exec, s));
             n->launches += g.kernels;
-            ++steps;
+            steps += g.steps;
         }
         if ((rc = az_forest_counts(f, nullptr, &done, s))) return rc;
         if (done >= d->n_trees) break;
