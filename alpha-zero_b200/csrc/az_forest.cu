@@ -55,21 +55,63 @@ struct AzWView {
     __device__ __forceinline__ double& operator[](size_t i) const { return p[i].W; }
 };
 
-__device__ __forceinline__ void az_backup_node(AzHotView hot, AzWView wsum, uint32_t nd, double v, bool release_vl) {
-    AzHot h = hot[nd];
-    const double W = __dadd_rn(wsum[nd], v);
-    h.N += 1;
-    h.Q = az_q32(W, h.N);
-    if (release_vl) h.V -= 1;
-    hot[nd] = h;
-    wsum[nd] = W;
-}
-
 // f64 variant: root children when Dirichlet noise made their priors np.float64.
 __device__ __forceinline__ double az_puct64(double W, double P, int n, double s) {
     const double u = __ddiv_rn(__dmul_rn(P, s), (double)(n + 1));
     if (n == 0) return u;
     return __dadd_rn(__ddiv_rn(W, (double)n), u);
+}
+
+// Tree records are re-read every step, but between two advance launches the evaluator streams ~40 MB of activations and
+// weights through the L2: without a hint most child scans came from DRAM (ncu: 5.7 MB DRAM read per launch against 2.2 MB of
+// algorithmic bytes) and a select level cost ~1.9 k cycles.  Node loads carry an L2 evict_last policy so the streamed data
+// is evicted before them.  AZ_NO_L2_KEEP (build) switches the hint off.
+__device__ __forceinline__ uint64_t az_l2_keep_policy() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ void az_load_node(const AzNode* nd, uint64_t pol, AzHot& h, ulonglong2& mw) {
+#ifdef AZ_NO_L2_KEEP
+    h = nd->hot;
+    mw = *reinterpret_cast<const ulonglong2*>(&nd->meta);
+#else
+    uint32_t a0, a1, a2, a3;
+    asm volatile("ld.global.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;" : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3) : "l"(nd), "l"(pol) : "memory");
+    asm volatile("ld.global.L2::cache_hint.v2.u64 {%0, %1}, [%2], %3;" : "=l"(mw.x), "=l"(mw.y) : "l"(reinterpret_cast<const char*>(nd) + 16), "l"(pol) : "memory");
+    h.N = (int)a0;
+    h.Q = __uint_as_float(a1);
+    h.P = __uint_as_float(a2);
+    h.V = a3;
+#endif
+}
+
+__device__ __forceinline__ void az_store16_keep(void* p, const uint4& v, uint64_t pol) {
+#ifdef AZ_NO_L2_KEEP
+    *reinterpret_cast<uint4*>(p) = v;
+#else
+    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol) : "memory");
+#endif
+}
+__device__ __forceinline__ void az_store8_keep(void* p, unsigned long long v, uint64_t pol) {
+#ifdef AZ_NO_L2_KEEP
+    *reinterpret_cast<unsigned long long*>(p) = v;
+#else
+    asm volatile("st.global.L2::cache_hint.u64 [%0], %1, %2;" ::"l"(p), "l"(v), "l"(pol) : "memory");
+#endif
+}
+
+// node.py:69-72 for one path node: visit += 1, value += v (f64, visitation order), cached Q refreshed.
+__device__ __forceinline__ void az_backup_node(AzNode* nodes, uint32_t nd, double v, bool release_vl, uint64_t pol) {
+    AzHot h;
+    ulonglong2 mw;
+    az_load_node(&nodes[nd], pol, h, mw);
+    const double W = __dadd_rn(__longlong_as_double((long long)mw.y), v);
+    h.N += 1;
+    h.Q = az_q32(W, h.N);
+    if (release_vl) h.V -= 1;
+    az_store16_keep(&nodes[nd].hot, make_uint4((uint32_t)h.N, __float_as_uint(h.Q), __float_as_uint(h.P), h.V), pol);
+    az_store8_keep(&nodes[nd].W, (unsigned long long)__double_as_longlong(W), pol);
 }
 
 // Vanilla mode (model=None), utils.py:36,43 in Python floats: sqrt(2 ln Np / (n+1)) (+ W/n once visited); an
@@ -172,6 +214,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     uint8_t* s_lm = sm + 4 * f.max_depth;
 
     AzNode* const nodes = f.nodes + (size_t)tree * f.cap;
+    const uint64_t l2keep = az_l2_keep_policy();
     const AzHotView hot{nodes};
     const AzMetaView meta{nodes};
     const AzMeta64View meta64{nodes};
@@ -272,8 +315,8 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
                 nn.meta.status = AZ_ST_LEAF;
                 nn.W = 0.0;
                 uint4* dst = reinterpret_cast<uint4*>(&nodes[base + c]);   // one sector, two 16-byte stores
-                dst[0] = reinterpret_cast<const uint4*>(&nn)[0];
-                dst[1] = reinterpret_cast<const uint4*>(&nn)[1];
+                az_store16_keep(dst, reinterpret_cast<const uint4*>(&nn)[0], l2keep);
+                az_store16_keep(dst + 1, reinterpret_cast<const uint4*>(&nn)[1], l2keep);
             }
             {
                 AzMeta m;
@@ -288,7 +331,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             const double result = -(double)val;                   // mcts.py:56
             for (int i = lane; i < len; i += G) {                 // node.py:69-72
                 const uint32_t nd = pre ? (i < 32 ? q0 : q1) : gpath[i];
-                az_backup_node(hot, wsum, nd, ((len - 1 - i) & 1) ? -result : result, use_vl);
+                az_backup_node(nodes, nd, ((len - 1 - i) & 1) ? -result : result, use_vl, l2keep);
             }
             root_nv += use_vl ? 0 : 1;                            // the root: N + 1, V - 1 under virtual loss
             __syncwarp(gmask);
@@ -353,8 +396,9 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
                 const double s = f.ucb1 ? __dmul_rn(2.0, f.log_tab[pn]) : __dsqrt_rn((double)pn);
                 double best = -1.0 / 0.0;
                 for (int c = lane; c < nc; c += G) {
-                    const AzHot h = hot[cb + c];
-                    const ulonglong2 mw = *reinterpret_cast<const ulonglong2*>(&nodes[cb + c].meta);   // meta | W: same sector
+                    AzHot h;
+                    ulonglong2 mw;                                   // meta | W: same sector
+                    az_load_node(&nodes[cb + c], l2keep, h, mw);
                     const unsigned long long mm = mw.x;
                     const int n = h.N + (int)h.V;
                     const double W = __longlong_as_double((long long)mw.y) - (double)h.V;
@@ -366,8 +410,9 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
                 const float s = __fsqrt_rn((float)pn);
                 float best = -1.0f / 0.0f;
                 for (int c = lane; c < nc; c += G) {
-                    const AzHot h = hot[cb + c];
-                    const ulonglong2 mw = *reinterpret_cast<const ulonglong2*>(&nodes[cb + c].meta);   // meta | W: same sector
+                    AzHot h;
+                    ulonglong2 mw;                                   // meta | W: same sector
+                    az_load_node(&nodes[cb + c], l2keep, h, mw);
                     const unsigned long long mm = mw.x;
                     const double Wc = __longlong_as_double((long long)mw.y);
                     int n = h.N;
@@ -419,7 +464,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
         }
         if (status == AZ_ST_WIN || status == AZ_ST_DRAW) {
             const double v = status == AZ_ST_WIN ? 1.0 : 0.0;
-            for (int i = lane; i < len; i += G) az_backup_node(hot, wsum, s_path[i], ((len - 1 - i) & 1) ? -v : v, false);
+            for (int i = lane; i < len; i += G) az_backup_node(nodes, s_path[i], ((len - 1 - i) & 1) ? -v : v, false, l2keep);
             __syncwarp(gmask);
             root_nv += 1;
             ++st_term;

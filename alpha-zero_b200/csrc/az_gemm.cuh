@@ -53,6 +53,7 @@ struct AzGemmArgs {
     // AZ_EPI_HEAD: softmax over columns [0, head_A) -> priors, tanh(column head_A) -> values
     int head_A;
     float *priors, *values, *logits;
+    int l2_hints;               // A loads evict_first, W loads evict_last (the cls-row chain inside the search step)
     int dbg;                    // experiments (tools/gemm_bench.py): bit 0 no MMA, bit 1 no W loads, bit 2 no A loads (results are garbage)
 };
 
@@ -234,6 +235,7 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         if (lane == 0) {                                      // ---- TMA producer
             int stage = 0;
             uint32_t phase = 0;
+            const uint64_t pol_a = azptx::l2_policy_evict_first(), pol_w = azptx::l2_policy_evict_last();
             for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
                 const int m_blk = tile / n_tiles, n_blk = tile - m_blk * n_tiles;
                 for (int kb = 0; kb < kblocks; ++kb) {
@@ -247,8 +249,13 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                         continue;
                     }
                     azptx::mbar_arrive_expect_tx(&full[stage], Cfg::A_BYTES + Cfg::B_BYTES);
-                    azptx::tma_load_2d(s_a + stage * Cfg::A_BYTES, &tm_a, &full[stage], kb * Cfg::BK, m_blk * Cfg::BM);
-                    azptx::tma_load_2d(s_b + stage * Cfg::B_BYTES, &tm_b, &full[stage], kb * Cfg::BK, n_blk * BN);
+                    if (args.l2_hints) {                          // activations stream through once per step, weights come back every step
+                        azptx::tma_load_2d_hint(s_a + stage * Cfg::A_BYTES, &tm_a, &full[stage], kb * Cfg::BK, m_blk * Cfg::BM, pol_a);
+                        azptx::tma_load_2d_hint(s_b + stage * Cfg::B_BYTES, &tm_b, &full[stage], kb * Cfg::BK, n_blk * BN, pol_w);
+                    } else {
+                        azptx::tma_load_2d(s_a + stage * Cfg::A_BYTES, &tm_a, &full[stage], kb * Cfg::BK, m_blk * Cfg::BM);
+                        azptx::tma_load_2d(s_b + stage * Cfg::B_BYTES, &tm_b, &full[stage], kb * Cfg::BK, n_blk * BN);
+                    }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }

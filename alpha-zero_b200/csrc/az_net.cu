@@ -896,8 +896,10 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         AzProfScope ps(n, kind, s);
         return az_launch_gemm(ta, tb, ga, epi, mr, s);
     };
-    auto gemm_bn = [&](int kind, const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& ga, int epi, int mr, int bn) {
+    static const bool l2_hints = !getenv("AZ_NO_L2_HINTS");
+    auto gemm_bn = [&](int kind, const CUtensorMap& ta, const CUtensorMap& tb, AzGemmArgs ga, int epi, int mr, int bn) {
         AzProfScope ps(n, kind, s);
+        ga.l2_hints = l2_hints ? 1 : 0;
         return az_launch_gemm(ta, tb, ga, epi, mr, s, bn);
     };
     if (!g_num_sms) {
