@@ -101,6 +101,34 @@ __device__ __forceinline__ void az_store8_keep(void* p, unsigned long long v, ui
 #endif
 }
 
+// Scalar loads with the same evict_last policy (per-tree state, pending-leaf records, the evaluator's answers).
+#ifdef AZ_NO_L2_KEEP
+template <typename T> __device__ __forceinline__ T az_ldk(const T* p, uint64_t) { return *p; }
+#else
+__device__ __forceinline__ uint8_t az_ldk(const uint8_t* p, uint64_t pol) {
+    uint32_t v;
+    asm volatile("ld.global.L2::cache_hint.u8 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol) : "memory");
+    return (uint8_t)v;
+}
+__device__ __forceinline__ uint16_t az_ldk(const uint16_t* p, uint64_t pol) {
+    uint16_t v;
+    asm volatile("ld.global.L2::cache_hint.u16 %0, [%1], %2;" : "=h"(v) : "l"(p), "l"(pol) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t az_ldk(const uint32_t* p, uint64_t pol) {
+    uint32_t v;
+    asm volatile("ld.global.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol) : "memory");
+    return v;
+}
+__device__ __forceinline__ int az_ldk(const int* p, uint64_t pol) { return (int)az_ldk(reinterpret_cast<const uint32_t*>(p), pol); }
+__device__ __forceinline__ float az_ldk(const float* p, uint64_t pol) { return __uint_as_float(az_ldk(reinterpret_cast<const uint32_t*>(p), pol)); }
+__device__ __forceinline__ uint64_t az_ldk(const uint64_t* p, uint64_t pol) {
+    uint64_t v;
+    asm volatile("ld.global.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol) : "memory");
+    return v;
+}
+#endif
+
 // node.py:69-72 for one path node: visit += 1, value += v (f64, visitation order), cached Q refreshed.
 __device__ __forceinline__ void az_backup_node(AzNode* nodes, uint32_t nd, double v, bool release_vl, uint64_t pol) {
     AzHot h;
@@ -182,24 +210,28 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     const long long at_t0 = at_prev;
 #endif
     // independent loads first, decisions after: one memory round trip
-    const uint8_t is_active = f.active[tree], is_done = f.done_flag[tree];
-    int n_nodes = f.n_nodes[tree];
-    int sims = f.sims_done[tree];
-    const int npend = f.n_pending[tree];
-    const int root_player = f.root_player[tree];
-    const int root_mc = f.root_mc[tree];
+    const uint64_t l2keep = az_l2_keep_policy();
+    const uint8_t is_active = az_ldk(f.active + tree, l2keep), is_done = az_ldk(f.done_flag + tree, l2keep);
+    int n_nodes = az_ldk(f.n_nodes + tree, l2keep);
+    int sims = az_ldk(f.sims_done + tree, l2keep);
+    const int npend = az_ldk(f.n_pending + tree, l2keep);
+    const int root_player = az_ldk(f.root_player + tree, l2keep);
+    const int root_mc = az_ldk(f.root_mc + tree, l2keep);
     AzBoard<NW> rootb;
 #pragma unroll
     for (int w = 0; w < NW; ++w) {
-        rootb.w[0][w] = f.root_words[(size_t)tree * 2 * NW + w];
-        rootb.w[1][w] = f.root_words[(size_t)tree * 2 * NW + NW + w];
+        rootb.w[0][w] = az_ldk(f.root_words + (size_t)tree * 2 * NW + w, l2keep);
+        rootb.w[1][w] = az_ldk(f.root_words + (size_t)tree * 2 * NW + NW + w, l2keep);
     }
     // the root's record is tracked in registers for the whole launch: every backup and every virtual
     // loss passes through it, and a reload after the backup stores would cost a round trip per descent
-    AzMeta root_m = f.nodes[(size_t)tree * f.cap].meta;
+    AzMeta root_m;
     int root_nv;
     {
-        const AzHot hr = f.nodes[(size_t)tree * f.cap].hot;
+        AzHot hr;
+        ulonglong2 mwr;
+        az_load_node(f.nodes + (size_t)tree * f.cap, l2keep, hr, mwr);
+        root_m = *reinterpret_cast<const AzMeta*>(&mwr.x);
         root_nv = hr.N + (int)hr.V;
     }
     if (!is_active || is_done) return;
@@ -214,7 +246,6 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     uint8_t* s_lm = sm + 4 * f.max_depth;
 
     AzNode* const nodes = f.nodes + (size_t)tree * f.cap;
-    const uint64_t l2keep = az_l2_keep_policy();
     const AzHotView hot{nodes};
     const AzMetaView meta{nodes};
     const AzMeta64View meta64{nodes};
@@ -240,13 +271,13 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             const size_t pj = (size_t)tree * f.vl + j0 + lane;
 #pragma unroll
             for (int w = 0; w < NW; ++w) {
-                pb_.w[0][w] = f.pend_words[pj * 2 * NW + w];
-                pb_.w[1][w] = f.pend_words[pj * 2 * NW + NW + w];
+                pb_.w[0][w] = az_ldk(f.pend_words + pj * 2 * NW + w, l2keep);
+                pb_.w[1][w] = az_ldk(f.pend_words + pj * 2 * NW + NW + w, l2keep);
             }
-            my_slot = f.leaf_slot[pj];
-            my_len = f.path_len[pj];
-            my_action = f.pend_action[pj];
-            my_leaf = f.pend_leaf[pj];
+            my_slot = az_ldk(f.leaf_slot + pj, l2keep);
+            my_len = az_ldk(f.path_len + pj, l2keep);
+            my_action = az_ldk(f.pend_action + pj, l2keep);
+            my_leaf = az_ldk(f.pend_leaf + pj, l2keep);
             my_val = f.values[my_slot];
         }
         float pa = 0.f, pb = 0.f;
@@ -257,8 +288,8 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             const uint32_t* gp = f.path + ((size_t)tree * f.vl + j0 + j) * f.max_depth;
             xa = lane < A ? prx[lane] : 0.f;
             xb = lane + 32 < A ? prx[lane + 32] : 0.f;
-            y0 = lane < f.max_depth ? gp[lane] : 0u;
-            y1 = lane + 32 < f.max_depth ? gp[lane + 32] : 0u;
+            y0 = lane < f.max_depth ? az_ldk(gp + lane, l2keep) : 0u;
+            y1 = lane + 32 < f.max_depth ? az_ldk(gp + lane + 32, l2keep) : 0u;
         };
         if (pre) fetch(0, pa, pb, q0, q1);
         if (lane < nj) {                                      // legal moves of leaf j0 + j (Gomoku: sequential set emulation)
