@@ -56,7 +56,10 @@ class MCTS:
             if ent is not None and ent[3]() is not model:   # id() of a collected Net reused by another model
                 ent[0].close()
                 ent = None
-            if ent is None or ent[2] < max_batch:
+            if ent is not None and ent[2] < max_batch:      # a larger forest than the engine was sized for
+                ent[0].close()
+                ent = None
+            if ent is None:
                 for k in [k for k, e in MCTS._engines.items() if e[3]() is None]:   # engines of collected models
                     MCTS._engines.pop(k)[0].close()
                 ent = [B200Net(model, max_batch=max_batch), stamp, max_batch, weakref.ref(model)]

@@ -50,10 +50,6 @@ struct AzMeta64View {
     AzNode* p;
     __device__ __forceinline__ unsigned long long operator[](size_t i) const { return *reinterpret_cast<const unsigned long long*>(&p[i].meta); }
 };
-struct AzWView {
-    AzNode* p;
-    __device__ __forceinline__ double& operator[](size_t i) const { return p[i].W; }
-};
 
 // f64 variant: root children when Dirichlet noise made their priors np.float64.
 __device__ __forceinline__ double az_puct64(double W, double P, int n, double s) {
@@ -249,7 +245,6 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     const AzHotView hot{nodes};
     const AzMetaView meta{nodes};
     const AzMeta64View meta64{nodes};
-    const AzWView wsum{nodes};
     const bool use_vl = f.vl > 1;
     const int A = g.action_dim;
     const int LP = f.lp;
@@ -278,7 +273,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             my_len = az_ldk(f.path_len + pj, l2keep);
             my_action = az_ldk(f.pend_action + pj, l2keep);
             my_leaf = az_ldk(f.pend_leaf + pj, l2keep);
-            my_val = f.values[my_slot];
+            my_val = az_ldk(f.values + my_slot, l2keep);
         }
         float pa = 0.f, pb = 0.f;
         uint32_t q0 = 0, q1 = 0;
@@ -286,8 +281,8 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             const int slotx = __shfl_sync(gmask, my_slot, j, G);
             const float* prx = f.priors + (size_t)slotx * A;
             const uint32_t* gp = f.path + ((size_t)tree * f.vl + j0 + j) * f.max_depth;
-            xa = lane < A ? prx[lane] : 0.f;
-            xb = lane + 32 < A ? prx[lane + 32] : 0.f;
+            xa = lane < A ? az_ldk(prx + lane, l2keep) : 0.f;
+            xb = lane + 32 < A ? az_ldk(prx + lane + 32, l2keep) : 0.f;
             y0 = lane < f.max_depth ? az_ldk(gp + lane, l2keep) : 0u;
             y1 = lane + 32 < f.max_depth ? az_ldk(gp + lane + 32, l2keep) : 0u;
         };

@@ -1,5 +1,5 @@
 """Phase clocks of az_advance_kernel over one whole search (library built with -DAZ_ADV_TRACE as
-tools/libaz_trace.so).  usage: python tools/adv_trace.py [connect4|gomoku] [trees] [iters] [vl]"""
+tools/libaz_trace.so: nvcc ... -fmad=false -DAZ_ADV_TRACE -c az_forest.cu, linked with az_net.o).  usage: python tools/adv_trace.py [connect4|gomoku] [trees] [iters] [vl]"""
 import ctypes as C, sys, os
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
