@@ -24,6 +24,13 @@
 
 #define AZ_FRONT2_STAGES 4
 #define AZ_FRONT2_LAG 2
+// Experiment, off: warp 9 (U epilogue group) issues the U MMAs and warp 15 only the statistic MMAs.  Measured: no gain
+// (Connect4 front 23.0 -> 25.0 us, Gomoku 0.2275 -> 0.2257 ms).  The issuing thread is blocked for the ~70-95 cycles each
+// small-N MMA occupies the tensor pipe, so two issuers share the same 1.13 k pipe-cycles per tile, and warp 9's issue now
+// delays the drain its three sibling warps wait for.
+#ifndef AZ_FRONT2_SPLIT_ISSUE
+#define AZ_FRONT2_SPLIT_ISSUE 0
+#endif
 #define AZ_FRONT2_BUILDERS 96      // warps 12-14: one rewritten token row per thread (two when a tile has more than 96)
 
 static inline size_t az_front2_smem(const AzFrontArgs& a) {
@@ -217,7 +224,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
         azptx::mbar_wait(w_full, 0);
         wait_upstream();
         const int n_my = tiles > (int)blockIdx.x ? (tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-        for (int j = 0; j < n_my + LAG; ++j) {
+        for (int j = 0; j < n_my + (AZ_FRONT2_SPLIT_ISSUE ? 0 : LAG); ++j) {
             const int it = j;
             AZ_TR1(0, 0);
             if (j < n_my) {                                           // statistics of tile j
@@ -240,7 +247,7 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
                 __syncwarp();
             }
             const int i = j - LAG;
-            if (i >= 0) {                                             // U of tile i: its softmax weights are in Wblk
+            if (!AZ_FRONT2_SPLIT_ISSUE && i >= 0) {                   // U of tile i: its softmax weights are in Wblk
                 const int st = i % NA, g = i & 1;
                 AZ_TR1(0, 3);
                 azptx::mbar_wait(&sw_full[g], (i >> 1) & 1);
@@ -424,7 +431,17 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
         // statistics MMA serialised the whole pipeline: 3.4 k cycles per tile instead of 1.5 k).
         const bool extra = a.nb * (T - 1) > AZ_FRONT2_BUILDERS;
         const bool assist = warp == 8 && extra;
+#if AZ_FRONT2_SPLIT_ISSUE
+        // Warp 9 issues the U MMAs of tile j - 2 (its softmax finished about one tile ago: no wait), then all four warps
+        // drain tile j - 3, whose MMAs were issued one iteration earlier.  Two U accumulators: U(i) needs drain(i - 2),
+        // which ran in iteration i + 1 < i + 2.
+        const int ulag = 3;
+        const bool uissue = warp == 9;
+        const uint32_t idesc_u = azptx::umma_idesc_bf16(128, (uint32_t)NP) | (1u << 15);     // A operand MN-major
+        const int usteps = NTP >> 4;                                  // 16 tokens per U MMA
+#else
         const int ulag = extra ? NA : 0;
+#endif
         const int nch = (a.kc + 7) >> 3;
         AzRowBuilder rb;
         rb.init(a, AZ_FRONT2_BUILDERS + lane, TS);
@@ -443,8 +460,31 @@ __global__ void __launch_bounds__(AZ_FRONT_THREADS, 1) az_front2_kernel(const __
                 rb.w_cur = rb.w_nxt;
                 rb.s_cur = rb.s_nxt;
             }
+#if AZ_FRONT2_SPLIT_ISSUE
+            {
+                const int i = j - 2;
+                if (uissue && i >= 0 && i < n_my) {                   // U of tile i: its softmax weights are in Wblk
+                    const int st = i % NA, g = i & 1;
+                    azptx::mbar_wait(&sw_full[g], (i >> 1) & 1);
+                    azptx::mbar_wait(&u_empty[g], ((i >> 1) & 1) ^ 1);
+                    azptx::tc_fence_after();
+                    if (azptx::elect_one()) {
+                        const uint64_t dat = azptx::umma_desc_mn128(azptx::smem_u32(s_a + (size_t)st * 2 * tile_bytes), tile_bytes);
+                        const uint32_t wb = azptx::smem_u32(s_wb + (size_t)g * 2 * NP * 128);
+                        const uint64_t dw0 = azptx::umma_desc_k128(wb), dw1 = azptx::umma_desc_k128(wb + NP * 128);
+                        const uint32_t dcol = tmem_base + 256 + g * NP;
+                        for (int ks = 0; ks < usteps; ++ks)           // +16 tokens: 2048 bytes of A, 32 bytes of a Wblk row
+                            azptx::umma_bf16(dcol, dat + 128 * ks, (ks < 4 ? dw0 : dw1) + 2 * (ks & 3), idesc_u, ks != 0);
+                        azptx::umma_commit(&u_full[g]);
+                        azptx::umma_commit(&a_empty[st]);
+                        azptx::umma_commit(&sw_empty[g]);
+                    }
+                    __syncwarp();
+                }
+            }
+#endif
             const int it = j - ulag;
-            if (it < 0) continue;
+            if (it < 0 || it >= n_my) continue;
             const int tile = blockIdx.x + it * gridDim.x;
             const int g = it & 1, u = it >> 1;
             AZ_TR(3, 0);
