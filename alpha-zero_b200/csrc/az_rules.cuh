@@ -12,8 +12,10 @@
 
 #ifdef __CUDA_ARCH__
 #define AZ_CTZ64(x) (__ffsll((long long)(x)) - 1)
+#define AZ_POPC64(x) __popcll(x)
 #else
 #define AZ_CTZ64(x) __builtin_ctzll(x)
+#define AZ_POPC64(x) __builtin_popcountll(x)
 #endif
 
 template <int NW>
@@ -138,6 +140,48 @@ __host__ __device__ inline int az_legal_moves(const AzGame& g, const AzBoard<NW>
     // of a cell reaches the table: `blocked` = stones | cells already inserted is a bit test.
     // Pass 1 lists the first occurrences in scan order (into `out`, reused below), pass 2 replays
     // them through the table.
+    // Shortcut (boards of <= 64 cells).  The table size a CPython set ends with depends only on the number of keys
+    // (8 slots up to 4 keys, 32 up to 18, 128 up to 76: growth is triggered by the fill count alone, nothing is ever
+    // deleted).  At the last resize the keys are reinserted into an EMPTY table and every later key is added to that
+    // table, so whenever the keys' home slots `hash & mask` in the final table are pairwise distinct, no probe ever
+    // collides there and every key sits in its home slot whatever the insertion history was: iteration order = keys
+    // sorted by home slot.  The candidate SET is the 8-neighbour dilation of the stones, a handful of shifts; a
+    // collision in the final table falls through to the full emulation below.
+#ifndef AZ_NO_LEGAL_SHORTCUT
+    if (NW == 1) {
+        const uint64_t occ = b.w[0][0] | b.w[1][0];
+        uint64_t col0 = 0ull;
+        for (int r = 0; r < g.rows; ++r) col0 |= 1ull << (r * g.cols);
+        const uint64_t colr = col0 << (g.cols - 1);
+        const uint64_t full = g.state_dim >= 64 ? ~0ull : (1ull << g.state_dim) - 1ull;
+        const uint64_t h = occ | ((occ & ~colr) << 1) | ((occ & ~col0) >> 1);
+        const uint64_t cand = (h | (h << g.cols) | (h >> g.cols)) & ~occ & full;
+        if (cand == 0ull) {                                   // no candidate (empty board): centre (gomoku.py:104-105)
+            out[0] = (uint8_t)((g.rows / 2) * g.cols + g.cols / 2);
+            return 1;
+        }
+        const int nk = AZ_POPC64(cand);
+        const uint32_t fm = nk <= 4 ? 7u : (nk <= 18 ? 31u : 127u);
+        uint64_t s0 = 0ull, s1 = 0ull;                        // occupied home slots 0..63 / 64..127
+        bool clash = false;
+        for (uint64_t w = cand; w; w &= w - 1) {
+            const uint32_t slot = (uint32_t)cell_hash[AZ_CTZ64(w)] & fm;
+            const uint64_t bit = 1ull << (slot & 63);
+            if (slot < 64) { clash |= (s0 & bit) != 0ull; s0 |= bit; }
+            else { clash |= (s1 & bit) != 0ull; s1 |= bit; }
+        }
+        if (!clash) {
+            for (uint64_t w = cand; w; w &= w - 1) {
+                const int x = AZ_CTZ64(w);
+                const uint32_t slot = (uint32_t)cell_hash[x] & fm;
+                const int pos = slot < 64 ? AZ_POPC64(s0 & ((1ull << slot) - 1ull))
+                                          : AZ_POPC64(s0) + AZ_POPC64(s1 & ((1ull << (slot - 64)) - 1ull));
+                out[pos] = (uint8_t)x;
+            }
+            return nk;
+        }
+    }
+#endif
     uint64_t blocked[NW];
 #pragma unroll
     for (int wi = 0; wi < NW; ++wi) blocked[wi] = b.w[0][wi] | b.w[1][wi];
