@@ -47,6 +47,37 @@ def test_gomoku_set_order_matches_real_set():
             assert orc.valid_moves(g, b) == orc.valid_moves_pyset(g, b)
 
 
+def test_gomoku_set_order_is_home_slot_order_when_homes_are_distinct():
+    """What the device shortcut in csrc/az_rules.cuh relies on, checked on REAL CPython sets built with the reference's
+    insertion sequence (gomoku.py:95-104): the final table has 8 / 32 / 128 slots for <= 4 / 5-18 / 19-76 keys, and whenever
+    the keys' home slots hash & mask in that table are pairwise distinct, list(set) is the keys sorted by home slot."""
+    rng = np.random.default_rng(11)
+    hit = miss = 0
+    for g in (orc.GOMOKU, orc.gomoku_spec(8), orc.gomoku_spec(6)):
+        cells = g.rows * g.cols
+        for _ in range(1500):
+            b = orc.new_board(g)
+            k = int(rng.integers(1, cells))
+            for i, cell in enumerate(rng.permutation(cells)[:k]):
+                b[i % 2, cell // g.cols, cell % g.cols] = 1
+            real = set()
+            for cell in orc.gomoku_insertion_sequence(g, b):
+                real.add(divmod(cell, g.cols))
+            if not real:
+                continue
+            n = len(real)
+            mask = 7 if n <= 4 else (31 if n <= 18 else 127)
+            homes = {a: hash(a) & mask for a in real}
+            if len(set(homes.values())) < n:
+                miss += 1
+                continue
+            hit += 1
+            assert list(real) == sorted(real, key=lambda a: homes[a])
+    assert hit > 1000 and miss > 50                           # both branches of the device code occur
+    h7 = {hash((r, c)) & 127 for r in range(7) for c in range(7)}
+    assert len(h7) == 49                                      # 7x7: every position with >= 19 candidates takes the shortcut
+
+
 def test_puct_bits():
     for case in load_json("puct.json"):
         parent = orc.Node(None, None, 0, 0)
