@@ -53,6 +53,8 @@ struct AzGemmArgs {
     // AZ_EPI_HEAD: softmax over columns [0, head_A) -> priors, tanh(column head_A) -> values
     int head_A;
     float *priors, *values, *logits;
+    int w_early;                // the first W tiles are requested BEFORE griddepcontrol.wait (weights do not depend on the predecessor;
+                                // only where the row counter was written at least two kernels upstream)
     int l2_hints;               // A loads evict_first, W loads evict_last (the cls-row chain inside the search step)
     int dbg;                    // experiments (tools/gemm_bench.py): bit 0 no MMA, bit 1 no W loads, bit 2 no A loads (results are garbage)
 };
@@ -225,6 +227,19 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     const uint32_t tmem_base = *tmem_slot;
     // Programmatic dependent launch: everything above overlapped the predecessor's tail; its outputs
     // (the A rows, the row statistics and the device-side row count) are read only from here on.
+    int pre = 0;                                              // stages whose W tile is already in flight (producer thread only)
+    if (args.w_early && !args.dbg && threadIdx.x == 0) {
+        const int total0 = ((az_gemm_rows(args) + Cfg::BM - 1) / Cfg::BM) * n_tiles;
+        if ((int)blockIdx.x < total0) {
+            const uint64_t pol_w = azptx::l2_policy_evict_last();
+            const int n_blk0 = (int)blockIdx.x % n_tiles;
+            pre = kblocks < STAGES ? kblocks : STAGES;
+            for (int kb = 0; kb < pre; ++kb) {
+                azptx::mbar_arrive_expect_tx(&full[kb], Cfg::A_BYTES + Cfg::B_BYTES);
+                azptx::tma_load_2d_hint(s_b + kb * Cfg::B_BYTES, &tm_b, &full[kb], kb * Cfg::BK, n_blk0 * BN, pol_w);
+            }
+        }
+    }
     azptx::griddep_wait();
     azptx::griddep_launch();
     const int M = az_gemm_rows(args);
@@ -245,6 +260,12 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                         if (bytes) azptx::mbar_arrive_expect_tx(&full[stage], bytes); else azptx::mbar_arrive(&full[stage]);
                         if (!(args.dbg & 4)) azptx::tma_load_2d(s_a + stage * Cfg::A_BYTES, &tm_a, &full[stage], kb * Cfg::BK, m_blk * Cfg::BM);
                         if (!(args.dbg & 2)) azptx::tma_load_2d(s_b + stage * Cfg::B_BYTES, &tm_b, &full[stage], kb * Cfg::BK, n_blk * BN);
+                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
+                    if (pre > 0) {                                // W of this stage was requested before the dependency wait
+                        --pre;
+                        azptx::tma_load_2d_hint(s_a + stage * Cfg::A_BYTES, &tm_a, &full[stage], kb * Cfg::BK, m_blk * Cfg::BM, pol_a);
                         if (++stage == STAGES) { stage = 0; phase ^= 1; }
                         continue;
                     }

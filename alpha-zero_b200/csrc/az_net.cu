@@ -897,9 +897,11 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         return az_launch_gemm(ta, tb, ga, epi, mr, s);
     };
     static const bool l2_hints = !getenv("AZ_NO_L2_HINTS");
+    static const bool w_early = getenv("AZ_W_EARLY") != nullptr;   // measured: no gain (41.8 vs 41.8 M sims/s on Connect4), off by default
     auto gemm_bn = [&](int kind, const CUtensorMap& ta, const CUtensorMap& tb, AzGemmArgs ga, int epi, int mr, int bn) {
         AzProfScope ps(n, kind, s);
         ga.l2_hints = l2_hints ? 1 : 0;
+        ga.w_early = w_early ? 1 : 0;                          // the leaf counter was written by the advance kernel, >= 2 kernels upstream
         return az_launch_gemm(ta, tb, ga, epi, mr, s, bn);
     };
     if (!g_num_sms) {
