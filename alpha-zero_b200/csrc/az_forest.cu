@@ -192,6 +192,15 @@ __device__ unsigned int g_adv_hist[66];      // warp lifetimes of the launches s
 #define AZ_AT_COUNT(k, n) do {} while (0)
 #endif
 
+// The legal-move listing as a real call: inlined, its loops and 64-bit masks compete for the 72 registers the kernel
+// is held to (7 CTAs per SM) and the allocator spills in the select loop instead.
+#ifndef AZ_LEGAL_INLINE
+template <int NW>
+__device__ __noinline__ int az_legal_moves_call(AzGame g, AzBoard<NW> b, const uint64_t* cell_hash, uint8_t* lm, int moves_pad) {
+    return az_legal_moves<NW>(g, b, cell_hash, lm + moves_pad, lm + moves_pad + g.set_slots, lm);
+}
+#endif
+
 template <int NW, int G>
 __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int smem_per_group) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -289,7 +298,11 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
         if (pre) fetch(0, pa, pb, q0, q1);
         if (lane < nj) {                                      // legal moves of leaf j0 + j (Gomoku: sequential set emulation)
             uint8_t* lm = s_lm + (size_t)lane * lm_bytes;
+#ifndef AZ_LEGAL_INLINE
+            my_nc = az_legal_moves_call<NW>(g, pb_, f.cell_hash, lm, moves_pad);
+#else
             my_nc = az_legal_moves<NW>(g, pb_, f.cell_hash, lm + moves_pad, lm + moves_pad + g.set_slots, lm);
+#endif
         }
         __syncwarp(gmask);                                    // move lists visible to the group
         AZ_AT(1);                                             // pending scalars + legal moves
