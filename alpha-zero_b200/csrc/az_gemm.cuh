@@ -119,12 +119,23 @@ __device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uin
                                                      float rstd, float nmr) {
     constexpr int CPW = BN / 64;                               // 32-column chunks per warp
     float st1 = 0.f, st2 = 0.f;
+#ifdef AZ_EPI_PREFETCH                                          // the next chunk's tcgen05.ld runs under this chunk's arithmetic
+    uint32_t rn[32];
+    azptx::tmem_ld32(tacc + half * CPW * 32, rn);
+#endif
 #pragma unroll 1
     for (int cc = 0; cc < CPW; ++cc) {
         const int c = half * CPW + cc;
         uint32_t r[32];
+#ifdef AZ_EPI_PREFETCH
+        azptx::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) r[i] = rn[i];
+        if (cc + 1 < CPW) azptx::tmem_ld32(tacc + (c + 1) * 32, rn);
+#else
         azptx::tmem_ld32(tacc + c * 32, r);
         azptx::tmem_ld_wait();
+#endif
         const int col0 = n_blk * BN + c * 32;
         if (live && args.out_f32 && col0 >= args.f32_col0) {      // fp32 side output (attention scores)
             const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
@@ -157,7 +168,11 @@ __device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uin
                 float v1 = fmaf(rstd, __uint_as_float(r[4 * i + 1]), bb.y);
                 float v2 = fmaf(rstd, __uint_as_float(r[4 * i + 2]), bb.z);
                 float v3 = fmaf(rstd, __uint_as_float(r[4 * i + 3]), bb.w);
+#ifdef AZ_EPI_EXPERIMENT                                          // tools/gemm_bench.py: dbg bit 4 = no GELU, bit 3 = no output stores
+                if (EPI == AZ_EPI_GELU && !(args.dbg & 16)) {
+#else
                 if (EPI == AZ_EPI_GELU) {
+#endif
                     v0 = az_gelu(v0); v1 = az_gelu(v1); v2 = az_gelu(v2); v3 = az_gelu(v3);
                 }
                 if (EPI == AZ_EPI_RESID) {
@@ -180,6 +195,9 @@ __device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uin
                 ow[1] = *reinterpret_cast<uint32_t*>(&o23);
             }
             uint4* op = reinterpret_cast<uint4*>(args.out + (size_t)row * args.ldo + col0);
+#ifdef AZ_EPI_EXPERIMENT
+            if ((args.dbg & 8) && ov[0].x != 0x7fc07fc1u) continue;   // value-dependent, so the arithmetic is not eliminated
+#endif
 #pragma unroll
             for (int i = 0; i < 4; ++i) op[i] = ov[i];
         }

@@ -1,5 +1,7 @@
 """Warm-L2 timing of the cls-row GEMM shapes through az_gemm_bf16 (CUDA events, 200 launches each),
-single-CTA tiles vs CTA-pair tiles (AZ_GEMM_BN = width, +1000 for the pair kernel).  GPU box only."""
+single-CTA tiles vs CTA-pair tiles (AZ_GEMM_BN = width, +1000 for the pair kernel).  GPU box only.
+Epilogue ablation: build az_net.cu with -DAZ_EPI_EXPERIMENT into tools/_build/, point AZ_B200_LIB at it and set
+AZ_GEMM_DBG bit 3 (no output stores) / bit 4 (no GELU); `python tools/gemm_bench.py <shape index> <bn>` runs one case."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
