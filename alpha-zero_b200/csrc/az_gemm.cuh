@@ -119,7 +119,7 @@ __device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uin
                                                      float rstd, float nmr) {
     constexpr int CPW = BN / 64;                               // 32-column chunks per warp
     float st1 = 0.f, st2 = 0.f;
-#ifdef AZ_EPI_PREFETCH                                          // the next chunk's tcgen05.ld runs under this chunk's arithmetic
+#ifndef AZ_NO_EPI_PREFETCH                                          // the next chunk's tcgen05.ld runs under this chunk's arithmetic
     uint32_t rn[32];
     azptx::tmem_ld32(tacc + half * CPW * 32, rn);
 #endif
@@ -127,7 +127,7 @@ __device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uin
     for (int cc = 0; cc < CPW; ++cc) {
         const int c = half * CPW + cc;
         uint32_t r[32];
-#ifdef AZ_EPI_PREFETCH
+#ifndef AZ_NO_EPI_PREFETCH
         azptx::tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) r[i] = rn[i];
