@@ -7,4 +7,6 @@ it as `alpha_zero_b200` (the shim package next to it).
 from . import lib  # noqa: F401
 from .forest import Forest, GameSpec, GAMES, game_spec  # noqa: F401
 
-__all__ = ["lib", "Forest", "GameSpec", "GAMES", "game_spec"]
+from .selfplay import SelfPlayEngine  # noqa: F401
+
+__all__ = ["lib", "Forest", "GameSpec", "GAMES", "game_spec", "SelfPlayEngine"]

@@ -9,8 +9,8 @@ prevAction}, in the reference's child order.  `model` may be
     the whole search is one CUDA-graph replay loop inside libaz_b200.so;
   * any other callable x[B,C,H,W] -> (logits[B,A], values[B,1]): leaves are handed to it as a
     float32 CUDA tensor batch each step (external evaluator);
-  * a falsy value selects the reference's vanilla mode (UCB1 + random rollouts) -- not on the
-    network hot path; not implemented on the GPU.
+  * a falsy value selects the reference's vanilla mode (ai/mcts.py:57-79): UCB1 selection (bit-exact) and
+    uniformly random rollouts on the device (az_forest_search_rollout; statistical parity).
 MCTS.mcts_batch does the same for many independent positions at once (the throughput path).
 """
 import numpy as np
@@ -70,17 +70,31 @@ class MCTS:
             return ent[0]
         return None
 
+    _MAX_FORESTS = 3            # node pools are large (Gomoku 8192 x 800: 10 GB): keep the most recently used few
+
     @staticmethod
     def _forest_for(Game, n_trees, iters, vl):
         spec = _spec_of(Game)
         key = (spec.name, spec.rows, n_trees, vl)
-        f = MCTS._forests.get(key)
+        f = MCTS._forests.pop(key, None)
         if f is None or f.max_iters < iters:
             if f is not None:
                 f.close()
+            while len(MCTS._forests) >= MCTS._MAX_FORESTS:            # least recently used first (dicts keep insertion order)
+                MCTS._forests.pop(next(iter(MCTS._forests))).close()
             f = Forest(spec, n_trees, max(iters, 1), vl=vl)
-            MCTS._forests[key] = f
+        MCTS._forests[key] = f                                        # (re)inserted last = most recently used
         return f
+
+    @staticmethod
+    def release():
+        """Frees every cached forest and inference engine (device memory); they are rebuilt on demand."""
+        for f in MCTS._forests.values():
+            f.close()
+        MCTS._forests.clear()
+        for ent in MCTS._engines.values():
+            ent[0].close()
+        MCTS._engines.clear()
 
     @staticmethod
     def _search_external(forest, model, iters):
@@ -90,9 +104,11 @@ class MCTS:
         m = forest.n_trees * forest.vl
         planes = torch.zeros((m, g.planes, g.rows, g.cols), dtype=torch.float32, device="cuda")
         dev = next((p.device for p in getattr(model, "parameters", lambda: [])()), torch.device("cpu"))
-        forest.begin_move(iters)
         L = forest._L
         from .. import lib as _lib
+        stamp = hash((id(model),) + tuple(p._version for p in getattr(model, "parameters", lambda: [])())) & (2 ** 63 - 1)
+        _lib.check(L.az_forest_set_evaluator(forest.h, stamp | (1 << 62), forest.stream), "set_evaluator")
+        forest.begin_move(iters)
         for _ in range(2 * iters + 8):
             forest.advance()
             n_leaves, n_done = forest.counts()

@@ -172,6 +172,78 @@ __device__ __forceinline__ int az_group_argmax(unsigned gmask, double best, int 
     return (int)__reduce_min_sync(gmask, (hi == mh && lo == ml) ? (unsigned)idx : 0x7fffffffu);
 }
 
+// ---- evaluation cache (az_forest.h: AzCacheDev) ---------------------------------------------------
+__device__ __forceinline__ uint64_t az_cache_hash(uint64_t mine, uint64_t theirs) {
+    uint64_t x = mine * 0x9E3779B97F4A7C15ull ^ (theirs + 0xD1B54A32D192ED03ull) * 0xBF58476D1CE4E5B9ull;
+    x ^= x >> 29;
+    x *= 0x94D049BB133111EBull;
+    return x ^ (x >> 32);
+}
+__device__ __forceinline__ uint32_t az_cache_word(uint32_t kind, uint32_t epoch) { return (kind << 30) | (epoch & 0xffu); }
+
+// Warp-cooperative lookup of one canonical position.  Returns
+//   2  the entry holds the answer already (AZ_CK_READY): usable at once,
+//   1  another leaf of THIS launch claimed the entry and its evaluation is in flight: the answer is in the entry by the
+//      next launch (az_cache_publish_kernel runs before it),
+//   0  miss; *entry = the entry claimed for this leaf (its batch row will be published there) or 0xffffffff when the
+//      window had no free entry (the leaf is evaluated and simply not cached).
+// Every state transition is a CAS on the entry's state word, so a reader that found a stale entry and a writer that wants
+// to recycle it cannot both win; the key is written while the entry is LOCKED and only then made PENDING.
+template <int G>
+__device__ __noinline__ int az_cache_probe(const AzCacheDev c, uint64_t mine, uint64_t theirs, int lane, unsigned gmask, uint32_t* entry) {
+    const uint32_t epoch = __ldcg(c.epoch);
+    const uint32_t base = (uint32_t)az_cache_hash(mine, theirs) & (c.cap - 1u) & ~(uint32_t)(AZ_CACHE_WINDOW - 1);
+    ulonglong2 k = make_ulonglong2(0ull, 0ull);
+    uint32_t st = 0u;
+    const bool in = lane < AZ_CACHE_WINDOW;
+    if (in) {
+        k = __ldcg(c.keys + base + lane);
+        st = __ldcg(c.state + base + lane);
+    }
+    const uint32_t kind = st >> 30, age = (epoch - st) & 0xffu;
+    const bool same = in && k.x == mine && k.y == theirs;
+    const unsigned mb = __ballot_sync(gmask, same && (kind == AZ_CK_READY || (kind == AZ_CK_PENDING && age == 0u))) & gmask;
+    if (mb) {
+        const int l = (__ffs(mb) - 1) % G;
+        const uint32_t e = base + (uint32_t)l;
+        const uint32_t sl = __shfl_sync(gmask, st, l, G);
+        *entry = e;
+        if ((sl >> 30) == AZ_CK_PENDING) return 1;
+        const uint32_t al = (epoch - sl) & 0xffu;
+        if (al == 0u) return 2;
+        int ok = 1;                                          // touch: a stale entry must be re-validated atomically
+        if (lane == 0) ok = atomicCAS(c.state + e, sl, az_cache_word(AZ_CK_READY, epoch)) == sl;
+        ok = __shfl_sync(gmask, ok, 0, G);
+        if (ok || al < AZ_CACHE_STALE) return 2;             // a failed refresh of a fresh entry: somebody else refreshed it
+        *entry = 0xffffffffu;                                // lost a stale entry to a writer: plain miss, not cached
+        return 0;
+    }
+    unsigned cb = __ballot_sync(gmask, in && (kind == AZ_CK_EMPTY || (kind == AZ_CK_READY && age >= AZ_CACHE_STALE) ||
+                                              (kind == AZ_CK_PENDING && age >= 1u))) & gmask;
+    while (cb) {
+        const int l = (__ffs(cb) - 1) % G;
+        cb &= cb - 1;
+        const uint32_t e = base + (uint32_t)l;
+        const uint32_t old = __shfl_sync(gmask, st, l, G);
+        int ok = 0;
+        if (lane == 0) {
+            ok = atomicCAS(c.state + e, old, az_cache_word(AZ_CK_LOCKED, epoch)) == old;
+            if (ok) {
+                __stcg(c.keys + e, make_ulonglong2(mine, theirs));
+                __threadfence();
+                atomicExch(c.state + e, az_cache_word(AZ_CK_PENDING, epoch));
+            }
+        }
+        ok = __shfl_sync(gmask, ok, 0, G);
+        if (ok) {
+            *entry = e;
+            return 0;
+        }
+    }
+    *entry = 0xffffffffu;
+    return 0;
+}
+
 // Expansion of up to AZ_LP pending leaves of a tree runs in parallel (one lane per leaf generates
 // that leaf's legal moves -- for Gomoku the sequential CPython-set emulation -- into its own scratch).
 #define AZ_LP 8
@@ -219,7 +291,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     const uint8_t is_active = az_ldk(f.active + tree, l2keep), is_done = az_ldk(f.done_flag + tree, l2keep);
     int n_nodes = az_ldk(f.n_nodes + tree, l2keep);
     int sims = az_ldk(f.sims_done + tree, l2keep);
-    const int npend = az_ldk(f.n_pending + tree, l2keep);
+    const int npend0 = az_ldk(f.n_pending + tree, l2keep);
     const int root_player = az_ldk(f.root_player + tree, l2keep);
     const int root_mc = az_ldk(f.root_mc + tree, l2keep);
     AzBoard<NW> rootb;
@@ -258,8 +330,18 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     const int A = g.action_dim;
     const int LP = f.lp;
 
-    unsigned st_sims = 0, st_term = 0, st_exp = 0, st_child = 0, st_sel = 0, st_reads = 0, st_coll = 0;
+    unsigned st_sims = 0, st_term = 0, st_exp = 0, st_child = 0, st_sel = 0, st_reads = 0, st_coll = 0, st_hit = 0;
+    // An answer lives in the evaluation batch (slot < max_leaves) or in the evaluation cache (slot - max_leaves = entry).
+    auto priors_of = [&](int slot) -> const float* {
+        return slot < f.max_leaves ? f.priors + (size_t)slot * A : f.cache.priors + (size_t)(slot - f.max_leaves) * A;
+    };
+    auto value_of = [&](int slot) -> const float* {
+        return slot < f.max_leaves ? f.values + slot : f.cache.values + (slot - f.max_leaves);
+    };
+    int npend = npend0;
+    int np = 0;
 
+  for (int round = 0;; ++round) {     // vl == 1 with the cache: a leaf answered from the cache is expanded in the same launch
     // ---------------- phase A: expand + backup the evaluated leaves -----------------------
     // Priors (lane a keeps prior a and a + 32) and the stored path (lane i keeps entries i and i + 32)
     // of leaf j + 1 are fetched while leaf j is processed: one exposed round trip per leaf (the
@@ -282,13 +364,13 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             my_len = az_ldk(f.path_len + pj, l2keep);
             my_action = az_ldk(f.pend_action + pj, l2keep);
             my_leaf = az_ldk(f.pend_leaf + pj, l2keep);
-            my_val = az_ldk(f.values + my_slot, l2keep);
+            my_val = az_ldk(value_of(my_slot), l2keep);
         }
         float pa = 0.f, pb = 0.f;
         uint32_t q0 = 0, q1 = 0;
         auto fetch = [&](int j, float& xa, float& xb, uint32_t& y0, uint32_t& y1) {
             const int slotx = __shfl_sync(gmask, my_slot, j, G);
-            const float* prx = f.priors + (size_t)slotx * A;
+            const float* prx = priors_of(slotx);
             const uint32_t* gp = f.path + ((size_t)tree * f.vl + j0 + j) * f.max_depth;
             xa = lane < A ? az_ldk(prx + lane, l2keep) : 0.f;
             xb = lane + 32 < A ? az_ldk(prx + lane + 32, l2keep) : 0.f;
@@ -321,7 +403,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             const uint32_t* gpath = f.path + pj * f.max_depth;
             const uint32_t base = (uint32_t)n_nodes;
             n_nodes += nc;
-            const float* pri = f.priors + (size_t)slot * A;
+            const float* pri = priors_of(slot);
             const bool noisy_root = (leaf == 0) && f.use_noise;
             for (int c0 = 0; c0 < nc; c0 += G) {
                 const int c = c0 + lane;
@@ -385,7 +467,8 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
 
     // ---------------- phase B: descend until `vl` leaves are pending -----------------------
     int started = sims;
-    int np = 0;
+    np = 0;
+    bool ready_hit = false;                                   // the last pending leaf found its answer in the cache
     // A tree whose best line ends in a terminal node burns simulation after simulation without ever
     // needing the evaluator; left unbounded, one such tree (up to `iters` descents) sets the duration
     // of the whole launch (measured: one tree 15x the 99th percentile).  The step machine therefore
@@ -395,24 +478,37 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     const unsigned kMaxTerminalPerLaunch = (unsigned)f.vl;
     AzBoard<NW> kept = rootb;
     int kept_player = 0, flushed = 0;
+    uint32_t kept_entry = 0xffffffffu;                        // cache entry of this lane's pending leaf
+    int kept_cached = 0;                                      // ... which already holds (or will hold) the answer: no batch row
     auto hand_off = [&](int upto) {                           // evaluation slots of pending leaves [flushed, upto)
         const int cnt = upto - flushed;
         if (cnt <= 0) return;
+        const unsigned need = __ballot_sync(gmask, lane < cnt && !kept_cached) & gmask;
+        const int rows = __popc(need);
         int base = 0;
-        if (lane == 0) base = atomicAdd(f.n_leaves, cnt);
+        if (lane == 0 && rows) base = atomicAdd(f.n_leaves, rows);
         base = __shfl_sync(gmask, base, 0, G);
         if (lane < cnt) {
-            const int slot = base + lane;
             const size_t pk = (size_t)tree * f.vl + flushed + lane;
-            f.leaf_slot[pk] = slot;
-            f.leaf_player[slot] = (uint8_t)kept_player;
-            f.leaf_tree[slot] = tree;
 #pragma unroll
             for (int w = 0; w < NW; ++w) {
                 f.pend_words[pk * 2 * NW + w] = kept.w[0][w];
                 f.pend_words[pk * 2 * NW + NW + w] = kept.w[1][w];
-                f.leaf_words[(size_t)slot * 2 * NW + w] = kept_player ? kept.w[1][w] : kept.w[0][w];        // canonical: mine
-                f.leaf_words[(size_t)slot * 2 * NW + NW + w] = kept_player ? kept.w[0][w] : kept.w[1][w];   // theirs
+            }
+            if (kept_cached) {
+                f.leaf_slot[pk] = f.max_leaves + (int)kept_entry;
+            } else {
+                const unsigned below = need & ((1u << (threadIdx.x & 31)) - 1u);
+                const int slot = base + __popc(below);
+                f.leaf_slot[pk] = slot;
+                f.leaf_player[slot] = (uint8_t)kept_player;
+                f.leaf_tree[slot] = tree;
+                if (f.cache.cap) f.cache.leaf_entry[slot] = kept_entry;
+#pragma unroll
+                for (int w = 0; w < NW; ++w) {
+                    f.leaf_words[(size_t)slot * 2 * NW + w] = kept_player ? kept.w[1][w] : kept.w[0][w];        // canonical: mine
+                    f.leaf_words[(size_t)slot * 2 * NW + NW + w] = kept_player ? kept.w[0][w] : kept.w[1][w];   // theirs
+                }
             }
         }
     };
@@ -523,9 +619,21 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             if (use_vl) atomicAdd(&nodes[nd].hot.V, 1u);      // fire-and-forget: nobody waits for the old count
         }
         if (use_vl) root_nv += 1;
+        uint32_t entry = 0xffffffffu;
+        int found = 0;
+        if (NW == 1 && f.cache.cap && !f.ucb1) {              // MCTS.cache lookup (ai/mcts.py:37-44) on the canonical position
+            const uint64_t mine = player ? b.w[1][0] : b.w[0][0];
+            uint64_t theirs = player ? b.w[0][0] : b.w[1][0];
+            if (g.planes == 3) theirs |= (uint64_t)player << 63;
+            found = az_cache_probe<G>(f.cache, mine, theirs, lane, gmask, &entry);
+            if (found) ++st_hit;
+            ready_hit = found == 2;
+        }
         if (lane == np - flushed) {
             kept = b;
             kept_player = player;
+            kept_entry = entry;
+            kept_cached = found;
         }
         if (use_vl) m.status = AZ_ST_PENDING;
         if (node == 0) root_m = m;
@@ -546,6 +654,12 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     }
 
     hand_off(np);
+    // vl == 1: the leaf's answer is in the cache -> apply it now and run the next simulation in this launch (the order
+    // of a tree's simulations is untouched, so the search is the reference's; only fewer launches are needed)
+    if (!(f.vl == 1 && np == 1 && ready_hit && round + 1 < f.max_rounds)) break;
+    __syncwarp(gmask);
+    npend = 1;
+  }
     if (lane == 0) {
         f.n_nodes[tree] = n_nodes;
         f.sims_done[tree] = sims;
@@ -555,11 +669,11 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             atomicAdd(f.n_done, 1);
         }
     }
-    if (f.stats && lane < 7) {
-        const unsigned vals[7] = {st_sims, st_term, st_exp, st_child, st_sel, st_reads, st_coll};
+    if (f.stats && lane < 8) {
+        const unsigned vals[8] = {st_sims, st_term, st_exp, st_child, st_sel, st_reads, st_coll, st_hit};
         unsigned v = 0;
 #pragma unroll
-        for (int k = 0; k < 7; ++k) if (lane == k) v = vals[k];
+        for (int k = 0; k < 8; ++k) if (lane == k) v = vals[k];
         if (v) atomicAdd(&f.stats[(size_t)tree * AZ_STAT_COUNT + lane], (unsigned long long)v);   // no reply needed
     }
     AZ_AT(8);                                                 // tail writes
@@ -582,6 +696,7 @@ namespace {
 __global__ void az_begin_move_kernel(AzForestDev f) {
     const int tree = blockIdx.x * blockDim.x + threadIdx.x;
     if (tree >= f.n_trees) return;
+    if (tree == 0 && f.cache.cap) *f.cache.epoch += 1u;       // a new search: entries age by one
     AzHot h;
     h.N = 0;
     h.Q = 0.f;
@@ -601,6 +716,35 @@ __global__ void az_begin_move_kernel(AzForestDev f) {
     const bool live = f.active[tree] != 0;
     f.done_flag[tree] = live ? 0 : 1;
     if (!live) atomicAdd(f.n_done, 1);                       // counters are zeroed by the host before
+}
+
+// Runs in front of every advance launch when the cache is on (instead of the memset of the batch counter): the rows the
+// evaluator answered since the last launch are copied into the entries their leaves claimed (the store of ai/mcts.py:51)
+// and the entries become READY; the last block to finish zeroes the batch counter for the launch that follows.
+__global__ void az_cache_publish_kernel(AzForestDev f, unsigned int* ticket) {
+    const int n = min(*f.n_leaves, f.max_leaves);
+    const int A = f.g.action_dim;
+    const uint32_t epoch = *f.cache.epoch;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < (long long)n * (A + 1); t += (long long)gridDim.x * blockDim.x) {
+        const int row = (int)(t / (A + 1));
+        const int a = (int)(t - (long long)row * (A + 1));
+        const uint32_t e = f.cache.leaf_entry[row];
+        if (e == 0xffffffffu) continue;
+        if (a < A) {
+            f.cache.priors[(size_t)e * A + a] = f.priors[(size_t)row * A + a];
+        } else {                                              // nobody reads the cache while this kernel runs (stream order)
+            f.cache.values[e] = f.values[row];
+            f.cache.state[e] = (AZ_CK_READY << 30) | (epoch & 0xffu);
+        }
+    }
+    __shared__ unsigned int last;                             // every block has read the counter: the last one out resets it
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+    __syncthreads();
+    if (last && threadIdx.x == 0) {
+        *f.n_leaves = 0;
+        *ticket = 0u;
+    }
 }
 
 // splitmix64 finaliser; the build-defined hash evaluator (oracle/az_oracle.py: hash_eval_*).
@@ -804,6 +948,7 @@ __global__ void az_root_visits_kernel(AzForestDev f, int* visits, double* q) {
 #include "../../include/az_b200.h"
 
 thread_local std::string g_az_error;
+extern "C" int az_forest_cache_clear(az_forest* f, void* stream);
 
 extern "C" const char* az_last_error(void) { return g_az_error.c_str(); }
 extern "C" const char* az_version(void) { return "az_b200 0.1 (sm_100a)"; }
@@ -876,7 +1021,13 @@ struct az_forest {
     size_t h_stage_bytes = 0;
     float* planes_stage_dev = nullptr;
     int32_t* i32_stage_dev = nullptr;
+    unsigned long long uid = 0;          // never reused (graphs are keyed by it, az_net.cu)
+    unsigned int* cache_ticket = nullptr;
+    std::vector<void*> cache_allocs;
+    unsigned long long eval_tag = 0;     // identity of the evaluator whose answers the cache holds
+    bool eval_tag_set = false;
 };
+static unsigned long long g_forest_uid = 0;
 
 namespace {
 
@@ -979,6 +1130,9 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     d.use_noise = 0;
     d.ucb1 = 0;
     d.log_tab = nullptr;
+    d.cache = AzCacheDev{};
+    d.max_rounds = 1;
+    f->uid = ++g_forest_uid;
     f->max_iters = max_iters;
     // One warp per tree: sub-warp groups (8 lanes for the <= 9-children games) share a warp between
     // four trees whose descents diverge and serialise; measured 4x slower on Connect4.  AZ_FOREST_GROUP=8
@@ -1032,7 +1186,9 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     AZ_ALLOC(f->i32_stage_dev, (size_t)n_trees * 2);
     uint64_t* hash_dev = nullptr;
     AZ_ALLOC(hash_dev, (size_t)g.state_dim);
+    AZ_ALLOC(f->cache_ticket, 4);
 #undef AZ_ALLOC
+    cudaMemset(f->cache_ticket, 0, 16);
     std::vector<uint64_t> hashes(g.state_dim);
     for (int i = 0; i < g.state_dim; ++i) hashes[i] = az_tuple2_hash(i / g.cols, i % g.cols);
     cudaMemcpy(hash_dev, hashes.data(), hashes.size() * 8, cudaMemcpyHostToDevice);
@@ -1063,12 +1219,135 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
         az_forest_destroy(f);
         return az_fail(AZ_ECUDA, std::string("az_forest_create: ") + cudaGetErrorString(e));
     }
+    // Evaluation cache on by default for boards of <= 64 cells: room for the distinct positions of ~3 searches of every
+    // tree (entries older than AZ_CACHE_STALE searches are recycled), at most 2^25 entries.  AZ_NO_CACHE=1 / AZ_CACHE_LOG2=n.
+    if (nw == 1 && f->G == 32 && !getenv("AZ_NO_CACHE")) {
+        int lg = 10;
+        const double want = 3.0 * (double)n_trees * (double)max_iters * (double)std::min(vl_batch, 2);
+        while (lg < 25 && (double)((size_t)1 << lg) < want) ++lg;
+        if (const char* e2 = getenv("AZ_CACHE_LOG2")) lg = std::max(4, std::min(28, atoi(e2)));
+        if ((rc = az_forest_cache_config(f, lg)) != AZ_OK) {
+            az_forest_destroy(f);
+            return rc;
+        }
+    }
     *out = f;
+    return AZ_OK;
+}
+
+static void az_cache_free(az_forest* f) {
+    for (void* p : f->cache_allocs) cudaFree(p);
+    f->cache_allocs.clear();
+    f->d.cache = AzCacheDev{};
+    f->d.max_rounds = 1;
+}
+
+// Evaluation cache of 2^log2_entries entries (0 = off).  Replaces any existing cache (and the step graphs that baked
+// its pointers in).  Each entry costs 24 + 4 * (A + 1) bytes.
+extern "C" int az_forest_cache_config(az_forest* f, int log2_entries) {
+    if (!f || log2_entries < 0 || log2_entries > 28) return az_fail(AZ_EINVAL, "cache_config: log2_entries in 0..28");
+    if (log2_entries && log2_entries < 4) log2_entries = 4;
+    cudaDeviceSynchronize();
+    az_net_forget_forest(f->uid);
+    az_cache_free(f);
+    if (!log2_entries) return AZ_OK;
+    if (f->d.g.nw != 1 || f->G != 32) return az_fail(AZ_EINVAL, "cache_config: boards of <= 64 cells only");
+    const size_t cap = (size_t)1 << log2_entries;
+    const int A = f->d.g.action_dim;
+    AzCacheDev c{};
+    auto alloc = [&](void** p, size_t bytes) {
+        if (cudaMalloc(p, bytes + 16) != cudaSuccess) return false;
+        f->cache_allocs.push_back(*p);
+        return true;
+    };
+    void *keys = nullptr, *state = nullptr, *values = nullptr, *priors = nullptr, *epoch = nullptr, *le = nullptr;
+    if (!alloc(&keys, cap * 16) || !alloc(&state, cap * 4) || !alloc(&values, cap * 4) || !alloc(&priors, cap * (size_t)A * 4) ||
+        !alloc(&epoch, 16) || !alloc(&le, (size_t)f->d.max_leaves * 4)) {
+        az_cache_free(f);
+        cudaGetLastError();
+        return az_fail(AZ_ENOMEM, "cache_config: cudaMalloc failed");
+    }
+    c.cap = (uint32_t)cap;
+    c.keys = reinterpret_cast<ulonglong2*>(keys);
+    c.state = reinterpret_cast<uint32_t*>(state);
+    c.values = reinterpret_cast<float*>(values);
+    c.priors = reinterpret_cast<float*>(priors);
+    c.epoch = reinterpret_cast<uint32_t*>(epoch);
+    c.leaf_entry = reinterpret_cast<uint32_t*>(le);
+    c.n_prev = nullptr;
+    cudaMemset(state, 0, cap * 4);
+    cudaMemset(keys, 0, cap * 16);
+    cudaMemset(epoch, 0, 16);
+    cudaMemset(le, 0xff, (size_t)f->d.max_leaves * 4);
+    f->d.cache = c;
+    int rounds = 4;                                           // simulations per tree and launch while leaves hit the cache (vl == 1)
+    if (const char* e = getenv("AZ_CACHE_ROUNDS")) rounds = std::max(1, std::min(64, atoi(e)));
+    f->d.max_rounds = rounds;
+    if (cudaDeviceSynchronize() != cudaSuccess) return az_fail(AZ_ECUDA, "cache_config: device error");
+    return AZ_OK;
+}
+
+// Forget every cached answer (main.py:55-57 clears MCTS.cache after each model update).
+extern "C" int az_forest_cache_clear(az_forest* f, void* stream) {
+    if (!f) return az_fail(AZ_EINVAL, "cache_clear: null");
+    if (!f->d.cache.cap) return AZ_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (cudaMemsetAsync(f->d.cache.state, 0, (size_t)f->d.cache.cap * 4, s) != cudaSuccess) return az_fail(AZ_ECUDA, "cache_clear: memset");
+    if (cudaMemsetAsync(f->d.cache.leaf_entry, 0xff, (size_t)f->d.max_leaves * 4, s) != cudaSuccess) return az_fail(AZ_ECUDA, "cache_clear: memset");
+    return AZ_OK;
+}
+
+extern "C" int az_forest_cache_info(az_forest* f, long long* entries, long long* bytes) {
+    if (!f) return az_fail(AZ_EINVAL, "cache_info: null");
+    const long long cap = f->d.cache.cap;
+    if (entries) *entries = cap;
+    if (bytes) *bytes = cap * (24 + 4 * (long long)(f->d.g.action_dim + 1));
+    return AZ_OK;
+}
+
+int az_forest_set_eval_tag(az_forest* f, unsigned long long tag, cudaStream_t s) {
+    if (f->eval_tag_set && f->eval_tag == tag) return AZ_OK;
+    const bool had = f->eval_tag_set;
+    f->eval_tag = tag;
+    f->eval_tag_set = true;
+    return had ? az_forest_cache_clear(f, s) : AZ_OK;
+}
+// Step-by-step searches (az_forest_advance + an evaluator call): the evaluator must be the one the cache was filled by.
+int az_forest_check_eval_tag(az_forest* f, unsigned long long tag) {
+    if (!f->d.cache.cap || f->d.ucb1) return AZ_OK;
+    if (!f->eval_tag_set) {
+        f->eval_tag = tag;
+        f->eval_tag_set = true;
+        return AZ_OK;
+    }
+    if (f->eval_tag != tag)
+        return az_fail(AZ_ESTATE, "the evaluation cache holds another evaluator's answers: call az_forest_set_evaluator (or "
+                                  "az_forest_cache_clear) before az_forest_begin_move when the evaluator changes");
+    return AZ_OK;
+}
+unsigned long long az_hash_eval_tag(uint64_t seed, int qbits) {
+    return 0x4841534800000000ull ^ (seed * 0x9E3779B97F4A7C15ull) ^ (unsigned long long)qbits;
+}
+// Public form of the tag: the caller names the evaluator whose answers may be cached from now on (any 64-bit id that
+// changes when the evaluator or its weights change); a different id drops the cached answers.
+extern "C" int az_forest_set_evaluator(az_forest* f, unsigned long long id, void* stream) {
+    if (!f) return az_fail(AZ_EINVAL, "set_evaluator: null");
+    return az_forest_set_eval_tag(f, id, (cudaStream_t)stream);
+}
+
+unsigned long long az_forest_uid(az_forest* f) { return f->uid; }
+double* az_forest_noise_dev(az_forest* f) { return f->noise_dev; }
+int az_forest_use_device_noise(az_forest* f, int on) {
+    f->d.use_noise = on ? 1 : 0;
+    f->d.root_noise = on ? f->noise_dev : nullptr;
     return AZ_OK;
 }
 
 extern "C" void az_forest_destroy(az_forest* f) {
     if (!f) return;
+    cudaDeviceSynchronize();
+    az_net_forget_forest(f->uid);                              // step graphs hold this forest's device pointers
+    az_cache_free(f);
     for (void* p : f->allocs) cudaFree(p);
     if (f->h_counts) cudaFreeHost(f->h_counts);
     if (f->h_stage) cudaFreeHost(f->h_stage);
@@ -1143,7 +1422,13 @@ extern "C" int az_forest_begin_move(az_forest* f, int iters, void* stream) {
 extern "C" int az_forest_advance(az_forest* f, void* stream) {
     if (!f) return az_fail(AZ_EINVAL, "advance: null");
     cudaStream_t s = (cudaStream_t)stream;
-    AZ_CUDA_OK(cudaMemsetAsync(f->d.n_leaves, 0, sizeof(int), s));
+    if (f->d.cache.cap) {
+        const long long work = (long long)f->d.max_leaves * (f->d.g.action_dim + 1);
+        const int grid = (int)std::max<long long>(1, std::min<long long>((work + 1023) / 1024, 148 * 4));
+        az_cache_publish_kernel<<<grid, 256, 0, s>>>(f->d, f->cache_ticket);
+    } else {
+        AZ_CUDA_OK(cudaMemsetAsync(f->d.n_leaves, 0, sizeof(int), s));
+    }
     if (f->d.g.nw == 1) {
         if (f->G == 8) az_launch_advance<1, 8>(f, s);
         else az_launch_advance<1, 32>(f, s);
@@ -1166,6 +1451,7 @@ extern "C" int az_forest_counts(az_forest* f, int* n_leaves, int* n_done, void* 
 
 extern "C" int az_eval_hash(az_forest* f, uint64_t seed, int qbits, void* stream) {
     if (!f || qbits < 1 || qbits > 16) return az_fail(AZ_EINVAL, "eval_hash: qbits in 1..16");
+    if (int rc = az_forest_check_eval_tag(f, az_hash_eval_tag(seed, qbits))) return rc;
     int lg = 0;
     while ((1 << lg) < f->d.g.action_dim) ++lg;
     const float scale = ldexpf(1.0f, -(qbits + lg));
@@ -1239,13 +1525,15 @@ extern "C" int az_leaves_set_logits(az_forest* f, const float* logits_dev, const
 }
 
 extern "C" int az_forest_search_hash(az_forest* f, int iters, uint64_t seed, int qbits, void* stream) {
-    int rc = az_forest_begin_move(f, iters, stream);
+    if (!f) return az_fail(AZ_EINVAL, "search_hash: null");
+    int rc = az_forest_set_eval_tag(f, az_hash_eval_tag(seed, qbits), (cudaStream_t)stream);
     if (rc) return rc;
+    if ((rc = az_forest_begin_move(f, iters, stream))) return rc;
     // vl == 1: every advance retires one simulation per live tree, so iters + 1 advances
     // finish the search (the last one only applies results); vl > 1 polls the done counter.
     int done = 0, steps = 0;
     for (;;) {
-        const int burst = steps == 0 ? (f->d.vl == 1 ? iters + 1 : std::max(8, iters / f->d.vl)) : 4;
+        const int burst = steps == 0 ? (f->d.vl == 1 && !f->d.cache.cap ? iters + 1 : std::max(8, iters / f->d.vl / (f->d.cache.cap ? 2 : 1))) : 4;
         for (int i = 0; i < burst; ++i) {
             if ((rc = az_forest_advance(f, stream))) return rc;
             if ((rc = az_eval_hash(f, seed, qbits, stream))) return rc;

@@ -17,7 +17,32 @@
 #define AZ_STAT_SELECT 4      // select steps (edges walked)
 #define AZ_STAT_CHILD_READS 5 // children scored in select
 #define AZ_STAT_COLLIDE 6     // virtual-loss batches cut short by a pending leaf
+#define AZ_STAT_CACHE_HIT 7   // leaves answered by the evaluation cache (no evaluator row)
 #define AZ_STAT_COUNT 8
+
+// Device evaluation cache: the GPU analogue of MCTS.cache (ai/mcts.py:7,37-51) -- canonical position -> (softmax priors
+// f32[A], value).  Open addressing in HBM, 8-entry windows (one 128-byte line of keys, probed by 8 lanes at once).
+// A leaf that finds its position takes the cached answer instead of an evaluator row; leaves of different trees that
+// reach the same new position in one launch share ONE row (the first claims the entry, the others wait for it).
+// state[e]: bits 31:30 kind (0 empty, 1 locked: key being written, 2 pending: evaluation in flight, 3 ready),
+//           bits 7:0 search number of the last use; entries not used for AZ_CACHE_STALE searches may be overwritten.
+// Boards of <= 64 cells only (16-byte keys; the side to move of the 3-plane games rides in bit 63 of `theirs`).
+#define AZ_CACHE_WINDOW 8
+#define AZ_CACHE_STALE 2
+#define AZ_CK_EMPTY 0u
+#define AZ_CK_LOCKED 1u
+#define AZ_CK_PENDING 2u
+#define AZ_CK_READY 3u
+struct AzCacheDev {
+    uint32_t cap;             // entries, power of two; 0 = cache off
+    ulonglong2* keys;         // [cap] {mine, theirs | player << 63}
+    uint32_t* state;          // [cap]
+    float* values;            // [cap]
+    float* priors;            // [cap][A]
+    uint32_t* epoch;          // device scalar: search number (az_begin_move_kernel increments it)
+    uint32_t* leaf_entry;     // [max_leaves] entry claimed by the batch row, 0xffffffff = none
+    int* n_prev;              // device scalar: rows of the previous batch still to be published
+};
 
 struct AzForestDev {
     AzGame g;
@@ -69,4 +94,6 @@ struct AzForestDev {
 
     const uint64_t* cell_hash; // CPython hash((r,c)) per cell (Gomoku child order)
     unsigned long long* stats; // AZ_STAT_*
+    AzCacheDev cache;
+    int max_rounds;            // vl == 1 with the cache: simulations a tree may run in one launch while its leaves hit the cache
 };

@@ -331,6 +331,7 @@ struct az_net {
     uint8_t* in_player = nullptr;
     float *out_priors = nullptr, *out_values = nullptr, *out_logits = nullptr;
     unsigned long long launches = 0;     // kernels launched by forward passes
+    unsigned long long weights_version = 0;   // changes with every az_net_finalize: tag of the forests' evaluation caches
     // optional per-kernel timing of eager forward passes (bench.py roofline numbers)
     bool prof_on = false;
     struct ProfRec { int kind; cudaEvent_t a, b; };
@@ -432,6 +433,8 @@ static const std::vector<float>* az_param(az_net* n, const std::string& name, si
 // encodes the TMA descriptors.  Call again after az_net_set_param to refresh the weights.
 extern "C" int az_net_finalize(az_net* n) {
     if (!n) return az_fail(AZ_EINVAL, "az_net_finalize: null");
+    static unsigned long long g_weights_version = 0;
+    n->weights_version = 0x4E45540000000000ull + (++g_weights_version);
     az_net_invalidate_graphs(n);
     for (void* p : n->allocs) cudaFree(p);
     n->allocs.clear();
@@ -1120,6 +1123,7 @@ extern "C" int az_net_eval_leaves(az_net* n, az_forest* f, void* stream) {
     AzForestDev* d = az_forest_dev(f);
     if (d->g.rows != n->rows || d->g.cols != n->cols || d->g.planes != n->C || d->g.action_dim != n->A)
         return az_fail(AZ_EINVAL, "az_net_eval_leaves: net and forest disagree on the game");
+    if (int rc = az_forest_check_eval_tag(f, n->weights_version)) return rc;
     for (int off = 0; off < d->max_leaves; off += n->chunk) {
         AzBatch b{d->n_leaves, 0, off, std::min(n->chunk, d->max_leaves - off)};
         int rc = az_net_forward_chunk(n, b, d->leaf_words, d->leaf_player, d->g.nw, d->priors, d->values, nullptr, (cudaStream_t)stream);
@@ -1188,11 +1192,18 @@ extern "C" long long az_net_launch_count(az_net* n) { return n ? (long long)n->l
 struct AzStepGraph {
     unsigned long long kernels = 0;     // kernels in one captured graph
     int steps = 1;                      // search steps per graph
-    az_forest* f = nullptr;
-    int iters = -1, use_noise = -1;
+    unsigned long long forest_uid = 0;  // az_forest_uid of the forest whose buffers the graph bakes in (never reused, unlike the pointer)
+    int iters = -1, use_noise = -1, cache_on = -1;
+    unsigned long long last_use = 0;
     cudaGraphExec_t exec = nullptr;
 };
-static std::map<az_net*, AzStepGraph> g_graphs;
+// A captured step bakes in AzForestDev by value (device pointers, n_trees, cap, vl), so a graph belongs to ONE forest:
+// graphs are keyed by the forest's unique id (a destroyed forest's address is routinely handed out again by `new`),
+// and az_forest_destroy drops every graph of that forest (az_net_forget_forest).  A net keeps up to AZ_MAX_GRAPHS graphs
+// (e.g. two arena engines or a warm-up forest next to the main one) and evicts the least recently used.
+#define AZ_MAX_GRAPHS 4
+static std::map<az_net*, std::vector<AzStepGraph>> g_graphs;
+static unsigned long long g_graph_clock = 0;
 static cudaStream_t g_own_stream = nullptr;
 
 static int az_step_eager(az_net* n, az_forest* f, cudaStream_t s) {
@@ -1200,6 +1211,20 @@ static int az_step_eager(az_net* n, az_forest* f, cudaStream_t s) {
     if (rc) return rc;
     ++n->launches;                                          // the advance kernel
     return az_net_eval_leaves(n, f, s);
+}
+
+void az_net_forget_forest(unsigned long long forest_uid) {
+    for (auto& kv : g_graphs) {
+        auto& v = kv.second;
+        for (size_t i = 0; i < v.size();) {
+            if (v[i].forest_uid == forest_uid) {
+                if (v[i].exec) cudaGraphExecDestroy(v[i].exec);
+                v.erase(v.begin() + (long)i);
+            } else {
+                ++i;
+            }
+        }
+    }
 }
 
 extern "C" int az_forest_search_net(az_forest* f, az_net* n, int iters, void* stream) {
@@ -1211,13 +1236,25 @@ extern "C" int az_forest_search_net(az_forest* f, az_net* n, int iters, void* st
         AZ_CUDA_OK(cudaStreamSynchronize(0));
         s = g_own_stream;
     }
-    int rc = az_forest_begin_move(f, iters, s);
+    int rc = az_forest_set_eval_tag(f, n->weights_version, s);   // a weight upload clears the cache (main.py:55-57)
     if (rc) return rc;
+    if ((rc = az_forest_begin_move(f, iters, s))) return rc;
     AzForestDev* d = az_forest_dev(f);
-    AzStepGraph& g = g_graphs[n];
+    const unsigned long long uid = az_forest_uid(f);
+    const int cache_on = d->cache.cap ? 1 : 0;
+    std::vector<AzStepGraph>& gv = g_graphs[n];
+    AzStepGraph* gp = nullptr;
+    for (auto& c : gv)
+        if (c.forest_uid == uid && c.iters == iters && c.use_noise == d->use_noise && c.cache_on == cache_on && c.exec) gp = &c;
     int steps = 0;
-    if (g.f != f || g.iters != iters || g.use_noise != d->use_noise || !g.exec) {
-        if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
+    if (!gp) {
+        if (gv.size() >= AZ_MAX_GRAPHS) {                   // evict the least recently used graph of this net
+            size_t lru = 0;
+            for (size_t i = 1; i < gv.size(); ++i) if (gv[i].last_use < gv[lru].last_use) lru = i;
+            if (gv[lru].exec) cudaGraphExecDestroy(gv[lru].exec);
+            gv.erase(gv.begin() + (long)lru);
+        }
+        AzStepGraph g;
         if ((rc = az_step_eager(n, f, s))) return rc;      // warm-up outside capture (sets func attributes)
         ++steps;
         cudaGraph_t graph = nullptr;
@@ -1236,11 +1273,15 @@ extern "C" int az_forest_search_net(az_forest* f, az_net* n, int iters, void* st
         ce = cudaGraphInstantiate(&g.exec, graph, 0);
         cudaGraphDestroy(graph);
         if (ce != cudaSuccess) return az_fail(AZ_ECUDA, std::string("graph instantiate: ") + cudaGetErrorString(ce));
-        g.f = f; g.iters = iters; g.use_noise = d->use_noise;
+        g.forest_uid = uid; g.iters = iters; g.use_noise = d->use_noise; g.cache_on = cache_on;
+        gv.push_back(g);
+        gp = &gv.back();
     }
+    AzStepGraph& g = *gp;
+    g.last_use = ++g_graph_clock;
     int done = 0;
     for (;;) {
-        const int want = steps <= 1 ? (d->vl == 1 ? iters + 1 - steps : std::max(8, iters / d->vl)) : 4;
+        const int want = steps <= 1 ? (d->vl == 1 && !cache_on ? iters + 1 - steps : std::max(8, iters / d->vl)) : 4;
         const int burst = (want + g.steps - 1) / g.steps;
         for (int i = 0; i < burst; ++i) {
             AZ_CUDA_OK(cudaGraphLaunch(g.exec, s));
@@ -1257,7 +1298,8 @@ extern "C" int az_forest_search_net(az_forest* f, az_net* n, int iters, void* st
 extern "C" int az_net_invalidate_graphs(az_net* n) {
     auto it = g_graphs.find(n);
     if (it != g_graphs.end()) {
-        if (it->second.exec) cudaGraphExecDestroy(it->second.exec);
+        for (auto& g : it->second)
+            if (g.exec) cudaGraphExecDestroy(g.exec);
         g_graphs.erase(it);
     }
     return AZ_OK;

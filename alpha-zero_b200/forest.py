@@ -180,10 +180,27 @@ class Forest:
                                                        C.byref(rv), C.byref(rw), self.stream), "root_children")
         return dict(cells=cells[:n], visits=vis[:n], W=W[:n], P=P[:n], root_visit=rv.value, root_value=rw.value)
 
+    # ---- evaluation cache (MCTS.cache, ai/mcts.py:7,37-51) ------------------------------------------
+    def cache_config(self, log2_entries):
+        """2**log2_entries entries; 0 turns the cache off (boards of <= 64 cells only)."""
+        _lib.check(self._L.az_forest_cache_config(self.h, int(log2_entries)), "cache_config")
+
+    def cache_clear(self):
+        _lib.check(self._L.az_forest_cache_clear(self.h, self.stream), "cache_clear")
+
+    def cache_info(self):
+        a, b = C.c_longlong(), C.c_longlong()
+        _lib.check(self._L.az_forest_cache_info(self.h, C.byref(a), C.byref(b)), "cache_info")
+        return dict(entries=a.value, bytes=b.value)
+
+    def set_evaluator(self, ident):
+        """Step-by-step searches: name the evaluator (any integer that changes with it) before begin_move."""
+        _lib.check(self._L.az_forest_set_evaluator(self.h, C.c_ulonglong(int(ident) & (2 ** 64 - 1)), self.stream), "set_evaluator")
+
     def stats(self, reset=False):
         out = np.zeros(8, dtype=np.uint64)
         _lib.check(self._L.az_forest_stats(self.h, _ptr(out), int(reset), self.stream), "stats")
-        keys = ["sims", "terminal", "expansions", "children", "selects", "child_reads", "collisions", "_"]
+        keys = ["sims", "terminal", "expansions", "children", "selects", "child_reads", "collisions", "cache_hits"]
         return dict(zip(keys, out.tolist()))
 
 

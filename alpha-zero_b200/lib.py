@@ -53,6 +53,24 @@ _SIGS = {
     "az_net_profile_read": (i32, [vp, i32, vp, vp, vp]),
     "az_gemm_bf16": (i32, [vp, i32, vp, vp, vp, i32, vp, i32, i32, i32, i32, i32, vp]),
 }
+_SIGS.update({
+    "az_forest_cache_config": (i32, [vp, i32]),
+    "az_forest_cache_clear": (i32, [vp, vp]),
+    "az_forest_cache_info": (i32, [vp, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
+    "az_forest_set_evaluator": (i32, [vp, C.c_ulonglong, vp]),
+    "az_selfplay_create": (i32, [vp, i32, i32, i32, u64, i32, i32, C.POINTER(vp)]),
+    "az_selfplay_destroy": (None, [vp]),
+    "az_selfplay_begin": (i32, [vp, i32, vp]),
+    "az_selfplay_prepare": (i32, [vp, vp]),
+    "az_selfplay_move": (i32, [vp, vp]),
+    "az_selfplay_status": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(C.c_longlong), vp]),
+    "az_selfplay_run_net": (i32, [vp, vp, i32, i32, vp]),
+    "az_selfplay_run_hash": (i32, [vp, i32, u64, i32, i32, vp]),
+    "az_selfplay_buffers": (i32, [vp, C.POINTER(vp), C.POINTER(i32), C.POINTER(i32)]),
+    "az_selfplay_read": (i32, [vp] * 10),
+    "az_selfplay_read_slots": (i32, [vp, vp, vp, vp]),
+    "az_selfplay_launch_count": (C.c_longlong, [vp]),
+})
 # entry points added by later translation units; bound when present in the header
 _OPTIONAL = {}
 

@@ -1,20 +1,23 @@
 """Multi-GPU self-play: games are the unit of parallelism (the reference plays them one after
 another with no shared state, train.py:64-67).  One process per GPU; game g belongs to rank
-g % world; there is NO collective inside a search.  The only exchange is the all-gather of the
-finished trajectories into every rank's replay buffer, in a compact form
+g % world (local game k of rank r has global id r + k * world); there is NO collective inside a
+search or a game.  The only exchange is the all-gather of the finished trajectories, straight from
+the device-resident trajectory store of the self-play engine (csrc/az_selfplay.cu) in compact form
 
-    per position : side bitboards 2 x nw x u64, side to move u8, root visit counts u16[A], root Q f64
-    per game     : global id i32, plies u16, winner i8
+    per game     : plies i32, winner i32, first recorded ply i32
+    per position : side bitboards 2 x nw x u64, root visit counts u16[A], root Q f64, move (cell) i16
 
-(116 B per 7x7 position instead of the 788 B of the reference's f32 board + f64 policy).  The
-receiver rebuilds exactly what Game.self_play returns (boards float32 [C,H,W], policies
-visits / sum(visits) as float64, gomoku.py:138-141) and stores it with train.save_data_to_buffer
-(canonicalisation + augmentation, train.py:30-49) in GLOBAL game order, so the buffer content does
-not depend on the number of ranks.  Gradients are all-reduced in train.train.
+(124 B per 7x7 position instead of the 788 B of the reference's f32 board + f64 policy), ONE
+all_gather_into_tensor of the byte image of those arrays over NCCL / NVLink.  Because every random
+draw of a game is keyed by its GLOBAL id (Philox, az_selfplay.cu) and games are merged in global
+order, the gathered trajectories -- and the replay buffer filled from them -- do not depend on
+the number of ranks (given a deterministic evaluator).  Gradients are all-reduced in train.train.
 """
 import numpy as np
 import torch
 import torch.distributed as dist
+
+TRAJ_KEYS = ("plies", "winner", "first", "words", "visits", "q", "action")
 
 
 def world():
@@ -30,125 +33,100 @@ def shard_games(n_games, rank=None, world_size=None):
     return list(range(rank, n_games, world_size))
 
 
-def _nw(Game):
-    return 1 if Game.rows * Game.cols <= 64 else 4
+def _as_tensor(x):
+    if isinstance(x, torch.Tensor):
+        return x
+    a = np.ascontiguousarray(x)
+    if a.dtype == np.uint64:
+        a = a.view(np.int64)
+    elif a.dtype == np.uint16:
+        a = a.view(np.int16)
+    return torch.from_numpy(a)
 
 
-def pack_games(Game, games, global_ids, visits):
-    """games: list of (boards, actions, policies, qs, winner) as play_games returns them;
-    visits: per game, int array [plies][A] of root visit counts.  -> uint8 array."""
-    nw, A = _nw(Game), Game.action_dim
-    cells = Game.rows * Game.cols
-    out = []
-    for gid, (boards, actions, _policies, qs, winner), vis in zip(global_ids, games, visits):
-        plies = len(boards)
-        out.append(np.array([gid], np.int32).tobytes())
-        out.append(np.array([plies], np.uint16).tobytes())
-        out.append(np.array([winner], np.int8).tobytes())
-        words = np.zeros((plies, 2, nw), np.uint64)
-        for i, b in enumerate(boards):
-            for side in range(2):
-                idx = np.nonzero(b[side].reshape(-1) == 1.0)[0]
-                for c in idx:
-                    words[i, side, c >> 6] |= np.uint64(1) << np.uint64(c & 63)
-        assert cells <= 64 * nw
-        out.append(words.tobytes())
-        out.append(np.asarray(vis, np.uint16).reshape(plies, A).tobytes())
-        out.append(np.asarray(qs, np.float64).tobytes())
-        acts = np.array([[-1, -1] if a is None else list(a) for a in actions], np.int16)   # plies + 1 entries (gomoku.py:129)
-        out.append(np.array([len(acts)], np.uint16).tobytes())
-        out.append(acts.tobytes())
-    return np.frombuffer(b"".join(out), np.uint8).copy()
-
-
-def unpack_games(Game, blob):
-    """Inverse of pack_games -> list of (global id, (boards, actions, policies, qs, winner))."""
-    nw, A, C = _nw(Game), Game.action_dim, Game.feature_dim
-    rows, cols = Game.rows, Game.cols
-    buf = np.asarray(blob, np.uint8).tobytes()
-    off, games = 0, []
-
-    def take(dtype, count):
-        nonlocal off
-        n = np.dtype(dtype).itemsize * count
-        a = np.frombuffer(buf, dtype, count, off)
-        off += n
-        return a
-
-    while off < len(buf):
-        gid = int(take(np.int32, 1)[0])
-        plies = int(take(np.uint16, 1)[0])
-        winner = int(take(np.int8, 1)[0])
-        words = take(np.uint64, plies * 2 * nw).reshape(plies, 2, nw)
-        vis = take(np.uint16, plies * A).reshape(plies, A).astype(np.int64)
-        qs = [float(q) for q in take(np.float64, plies)]
-        na = int(take(np.uint16, 1)[0])
-        acts = [tuple(int(v) for v in a) for a in take(np.int16, na * 2).reshape(na, 2)]
-        boards, policies = [], []
-        for i in range(plies):
-            b = np.zeros((C, rows, cols), np.float32)
-            for side in range(2):
-                for w in range(nw):
-                    v = int(words[i, side, w])
-                    while v:
-                        low = v & -v
-                        c = w * 64 + low.bit_length() - 1
-                        b[side, c // cols, c % cols] = 1.0
-                        v ^= low
-            if C == 3:                                  # plane 2 = side to move (connect4.py:55-70): ply i is played by i % 2
-                b[2] = float(i % 2)
-            boards.append(b)
-            policies.append(vis[i] / vis[i].sum())      # utils.py:46-55 (float64)
-        games.append((gid, (boards, acts, policies, qs, winner)))
-    return games
-
-
-def all_gather_bytes(blob, device=None):
-    """Variable-length all-gather of uint8 arrays: sizes first, then the padded payload."""
+def gather_trajectories(local, n_total):
+    """local: dict of TRAJ_KEYS -> tensor (CUDA for NCCL, CPU for gloo) or array with leading dim = this rank's games
+    (ids rank, rank + world, ...).  Returns the same dict for ALL n_total games in global id order, on the same device.
+    One collective: the arrays' bytes are concatenated, padded to ceil(n_total / world) games and all-gathered."""
     rank, ws = world()
+    t = {k: _as_tensor(local[k]) for k in TRAJ_KEYS}
     if ws == 1:
-        return [np.asarray(blob, np.uint8)]
-    if device is None:
-        device = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
-    n = torch.tensor([len(blob)], dtype=torch.int64, device=device)
-    sizes = [torch.zeros_like(n) for _ in range(ws)]
-    dist.all_gather(sizes, n)
-    sizes = [int(s.item()) for s in sizes]
-    cap = max(max(sizes), 1)
-    mine = torch.zeros(cap, dtype=torch.uint8, device=device)
-    mine[:len(blob)] = torch.from_numpy(np.asarray(blob, np.uint8)).to(device)
-    parts = [torch.empty(cap, dtype=torch.uint8, device=device) for _ in range(ws)]
-    dist.all_gather(parts, mine)
-    return [p[:s].cpu().numpy() for p, s in zip(parts, sizes)]
-
-
-def gather_games(Game, games, global_ids, visits):
-    """Every rank receives every finished game, sorted by global id."""
-    blobs = all_gather_bytes(pack_games(Game, games, global_ids, visits))
-    merged = [g for blob in blobs for g in unpack_games(Game, blob)]
-    merged.sort(key=lambda t: t[0])
+        return {k: v[:n_total] for k, v in t.items()}
+    gmax = (n_total + ws - 1) // ws
+    dev = t["q"].device
+    parts, meta = [], []
+    for k in TRAJ_KEYS:
+        x = t[k].contiguous()
+        if x.shape[0] < gmax:                                          # ranks with one game fewer: zero padding (plies = 0)
+            pad = torch.zeros((gmax - x.shape[0],) + tuple(x.shape[1:]), dtype=x.dtype, device=dev)
+            x = torch.cat([x, pad], 0)
+        meta.append((k, x.dtype, tuple(x.shape[1:])))
+        parts.append(x[:gmax].reshape(-1).view(torch.uint8))
+    mine = torch.cat(parts)
+    flat = torch.empty(ws * mine.numel(), dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(flat, mine)
+    out = flat.view(ws, mine.numel())
+    merged, off = {}, 0
+    for k, dt, tail in meta:
+        nbytes = gmax * int(np.prod(tail, dtype=np.int64)) * torch.empty((), dtype=dt).element_size()
+        x = out[:, off:off + nbytes].contiguous().view(dt).reshape((ws, gmax) + tail)
+        merged[k] = x.transpose(0, 1).reshape((ws * gmax,) + tail)[:n_total]     # [k][rank] -> global id rank + k * world
+        off += nbytes
     return merged
 
 
-def store_games(Game, buffer, merged):
-    """train.collect_data's bookkeeping (train.py:69-75) for gathered games, in global order."""
+def trajectories_to_host(t):
+    """dict of tensors -> dict of NumPy arrays with the engine's dtypes (u64 words, u16 visits)."""
+    out = {k: v.detach().cpu().numpy() for k, v in t.items() if k in TRAJ_KEYS}
+    out["words"] = out["words"].view(np.uint64)
+    out["visits"] = out["visits"].view(np.uint16)
+    return out
+
+
+def store_games(Game, buffer, games):
+    """train.collect_data's bookkeeping (train.py:69-75) for games in global order."""
     from .train import save_data_to_buffer
     results = [0, 0, 0]
-    for _gid, (boards, actions, policies, qs, winner) in merged:
+    for boards, actions, policies, qs, winner in games:
         reward = 0 if winner == -1 else 1
         results[2 if winner == -1 else winner] += 1
         save_data_to_buffer(Game, buffer, (boards, actions, policies, qs, winner, reward))
     return results
 
 
-def collect_data_distributed(Game, model, buffer, iterations, mcts_iter, vl=1, dirichlet=True):
-    """train.collect_data over all ranks: this rank plays games rank, rank + world, ... on its GPU,
-    then all ranks exchange trajectories and fill identical buffers."""
-    from .train import play_games
-    ids = shard_games(iterations)
-    games, visits = play_games(Game, model, len(ids), mcts_iter, vl=vl, dirichlet=dirichlet, return_visits=True) if ids else ([], [])
-    merged = gather_games(Game, games, ids, visits)
-    return store_games(Game, buffer, merged)
+def collect_data_distributed(Game, model, buffer, iterations, mcts_iter, vl=1, dirichlet=True, seed=None, concurrent=None):
+    """train.collect_data over all ranks: this rank plays games rank, rank + world, ... on its GPU (device-side
+    self-play), all ranks exchange the compact trajectories over NCCL and fill identical buffers in global game order.
+    `seed` must be the same on every rank (default: drawn from rank 0's NumPy RNG and broadcast)."""
+    from .forest import game_spec
+    from .selfplay import play_games_device, games_from_arrays
+    rank, ws = world()
+    if seed is None:
+        s = torch.tensor([int(np.random.randint(0, 2 ** 31 - 1)), int(np.random.randint(0, 2 ** 31 - 1))], dtype=torch.int64,
+                         device="cuda" if ws > 1 and dist.get_backend() == "nccl" else "cpu")
+        if ws > 1:
+            dist.broadcast(s, 0)
+        seed = int(s[0].item()) * 2654435761 + int(s[1].item())
+    ids = shard_games(iterations, rank, ws)
+    g = game_spec(Game.name, Game.rows)
+    if ids:
+        sp = play_games_device(Game, model, len(ids), mcts_iter, vl=vl, dirichlet=dirichlet, concurrent=concurrent, seed=seed,
+                               id_first=rank, id_stride=ws, return_engine=True)
+        local = sp.device_tensors()
+    else:                                                               # more ranks than games
+        local, sp = empty_trajectories(g, 0, "cuda"), None
+    merged = gather_trajectories(local, iterations)
+    games = games_from_arrays(g, trajectories_to_host(merged))
+    if sp is not None:
+        sp.close()
+    return store_games(Game, buffer, games)
+
+
+def empty_trajectories(g, n, device="cpu"):
+    P, A = g.state_dim, g.action_dim
+    z = lambda shape, dt: torch.zeros(shape, dtype=dt, device=device)
+    return dict(plies=z((n,), torch.int32), winner=z((n,), torch.int32), first=z((n,), torch.int32), words=z((n, P, 2, g.nw), torch.int64),
+                visits=z((n, P, A), torch.int16), q=z((n, P), torch.float64), action=z((n, P), torch.int16))
 
 
 def broadcast_model(model, src=0):

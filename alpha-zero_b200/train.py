@@ -86,13 +86,30 @@ def _wins(Game, boards, movers, r, c):
     return won
 
 
-def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, return_visits=False, concurrent=None):
+def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, return_visits=False, concurrent=None, seed=None):
     """n_games self-play games, `concurrent` of them in flight at once on the GPU forest (default: all);
     a finished game's slot is refilled with the next game until n_games have been started.  Returns the
-    reference's 5-tuple per game in game order (and, on request, the raw root visit counts per ply --
-    the compact form parallel.pack_games ships between ranks).  Per ply the host does only batched NumPy
-    work: pi = visits / sum (utils.py:46-55), a move drawn from pi while ply < sample_until else the
-    most visited action (gomoku.py:143-147 / connect4.py:133), make_move, check_winner."""
+    reference's 5-tuple per game in game order (and, on request, the raw root visit counts per ply).
+
+    With a `Net` / `B200Net` / `HashEvaluator` the whole loop runs on the device (selfplay.SelfPlayEngine: move choice,
+    rules, refill and Dirichlet noise are kernels; the host reads one status word per ply).  Other callables (external
+    evaluators) and vanilla mode (model=None) use the batched host loop below, one NumPy step per ply."""
+    from .ai.mcts import HashEvaluator
+    from .ai.nn import Net, B200Net
+    if isinstance(model, (Net, B200Net, HashEvaluator)) and type(model).__name__ != "UCB1HashEvaluator":
+        from .selfplay import play_games_device, games_from_arrays
+        from .forest import game_spec
+        arr = play_games_device(Game, model, n_games, mcts_iter, vl=vl, dirichlet=dirichlet, concurrent=concurrent, seed=seed,
+                                return_arrays=True)
+        return games_from_arrays(game_spec(Game.name, Game.rows), arr, return_visits=return_visits)
+    return _play_games_host(Game, model, n_games, mcts_iter, vl, dirichlet, return_visits, concurrent)
+
+
+def _play_games_host(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, return_visits=False, concurrent=None):
+    """Host-driven variant: per ply batched NumPy work -- pi = visits / sum (utils.py:46-55), a move drawn from pi
+    while ply < sample_until (np.random.choice's inverse CDF, searchsorted side='right') else the most visited action,
+    make_move, check_winner.  Ties of the most visited action resolve to the lowest action index here (the reference
+    takes the first maximum in child order, which the device engine reproduces)."""
     C, R, W_, A = Game.feature_dim, Game.rows, Game.cols, Game.action_dim
     slots = min(n_games, concurrent or n_games)
     boards = np.zeros((slots, C, R, W_), np.float32)
@@ -103,9 +120,10 @@ def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, return_vis
     started = slots
     winners = np.full(n_games, -1, np.int64)
     log = dict(gid=[], snap=[], pi=[], vis=[], q=[], r=[], c=[])       # one entry per ply: arrays over the live games
-    sample_until = 8 if Game.name == "gomoku" else Game.state_dim + 1          # gomoku.py:143 / connect4.py:133
+    sample_until = (8 if Game.name == "gomoku" else Game.state_dim + 1) if model else 0    # gomoku.py:143 / connect4.py:133
     # Dirichlet noise of the NEXT ply is drawn by a helper thread while the GPU searches (small-alpha gamma
     # sampling is the most expensive host step); its generator is seeded from the global RNG, so runs repeat.
+    dirichlet = bool(dirichlet and model)                           # vanilla mode never mixes noise in (ai/mcts.py:42,52)
     noise_rng = np.random.default_rng(np.random.randint(0, 2 ** 31 - 1, size=4))
     pool = ThreadPoolExecutor(1) if dirichlet else None
     draw = (lambda: noise_rng.dirichlet([0.03] * A, size=slots)) if dirichlet else None
@@ -122,7 +140,9 @@ def play_games(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, return_vis
         u = np.random.random_sample(len(live))
         cdf = np.cumsum(pi, axis=1)
         cdf /= cdf[:, -1:]
-        drawn = np.minimum((cdf < u[:, None]).sum(axis=1), A - 1)
+        drawn = np.minimum((cdf <= u[:, None]).sum(axis=1), A - 1)          # searchsorted(cdf, u, side='right')
+        zero = visits[live][np.arange(len(live)), drawn] == 0              # u exactly on a CDF step: never an unvisited action
+        drawn = np.where(zero, np.argmax(visits[live], axis=1), drawn)
         acts = np.where(plies[live] < sample_until, drawn, np.argmax(visits[live], axis=1))   # ties: lowest action index
         snap = boards[live].copy()
         r, c = _moves_from_actions(Game, snap, acts)

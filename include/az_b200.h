@@ -98,9 +98,56 @@ AZ_API int az_forest_root_children(az_forest* f, int tree, int max_children, int
  * This is the log that replays a GPU search in the oracle (MCTS.cache preload, mcts.py:40-41). */
 AZ_API int az_forest_read_leaves(az_forest* f, int max_n, uint64_t* words_host, uint8_t* players_host,
                                  int32_t* trees_host, float* priors_host, float* values_host, void* stream);
-/* counters: [sims, terminal sims, expansions, children, selects, children scored, collisions, -] */
+/* counters: [sims, terminal sims, expansions, children, selects, children scored, collisions, cache hits] */
 AZ_API int az_forest_stats(az_forest* f, uint64_t* out8_host, int reset, void* stream);
 AZ_API int az_forest_info(az_forest* f, int* n_trees, int* action_dim, int* planes, int* nw, int* cap);
+
+/* ---- evaluation cache: replaces MCTS.cache (ai/mcts.py:7,37-51; cleared per model update, main.py:55-57) ------
+ * canonical position -> (softmax priors, value) in an open-addressed HBM table probed by the advance kernel: a leaf
+ * whose position is cached costs no evaluator row, leaves of different trees reaching the same new position in one
+ * step share one row, and at vl_batch == 1 a tree keeps simulating inside a launch while its leaves hit.  Transparent
+ * for a deterministic evaluator (search_stats[7] counts the hits).  On by default for boards of <= 64 cells
+ * (AZ_NO_CACHE=1 turns it off); log2_entries = 0 removes it.  Entries unused for 2 searches are recycled. */
+AZ_API int az_forest_cache_config(az_forest* f, int log2_entries);
+AZ_API int az_forest_cache_clear(az_forest* f, void* stream);
+AZ_API int az_forest_cache_info(az_forest* f, long long* entries, long long* bytes);
+/* Names the evaluator whose answers may be cached from now on (any id that changes with the evaluator or its weights);
+ * a different id drops the cached answers.  az_forest_search_{hash,net} do this themselves; step-by-step callers
+ * (az_forest_advance + an evaluator) call it before az_forest_begin_move when they switch evaluators. */
+AZ_API int az_forest_set_evaluator(az_forest* f, unsigned long long id, void* stream);
+
+/* ---- whole self-play games on the device: replaces the per-ply driver Game.self_play (games/gomoku.py:123-164,
+ *      connect4.py:117-151, tictactoe.py:99-133) and train.collect_data's game loop (train.py:54-83) -----------------
+ * The forest's trees are game SLOTS: after every search one kernel records the position (side bitboards, u16 root
+ * visit counts by action, f64 root Q), chooses the move -- np.random.choice over pi while ply < sample_plies
+ * (node.py:83-93: f64 cumsum, searchsorted side='right') else the first most-visited child in child order
+ * (node.py:76-81) --, applies it, tests win / draw, starts the next game in a finished slot and writes the next roots;
+ * Dirichlet(0.03) root noise (utils.py:21) is drawn on the device.  Randomness is Philox4x32-10 keyed by (seed; global
+ * game id, ply), global id of local game k = id_first + k * id_stride: trajectories do not depend on slot, GPU or rank
+ * count.  n_games may exceed the forest's trees (slots are refilled). */
+typedef struct az_selfplay az_selfplay;
+AZ_API int az_selfplay_create(az_forest* f, int n_games, int id_first, int id_stride, uint64_t seed, int sample_plies,
+                              int use_noise, az_selfplay** out);
+AZ_API void az_selfplay_destroy(az_selfplay* sp);
+/* adopt_roots = 0: every game starts from the empty board; 1: games 0..slots-1 continue from the forest's current roots. */
+AZ_API int az_selfplay_begin(az_selfplay* sp, int adopt_roots, void* stream);
+/* One ply by hand: az_selfplay_prepare (root noise), any az_forest_search_*, az_selfplay_move. */
+AZ_API int az_selfplay_prepare(az_selfplay* sp, void* stream);
+AZ_API int az_selfplay_move(az_selfplay* sp, void* stream);
+/* Synchronises: games started / finished, live slots, positions recorded in finished games. */
+AZ_API int az_selfplay_status(az_selfplay* sp, int* started, int* finished, int* live, long long* positions, void* stream);
+/* Plays until every game has finished or max_plies searches were run (0 = no limit); returns the searches run. */
+AZ_API int az_selfplay_run_net(az_selfplay* sp, az_net* net, int iters, int max_plies, void* stream);
+AZ_API int az_selfplay_run_hash(az_selfplay* sp, int iters, uint64_t seed, int qbits, int max_plies, void* stream);
+/* Trajectories, positions indexed [game][ply] with max_plies = rows*cols per game.  Device pointers (library-owned):
+ * out8 = {plies i32[G], winner i32[G] (0/1, -1 draw, -2 unfinished), words u64[G][P][2][nw], visits u16[G][P][A],
+ * q f64[G][P], action(cell) i16[G][P], uniform f64[G][P] (-1 = argmax ply), first recorded ply i32[G]}. */
+AZ_API int az_selfplay_buffers(az_selfplay* sp, void** out8, int* n_games, int* max_plies);
+/* Host copies (any pointer may be NULL).  Synchronous. */
+AZ_API int az_selfplay_read(az_selfplay* sp, int32_t* plies_host, int32_t* winner_host, int32_t* first_host, uint64_t* words_host,
+                            uint16_t* visits_host, double* q_host, int16_t* action_host, double* u_host, void* stream);
+AZ_API int az_selfplay_read_slots(az_selfplay* sp, int32_t* slot_game_host, double* noise_host, void* stream);
+AZ_API long long az_selfplay_launch_count(az_selfplay* sp);
 
 /* ---- batched rules for differential tests: games/*.py get_valid_moves / check_winner ---- */
 /* words_host uint64 [n][2][nw]; out_counts int32 [n]; out_cells uint8 [n][rows*cols]. */

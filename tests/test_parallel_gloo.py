@@ -1,8 +1,10 @@
 """The N > 1 path on CPU: world_size-2 `gloo` processes shard games, all-gather the compact
-trajectories and must end with IDENTICAL replay buffers, equal to the single-process buffer built
-in global game order; the gradient all-reduce of train.train keeps the replicas in lock step.
-(The searches themselves need a GPU; here every rank fabricates its games with random legal play
-through the host Game classes, which exercises pack / gather / unpack / augmentation end to end.)"""
+trajectory arrays (the layout of the device trajectory store, csrc/az_selfplay.cu) and must end with
+IDENTICAL replay buffers, equal to the single-process buffer built in global game order; the gradient
+all-reduce of train.train keeps the replicas in lock step.  (The searches themselves need a GPU; here
+every rank fabricates its games with random legal play through the host Game classes, which exercises
+gather / unpack / canonicalisation / augmentation end to end.  tests/test_gpu_selfplay.py runs the same
+exchange over NCCL on every visible GPU.)"""
 import os
 import socket
 import sys
@@ -44,6 +46,24 @@ def _fake_game(Game, gid, iters=50):
     return (boards, actions, policies, qs, winner), np.stack(visits)
 
 
+def _arrays_of(Game, fakes):
+    """Fabricated games -> the compact arrays of selfplay.SelfPlayEngine.trajectory_arrays."""
+    from alpha_zero_b200.forest import game_spec, planes_to_words
+    g = game_spec(Game.name, Game.rows)
+    n, P, A = len(fakes), g.state_dim, g.action_dim
+    arr = dict(plies=np.zeros(n, np.int32), winner=np.zeros(n, np.int32), first=np.zeros(n, np.int32),
+               words=np.zeros((n, P, 2, g.nw), np.uint64), visits=np.zeros((n, P, A), np.uint16), q=np.zeros((n, P)),
+               action=np.zeros((n, P), np.int16))
+    for k, ((boards, actions, _pol, qs, winner), vis) in enumerate(fakes):
+        p = len(boards)
+        arr["plies"][k], arr["winner"][k] = p, winner
+        arr["words"][k, :p] = planes_to_words(g, np.stack(boards))
+        arr["visits"][k, :p] = vis
+        arr["q"][k, :p] = qs
+        arr["action"][k, :p] = [r * g.cols + c for r, c in actions[1:]]
+    return g, arr
+
+
 def _buffer_digest(buffer):
     import hashlib
     h = hashlib.sha256()
@@ -65,11 +85,14 @@ def _worker(rank, world, port, game_name, n_games, out):
     G = {"gomoku": games.Gomoku, "connect4": games.Connect4}[game_name]
     ids = parallel.shard_games(n_games)
     assert ids == list(range(rank, n_games, world))
-    mine = [_fake_game(G, g) for g in ids]
-    merged = parallel.gather_games(G, [m[0] for m in mine], ids, [m[1] for m in mine])
-    assert [g for g, _ in merged] == list(range(n_games))
+    from alpha_zero_b200.selfplay import games_from_arrays
+    spec, local = _arrays_of(G, [_fake_game(G, g) for g in ids])
+    merged = parallel.trajectories_to_host(parallel.gather_trajectories(local, n_games))
+    _spec, whole = _arrays_of(G, [_fake_game(G, g) for g in range(n_games)])
+    for k in parallel.TRAJ_KEYS:                                     # global game order, whatever the rank count
+        assert np.array_equal(merged[k], whole[k]), k
     buf = ReplayBuffer(100000)
-    results = parallel.store_games(G, buf, merged)
+    results = parallel.store_games(G, buf, games_from_arrays(spec, merged))
     digest = _buffer_digest(buf)
     # gradient all-reduce: different samples per rank, identical parameters afterwards
     torch.manual_seed(7)
@@ -111,14 +134,16 @@ def test_two_ranks_build_identical_buffers(game_name, n_games):
     assert out[0][2] and out[1][2]                                  # replicas identical after all-reduced steps
 
 
-def test_pack_roundtrip_single_process():
-    from alpha_zero_b200 import games, parallel
+def test_arrays_roundtrip_single_process():
+    """compact arrays -> the reference's (boards, actions, policies, qs, winner) tuples, exactly."""
+    from alpha_zero_b200 import games
+    from alpha_zero_b200.selfplay import games_from_arrays
     for G in (games.Gomoku, games.Connect4, games.TicTacToe):
         mine = [_fake_game(G, g, iters=30) for g in range(3)]
-        blob = parallel.pack_games(G, [m[0] for m in mine], [4, 9, 2], [m[1] for m in mine])
-        back = parallel.unpack_games(G, blob)
-        assert [g for g, _ in back] == [4, 9, 2]
-        for (gid, (boards, actions, policies, qs, winner)), ((b0, a0, p0, q0, w0), _) in zip(back, mine):
+        spec, arr = _arrays_of(G, mine)
+        back, vis = games_from_arrays(spec, arr, return_visits=True)
+        for (boards, actions, policies, qs, winner), ((b0, a0, p0, q0, w0), v0), v in zip(back, mine, vis):
             assert winner == w0 and qs == q0 and [tuple(a) for a in a0] == actions
-            assert all(np.array_equal(x, y) for x, y in zip(boards, b0))
-            assert all(np.array_equal(x, y) for x, y in zip(policies, p0))
+            assert all(x.dtype == np.float32 and np.array_equal(x, y) for x, y in zip(boards, b0))
+            assert all(x.dtype == np.float64 and np.array_equal(x, y) for x, y in zip(policies, p0))
+            assert np.array_equal(v, v0)
