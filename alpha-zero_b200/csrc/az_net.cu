@@ -1209,7 +1209,7 @@ static cudaStream_t g_own_stream = nullptr;
 static int az_step_eager(az_net* n, az_forest* f, cudaStream_t s) {
     int rc = az_forest_advance(f, s);
     if (rc) return rc;
-    ++n->launches;                                          // the advance kernel
+    n->launches += az_forest_dev(f)->cache.cap ? 2 : 1;      // the advance kernel (+ the cache publish kernel in front of it)
     return az_net_eval_leaves(n, f, s);
 }
 

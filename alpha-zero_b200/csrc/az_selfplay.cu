@@ -315,6 +315,12 @@ extern "C" int az_selfplay_begin(az_selfplay* sp, int adopt_roots, void* stream)
     AzForestDev* fd = az_forest_dev(sp->f);
     cudaStream_t s = (cudaStream_t)stream;
     const int n = std::max(fd->n_trees, 1);
+    const size_t npos = (size_t)sp->d.n_games * sp->d.max_plies;   // unrecorded positions read as zeros
+    AZ_CUDA_OK(cudaMemsetAsync(sp->d.t_words, 0, npos * 2 * fd->g.nw * 8, s));
+    AZ_CUDA_OK(cudaMemsetAsync(sp->d.t_visits, 0, npos * fd->g.action_dim * 2, s));
+    AZ_CUDA_OK(cudaMemsetAsync(sp->d.t_q, 0, npos * 8, s));
+    AZ_CUDA_OK(cudaMemsetAsync(sp->d.t_action, 0, npos * 2, s));
+    AZ_CUDA_OK(cudaMemsetAsync(sp->d.t_u, 0, npos * 8, s));
     az_selfplay_begin_kernel<<<(n + 255) / 256, 256, 0, s>>>(*fd, sp->d, adopt_roots ? 1 : 0);
     AZ_CUDA_OK(cudaGetLastError());
     sp->launches += 1;

@@ -1,17 +1,23 @@
 #!/usr/bin/env python
-"""Benchmark of the self-play hot path (BASELINE.json: MCTS simulations/s).
+"""Benchmark of the self-play hot path (BASELINE.json: MCTS simulations/s and self-play games/s).
 
-A "step" is one move search for every concurrent game: n_trees x `iters` simulations of the
-reference's loop (ai/mcts.py:16) incl. the policy/value net on every leaf.  Default workload
-= BASELINE.json configs[1]: Connect4 6x7, 4096 concurrent games, 800 sims/move, virtual-loss
-batch 1 (the reference's sequential search), random-init main.py:134 net (D=512, patch 5,
-8 heads, depth 1).  `--workload gomoku` runs configs[2] (Gomoku 7x7, 8192 games, vl=8).
+A "step" is one move search for every concurrent game -- n_trees x `iters` simulations of the reference's loop
+(ai/mcts.py:16) incl. the policy/value net on every leaf that is not answered by the evaluation cache -- followed by
+the device-side move (csrc/az_selfplay.cu).  Successive steps are successive plies of the SAME games (slots of
+finished games are refilled), which is what self-play is and what lets the evaluation cache (MCTS.cache) see the
+cross-move reuse the reference gets.  Default workload = BASELINE.json configs[1]: Connect4 6x7, 4096 concurrent
+games, 800 sims/move, virtual-loss batch 1 (the reference's sequential search), random-init main.py:134 net (D=512,
+patch 5, 8 heads, depth 1), games starting from synthetic positions of 0..7 random plies.  configs[2] (Gomoku 7x7,
+8192 games, vl = 8) is measured in the same run and reported under `workloads.gomoku`.
 
-  value  device-timed (CUDA events on the launching stream), root positions already in HBM
-  e2e    wall clock through the C ABI with HOST buffers: pinned float32 root planes in,
-         visit counts + root Q out, every step
-  --impl reference   the reference's CPU implementation of the same path (the oracle port of
-         its single-threaded Python search + batch-1 torch net), one process per host core.
+  value     device-timed (CUDA events on the launching stream), everything resident in HBM
+  e2e       wall clock through the public API with HOST buffers, every step: pinned float32 root planes + noise in,
+            visit counts + root Q out, the move applied by the caller on the host (what a user of MCTS.mcts_batch does)
+  selfplay  whole games from the empty board to the end on every rank + the NCCL all-gather of the trajectories inside
+            the timed region: games/s at N GPUs
+  --impl reference   the reference's CPU implementation of the same path on the host cores (oracle/cpu_baseline.py):
+            the oracle port for Connect4 (the reference cannot run it with a network), the UNMODIFIED reference from
+            baseline/_ref for Gomoku; 1-process and P-process figures.
 
 Prints ONE JSON line on rank 0.
 """
@@ -38,42 +44,68 @@ NET = dict(dim=512, depth=1, patch=5, heads=8)          # main.py:134
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=4)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=250, help="timed steps (plies); the default gives a >= 20 s timed region")
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="connect4", choices=sorted(WORKLOADS))
     ap.add_argument("--trees", type=int, default=0)
     ap.add_argument("--iters", type=int, default=0)
     ap.add_argument("--vl", type=int, default=0)
-    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--min-seconds", type=float, default=0.0, help="keep stepping until the timed region is at least this long")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the e2e leg (default min(steps, 48))")
+    ap.add_argument("--cpu-seconds", type=float, default=0.0, help="per CPU figure (default 15 in the b200 arm, 30 in the reference arm)")
     ap.add_argument("--cpu-procs", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-selfplay", action="store_true", help="skip the whole-game self-play leg (games/s)")
+    ap.add_argument("--no-second-workload", action="store_true", help="skip the workloads.<other> sub-record")
+    ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--no-cache", action="store_true", help="evaluation cache off (A/B)")
+    ap.add_argument("--selfplay-generations", type=float, default=2.0, help="whole games per slot in the self-play leg")
     return ap.parse_args()
 
 
-# ---- CPU baseline (oracle port, subprocess workers; the only place bench.py runs oracle/) ----
-def run_cpu_baseline(wl, seconds, procs):
+# ---- CPU baseline (subprocess workers; the only place bench.py runs oracle/) -------------------------------
+def have_ref():
+    return os.path.isdir(os.path.join(ROOT, "baseline", "_ref", "games"))
+
+
+def run_cpu_baseline(wl, seconds, procs, kind="auto"):
+    """P single-thread worker processes side by side.  kind: 'reference' (unmodified reference from baseline/_ref,
+    Gomoku 7x7 only), 'port' (oracle port), 'auto' = reference where it can run."""
     ncpu = os.cpu_count() or 1
     procs = procs or min(ncpu, 32)
-    cmd = [sys.executable, os.path.join(ROOT, "oracle", "cpu_baseline.py"), "--game", wl["game"], "--rows", str(wl["rows"]),
+    if kind == "auto":
+        kind = "reference" if (wl["game"] == "gomoku" and wl["rows"] == 7 and have_ref()) else "port"
+    cmd = [sys.executable, os.path.join(ROOT, "oracle", "cpu_baseline.py"), "--kind", kind, "--game", wl["game"], "--rows", str(wl["rows"]),
            "--dim", str(NET["dim"]), "--depth", str(NET["depth"]), "--patch", str(NET["patch"]), "--heads", str(NET["heads"]),
            "--iters", str(wl["iters"]), "--seconds", str(seconds)]
     env = dict(os.environ, OMP_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
     t0 = time.time()
-    ps = [subprocess.Popen(cmd + ["--seed", str(i)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, env=env, text=True)
+    ps = [subprocess.Popen(cmd + ["--seed", str(i)], stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env, text=True)
           for i in range(procs)]
-    rate, sims = 0.0, 0
+    rate, sims, hits, ok, err = 0.0, 0, [], 0, ""
     for p in ps:
-        out = p.communicate()[0].strip().splitlines()
+        so, se = p.communicate()
+        out = so.strip().splitlines()
         if p.returncode == 0 and out:
             r = json.loads(out[-1])
             rate += r["sims"] / r["seconds"]
             sims += r["sims"]
-    return dict(value=rate, unit="simulations/s", cores=procs, kind="port",
-                sample=f"{procs} single-thread processes x {seconds:.0f}s of the same search (oracle port of ai/mcts.py "
-                       f"+ batch-1 torch Net on CPU, {wl['iters']} sims/move, Dirichlet on); {sims} sims total; "
-                       f"host has {ncpu} logical cores", wall_s=time.time() - t0)
+            hits.append(r.get("cache_hit_rate", 0.0))
+            ok += 1
+        else:
+            err = (se or "").strip().splitlines()[-1:] or [""]
+            err = err[0][:200]
+    what = ("the UNMODIFIED reference (baseline/_ref: Gomoku().self_play with its own Net, MCTS.cache on, counted by MCTS.mcts_count)"
+            if kind == "reference" else
+            "the oracle port of ai/mcts.py (per-node Python objects, batch-1 torch Net on CPU, MCTS.cache analogue)")
+    d = dict(value=rate, unit="simulations/s", cores=ok, kind=kind,
+             sample=f"{ok} single-thread processes x {seconds:.0f}s of whole self-play games, {what}, {wl['game']} {wl['iters']} sims/move, "
+                    f"Dirichlet on; {sims} sims total; host has {ncpu} logical cores",
+             cache_hit_rate=(sum(hits) / len(hits)) if hits else None, wall_s=time.time() - t0)
+    if ok < procs:
+        d["worker_errors"] = f"{procs - ok} of {procs} workers failed: {err}"
+    return d
 
 
 # ---- clocks ---------------------------------------------------------------------------------
@@ -111,9 +143,11 @@ def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
             p = json.load(f)
-        return dict(tflops=p["bf16_tflops_sustained"], hbm=p["hbm_gbs"], src="measured (MEASURED_PEAKS.json, sustained bf16)")
+        return dict(tflops=p["bf16_tflops_sustained"], hbm=p["hbm_gbs"], src_tensor="measured (MEASURED_PEAKS.json, sustained bf16: kernels timed inside a long step)",
+                    src_hbm="measured (MEASURED_PEAKS.json, HBM copy bandwidth)")
     except Exception:
-        return dict(tflops=1400.0, hbm=6650.0, src="fallback (B200_PROFILING.md: ~1.4 PF sustained, 6.65 TB/s)")
+        return dict(tflops=1400.0, hbm=6650.0, src_tensor="fallback (B200_PROFILING.md: ~1.4 PFLOP/s sustained bf16)",
+                    src_hbm="fallback (B200_PROFILING.md: 6.65 TB/s)")
 
 
 def ncu_traffic(kind, wl):
@@ -128,22 +162,23 @@ def ncu_traffic(kind, wl):
 
 
 def roofline(wl, r, prof, pk, kind=None):
-    """Roofline entry of one kernel kind (default: the kind with the largest share of the step).
-    Algorithmic work per launch = per-leaf (or per-simulation) figure of DESIGN.md section 4 x the units of
-    one launch; duration = CUDA-event average over the profiled launches."""
+    """Roofline entry of one kernel kind (default: the kind with the largest SHARE of the step; the three cls-row GEMM
+    launches form one kind).  Algorithmic work per launch = per-leaf (or per-simulation) figure of DESIGN.md section 4 x
+    the units of one launch; duration = CUDA-event average over the profiled launches."""
     G = game_class(wl)
     D, H, P = NET["dim"], NET["heads"], NET["patch"]
     T = G.rows * G.cols + 1
     kused = G.feature_dim * P * P + T
     leaves = r["leaves_per_step"]
-    per_step = {k: v["ms"] * (v["launches"] / max(prof["forest_advance"]["launches"], 1) if k != "forest_advance" else 1.0)
-                for k, v in prof.items()}
-    if kind is None:                # dominant KERNEL: longest single launch (the three cls-row GEMMs are separate kernels)
-        kind = max(prof, key=lambda k: prof[k]["ms"])
+    adv_n = max(prof["forest_advance"]["launches"], 1)
+    per_step = {k: v["ms"] * (v["launches"] / adv_n if k != "forest_advance" else 1.0) for k, v in prof.items()}
+    if kind is None:
+        kind = max(per_step, key=lambda k: per_step[k])
     ms = prof[kind]["ms"]
     traffic = ncu_traffic(kind, wl)
     st = r["stats"]
-    flops = None
+    share = per_step[kind] / sum(per_step.values())
+    flops, ref_flops = None, None
     front2 = bool(r.get("path_flags", 0) & 2)
     if kind == "front_fused" and front2:   # statistics (H scores + K Cholesky columns) per token + U = A^T w: H columns per token
         flops, name = 2.0 * leaves * T * kused * (H + kused + H), "az_front2_kernel (embedding+LN1+score projection+cls softmax+U=A^T w, tcgen05)"
@@ -154,20 +189,28 @@ def roofline(wl, r, prof, pk, kind=None):
     elif kind == "gemm_cls_rows":   # out_proj D*D (D x H*128 after the front-kernel reassociation), mlp D*4D, 4D*D over 3 launches -> average launch
         kout = H * 128 if front2 else D
         flops, name = 2.0 * leaves * (kout * D + 8 * D * D) / 3.0, "az_gemm_kernel (cls-row out_proj / MLP GEMMs, tcgen05; average of the 3 launches)"
+        ref_flops = 2.0 * leaves * (D * D + 8 * D * D) / 3.0          # the reference's graph: out-proj over K = D
     elif kind == "embed_ln":
         flops, name = 2.0 * leaves * T * 128 * D, "az_embed_mma_kernel (im2col embedding + LN, tcgen05)"
     if flops is not None:
         ach = flops / (ms / 1e3) / 1e12
-        return dict(kernel=name, bound="tensor", achieved=ach, peak=pk["tflops"], unit="TFLOP/s", frac=ach / pk["tflops"],
-                    traffic=traffic, peak_source=pk["src"], flops_per_launch=flops, ms_per_launch=ms, share_of_step=per_step[kind] / sum(per_step.values()))
+        d = dict(kernel=name, bound="tensor", achieved=ach, peak=pk["tflops"], unit="TFLOP/s", frac=ach / pk["tflops"],
+                 traffic=traffic, peak_source=pk["src_tensor"], flops_per_launch=flops, ms_per_launch=ms, share_of_step=share,
+                 rows_per_launch=leaves)
+        if ref_flops is not None:
+            d["reference_graph"] = dict(flops_per_launch=ref_flops, achieved=ref_flops / (ms / 1e3) / 1e12,
+                                        frac=ref_flops / (ms / 1e3) / 1e12 / pk["tflops"],
+                                        note="out-proj counted over K = D as in ai/nn.py; the executed graph contracts over K = heads*128")
+        return d
     if kind == "forest_advance":    # 16 B per child scored + 8 B header per select + 24 B RMW per path node + 26 B per child written
         sims = max(st["sims"], 1)
         per_sim = (16.0 * st["child_reads"] + 8.0 * st["selects"] + 24.0 * (st["selects"] + st["sims"]) + 26.0 * st["children"]) / sims
-        nbytes = per_sim * wl["trees"] * wl["vl"]
+        sims_per_launch = r.get("sims_per_advance", wl["trees"] * wl["vl"])
+        nbytes = per_sim * sims_per_launch
         ach = nbytes / (ms / 1e3) / 1e9
-        return dict(kernel="az_advance_kernel (PUCT select + expand + backup, one warp per tree)", bound="hbm", achieved=ach, peak=pk["hbm"],
-                    unit="GB/s", frac=ach / pk["hbm"], traffic=traffic, peak_source=pk["src"], bytes_per_sim=per_sim, bytes_per_launch=nbytes,
-                    ms_per_launch=ms, share_of_step=per_step[kind] / sum(per_step.values()))
+        return dict(kernel="az_advance_kernel (PUCT select + expand + backup + cache probe, one warp per tree)", bound="hbm", achieved=ach,
+                    peak=pk["hbm"], unit="GB/s", frac=ach / pk["hbm"], traffic=traffic, peak_source=pk["src_hbm"], bytes_per_sim=per_sim,
+                    sims_per_launch=sims_per_launch, bytes_per_launch=nbytes, ms_per_launch=ms, share_of_step=share)
     return None
 
 
@@ -180,32 +223,49 @@ def game_class(wl):
     return G
 
 
-def run_b200(args, wl, rank, world):
+def host_ply(G, az_train, np, boards, players, plies, visits):
+    """What a caller of MCTS.mcts_batch does between two searches (e2e leg): the most visited action per game, make_move,
+    check_winner; finished games restart from the empty board.  Vectorised NumPy (train._moves_from_actions / _wins)."""
+    acts = np.argmax(visits, axis=1)
+    r, c = az_train._moves_from_actions(G, boards, acts)
+    idx = np.arange(len(acts))
+    movers = players.astype(np.int64)
+    boards[idx, movers, r, c] = 1
+    if G.feature_dim == 3:
+        boards[:, 2] = (1 - movers)[:, None, None]
+    players[:] = 1 - movers
+    plies += 1
+    over = az_train._wins(G, boards, movers, r, c) | (plies == G.state_dim)
+    boards[over] = 0
+    players[over] = 0
+    plies[over] = 0
+    return int(over.sum())
+
+
+def run_workload(args, wl, rank, world, steps, warmup, full):
+    """All legs of one workload on this rank.  full: also e2e bookkeeping details, profile pass (rank 0), clocks."""
     import numpy as np
     import torch
     import torch.distributed as dist
     import alpha_zero_b200 as az
+    from alpha_zero_b200 import parallel, train as az_train
     from alpha_zero_b200.ai.nn import Net, B200Net
+    from alpha_zero_b200.selfplay import SelfPlayEngine, reference_sample_plies
     from alpha_zero_b200.synth import random_roots
 
     local = int(os.environ.get("LOCAL_RANK", 0))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     G = game_class(wl)
     n, iters, vl = wl["trees"], wl["iters"], wl["vl"]
-    A, T = G.action_dim, G.rows * G.cols + 1
+    A = G.action_dim
     torch.manual_seed(0)                                              # identical random-init weights on every rank
     model = Net((G.rows, G.cols), NET["patch"], NET["dim"], A, NET["heads"], NET["depth"], G.feature_dim, dropout=0.1).eval()
     stream = torch.cuda.Stream()
     eng = B200Net(model, max_batch=n * vl)
     forest = az.Forest(az.game_spec(wl["game"], wl["rows"]), n, iters, vl=vl, stream=stream.cuda_stream)
-    rng = np.random.default_rng(1234 + rank)                          # Philox-free: host NumPy, per-rank stream
-    total = args.warmup + args.steps
-    roots = [random_roots(G, n, wl["max_plies"], rng) for _ in range(total)]
-    noise = [rng.dirichlet([0.03] * A, size=n) for _ in range(total)]
-    pinned = torch.empty((n, G.feature_dim, G.rows, G.cols), dtype=torch.float32).pin_memory()
-    pin_np = pinned.numpy()
+    if args.no_cache:
+        forest.cache_config(0)
+    rng = np.random.default_rng(1234 + rank)
+    sample_plies = reference_sample_plies(G, True)
 
     def barrier():
         torch.cuda.synchronize()
@@ -213,74 +273,147 @@ def run_b200(args, wl, rank, world):
             dist.barrier()
             torch.cuda.synchronize()
 
-    e2e_parts = []
+    def max_over_ranks(*vals):
+        if world == 1:
+            return list(vals)
+        tm = torch.tensor(vals, device="cuda", dtype=torch.float64)
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        return tm.tolist()
 
-    def one_step(i, e2e):
-        planes, players, mcs = roots[i]
+    out = dict(workload=wl["name"], cache=forest.cache_info())
+    clocks = ClockSampler(local) if full else None
+    # ---- value: device time, everything resident; successive plies of device-side self-play ----------------
+    total = warmup + steps
+    planes, players, mcs = random_roots(G, n, wl["max_plies"], rng)
+    forest.set_roots_planes(planes, players, mcs)                     # upload BEFORE the timed region
+    n_games = int(n * min(64, 2 + total // 5))                        # enough games to refill every finished slot
+    sp = SelfPlayEngine(forest, n_games, 1234, sample_plies, noise=True, id_first=rank, id_stride=world)
+    sp.begin(adopt_roots=True)
+    ev, launches0, t_clock0 = [], 0, time.time()
+    i = 0
+    while True:
+        if i == warmup:
+            barrier()
+            forest.stats(reset=True)
+            t_clock0 = time.time()
+            launches0 = eng.launch_count() + sp.launch_count()
+        timed = i >= warmup
+        if timed:
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+        sp.prepare()                                                  # Dirichlet noise of the new roots (device)
+        forest.search_net(eng, iters)                                 # n x iters simulations
+        sp.move()                                                     # record, choose, apply, refill (device)
+        if timed:
+            b.record(stream)
+            ev.append((a, b))
+        i += 1
+        if i >= total:
+            if args.min_seconds <= 0:
+                break
+            torch.cuda.synchronize()
+            if sum(x.elapsed_time(y) for x, y in ev) >= args.min_seconds * 1e3 or i >= 64 * total:
+                break
+    barrier()
+    steps_timed = len(ev)
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    gpu_launches = eng.launch_count() + sp.launch_count() - launches0 + steps_timed     # + begin_move kernels
+    stats = forest.stats(reset=True)
+    st = sp.status()
+    assert st["live"] == n, f"self-play ran out of games ({st})"
+    assert stats["sims"] == n * iters * steps_timed, (stats["sims"], n * iters * steps_timed)
+    sp.close()
+    dev_ms, = max_over_ranks(dev_ms)
+    out.update(dev_ms=dev_ms, steps=steps_timed, sims_per_step=n * iters * world, gpu_launches=int(gpu_launches), stats=stats,
+               games_finished_in_value_leg=st["finished"])
+    # ---- e2e: wall clock through the public API with host buffers --------------------------------------------
+    e2e_steps = args.e2e_steps or min(steps, 48)
+    pinned = torch.empty((n, G.feature_dim, G.rows, G.cols), dtype=torch.float32).pin_memory()
+    boards = pinned.numpy()                                           # the caller's boards live in pinned host memory
+    np.copyto(boards, planes)
+    pl, mc = players.astype(np.int32).copy(), mcs.astype(np.int32).copy()
+    noise = [rng.dirichlet([0.03] * A, size=n) for _ in range(4)]
+    forest.set_active(None)
+    parts = []
+
+    def e2e_step(k):
         ta = time.perf_counter()
-        if e2e:
-            np.copyto(pin_np, planes)                                 # the step's inputs start in pinned host memory
-            forest.set_roots_planes(pin_np, players, mcs)             # H2D inside the timed region
-        forest.set_noise(noise[i])
+        forest.set_roots_planes(boards, pl, mc)                       # H2D inside the timed region
+        forest.set_noise(noise[k % 4])                                # H2D
         tb = time.perf_counter()
         forest.search_net(eng, iters)
         tc = time.perf_counter()
-        if e2e:
-            out = forest.root_visits()                                # D2H of the step's result
-            e2e_parts.append((round((tb - ta) * 1e3, 2), round((tc - tb) * 1e3, 2), round((time.perf_counter() - tc) * 1e3, 2)))
-            return out
-
-    clocks = ClockSampler(local)
-    # ---- value: device time, inputs resident --------------------------------------------------
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    launches0 = 0
-    for i in range(total):
-        planes, players, mcs = roots[i]
-        forest.set_roots_planes(planes, players, mcs)                 # upload BEFORE the timed region
-        forest.set_noise(noise[i])
-        if i == args.warmup:
-            barrier()
-            t_clock0 = time.time()
-            launches0 = eng.launch_count()
-        torch.cuda.synchronize()
-        if i >= args.warmup:
-            ev[i - args.warmup][0].record(stream)
-        forest.search_net(eng, iters)
-        if i >= args.warmup:
-            ev[i - args.warmup][1].record(stream)
+        visits, _q = forest.root_visits()                             # D2H of the step's result
+        td = time.perf_counter()
+        host_ply(G, az_train, np, boards, pl, mc, visits)
+        parts.append((tb - ta, tc - tb, td - tc, time.perf_counter() - td))
+        return visits
+    for k in range(min(warmup, 3)):
+        e2e_step(k)
     barrier()
-    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
-    gpu_launches = eng.launch_count() - launches0 + args.steps        # + begin_move kernels
-    stats = forest.stats(reset=True)
-    # ---- e2e: wall clock through the public API with host buffers ------------------------------
-    for i in range(args.warmup):
-        one_step(i, True)
-    barrier()
+    parts.clear()
     t0 = time.perf_counter()
-    for i in range(args.warmup, total):
-        visits, q = one_step(i, True)
+    for k in range(e2e_steps):
+        visits = e2e_step(k)
     barrier()
     e2e_s = time.perf_counter() - t0
-    t_clock1 = time.time()
     assert int(visits.sum()) == n * (iters - 1), "every tree must have completed its simulations"
-    if world > 1:
-        tm = torch.tensor([dev_ms, e2e_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(tm, op=dist.ReduceOp.MAX)                      # max over ranks
-        dev_ms, e2e_s = tm.tolist()
-    sims_per_step = n * iters * world
-    out = dict(dev_ms=dev_ms, e2e_s=e2e_s, sims_per_step=sims_per_step, gpu_launches=int(gpu_launches),
-               h2d=int(pinned.numel() * 4 + n * 8 + n * A * 8), d2h=int(n * A * 4 + n * 8), stats=stats,
-               e2e_steps_ms=[dict(upload=a, search=b, readback=c) for a, b, c in e2e_parts[args.warmup:]])
-    # ---- per-kernel profile (rank 0): eager steps of one search with CUDA events ------------------
-    if rank == 0:
-        planes, players, mcs = roots[-1]
+    e2e_s, = max_over_ranks(e2e_s)
+    t_clock1 = time.time()
+    med = lambda xs: sorted(xs)[len(xs) // 2] * 1e3
+    out.update(e2e_s=e2e_s, e2e_steps=e2e_steps, h2d=int(pinned.numel() * 4 + n * 8 + n * A * 8), d2h=int(n * A * 4 + n * 8),
+               e2e_step_ms=dict(upload=round(med([p[0] for p in parts]), 3), search=round(med([p[1] for p in parts]), 3),
+                                readback=round(med([p[2] for p in parts]), 3), host_move=round(med([p[3] for p in parts]), 3)),
+               e2e_stats=forest.stats(reset=True))
+    if clocks:
+        out["clocks"] = clocks.summary(t_clock0, t_clock1)
+    # ---- whole games on every rank + the NCCL all-gather of the trajectories inside the timed region ---------
+    if not args.no_selfplay:
+        per_rank = max(int(n * args.selfplay_generations), 1)
+        games_total = per_rank * world
+        sp2 = SelfPlayEngine(forest, per_rank, 4321, sample_plies, noise=True, id_first=rank, id_stride=world)
+        forest.stats(reset=True)
+        barrier()
+        t0 = time.perf_counter()
+        sp2.begin()
+        searches = sp2.run(eng, iters)                                # device-side self-play until every game is over
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        merged = parallel.gather_trajectories(sp2.device_tensors(), games_total)     # one all_gather_into_tensor (NCCL)
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
+        barrier()
+        t3 = time.perf_counter()
+        positions = int(merged["plies"].sum().item()) if world > 1 else sp2.status()["positions"]
+        assert int((merged["winner"] == -2).sum().item()) == 0, "every gathered game must be finished"
+        st2 = forest.stats(reset=True)
+        play_s, gather_s, total_s = max_over_ranks(t1 - t0, t2 - t1, t3 - t0)
+        out["selfplay"] = dict(games=games_total, games_per_rank=per_rank, concurrent_per_gpu=n, positions=positions, searches_per_rank=searches,
+                               seconds=total_s, play_seconds=play_s, gather_seconds=gather_s, gather_share=gather_s / total_s,
+                               gather_bytes_per_rank=int(sum(v.numel() * v.element_size() for k, v in merged.items()) // world),
+                               games_per_s=games_total / total_s, positions_per_s=positions / total_s,
+                               simulations_per_s=positions * iters / total_s, sims_per_move=iters,
+                               cache_hit_rate=st2["cache_hits"] / max(st2["expansions"], 1),
+                               evaluator_rows_per_sim=(st2["expansions"] - st2["cache_hits"]) / max(st2["sims"], 1),
+                               how="selfplay.SelfPlayEngine: every game from the empty board to its end on the device (Dirichlet noise, "
+                                   "moves sampled / first-max as the reference, slots refilled until all games have started, so the batch "
+                                   "thins out only at the end), then parallel.gather_trajectories: one all_gather_into_tensor of the compact "
+                                   "trajectories; max over ranks")
+        del merged
+        sp2.close()
+    # ---- per-kernel profile (rank 0): eager steps of one search with CUDA events ------------------------------
+    if rank == 0 and full and not args.no_profile:
+        planes, players, mcs = random_roots(G, n, wl["max_plies"], rng)
+        forest.set_active(None)
         forest.set_roots_planes(planes, players, mcs)
+        forest.set_noise(None)
+        forest.stats(reset=True)
         forest.begin_move(iters)
         adv, lv, per_step = [], [], {}
         eng.profile(True)
         eng.profile(False)                                            # zero the totals, timing off
         prev = {}
-        for s in range(iters // vl + 1 if vl > 1 else iters):         # the whole search, every 8th step timed
+        for s in range(2 * iters):                                    # the whole search, every 8th step timed
             timed = s % 8 == 4
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             eng.profile_on(timed)
@@ -290,45 +423,72 @@ def run_b200(args, wl, rank, world):
             eng.eval_leaves(forest, stream.cuda_stream)
             if timed:
                 adv.append((a, b))
-                lv.append(forest.counts()[0])
+                nl, nd = forest.counts()
+                lv.append(nl)
                 cur = eng.profile_read()                              # per-step deltas: steps beyond 3x the median are dropped,
                 for k, (ms, cnt) in cur.items():                      # so one preempted launch cannot skew a kernel's figure
                     pms, pcnt = prev.get(k, (0.0, 0))
                     if cnt > pcnt:
                         per_step.setdefault(k, []).append(((ms - pms) / (cnt - pcnt), cnt - pcnt))
                 prev = cur
+                if nd >= n:
+                    break
         eng.profile(False)
-        leaves = sum(lv) / max(len(lv), 1)
+        n_adv = s + 1
 
         def robust_mean(xs):                                          # mean over the steps within 3x the median
             m = sorted(xs)[len(xs) // 2]
             keep = [x for x in xs if x <= 3.0 * m]
             return sum(keep) / len(keep)
+        pst = forest.stats(reset=True)
         out["profile"] = {k: dict(ms=robust_mean([m for m, _ in v]), launches=sum(c for _, c in v)) for k, v in per_step.items()}
         out["profile"]["forest_advance"] = dict(ms=robust_mean([a.elapsed_time(b) for a, b in adv]), launches=len(adv))
-        out["leaves_per_step"] = leaves
+        out["leaves_per_step"] = sum(lv) / max(len(lv), 1)
+        out["sims_per_advance"] = pst["sims"] / max(n_adv, 1)
+        out["profile_stats"] = pst
         out["proj_width"] = eng.proj_width()
         out["path_flags"] = eng.path_flags()
-    out["clocks"] = clocks.summary(t_clock0, t_clock1)
     forest.close()
     eng.close()
-    # ---- whole games through the public API (train.play_games): games/s, SURVEY 8d ------------------
-    if rank == 0 and world == 1 and not args.no_selfplay:
-        from alpha_zero_b200 import train as az_train
-        np.random.seed(4321)
-        az_train.play_games(G, model, min(n, 256), min(iters, 32), vl=vl, concurrent=min(n, 256))   # warm-up: engine + forest of the small size
-        t0 = time.perf_counter()
-        games = az_train.play_games(G, model, 2 * n, iters, vl=vl, dirichlet=True, concurrent=n)
-        dt = time.perf_counter() - t0
-        plies = sum(len(g[0]) for g in games)
-        out["selfplay"] = dict(games=len(games), plies=plies, seconds=dt, games_per_s=len(games) / dt, positions_per_s=plies / dt,
-                               simulations_per_s=plies * iters / dt, sims_per_move=iters, concurrent=n,
-                               how="train.play_games: every game from the empty board to its end, Dirichlet noise on, moves "
-                                   "sampled / argmax as the reference; 2 x concurrent games, a finished game's slot is refilled until all have "
-                                   "started (the batch thins out only at the end)")
-    if world > 1:
-        dist.destroy_process_group()
     return out
+
+
+def summarize(args, wl, r, world, pk):
+    """JSON fields of one workload from run_workload's raw numbers."""
+    value = r["sims_per_step"] * r["steps"] / (r["dev_ms"] / 1e3)
+    e2e = r["sims_per_step"] * r["e2e_steps"] / r["e2e_s"]
+    st, es = r["stats"], r["e2e_stats"]
+    d = dict(workload=wl["name"], value=value, unit="simulations/s", ms_per_step=r["dev_ms"] / r["steps"], steps=r["steps"],
+             e2e=dict(value=e2e, unit="simulations/s", h2d_bytes_per_step=r["h2d"], d2h_bytes_per_step=r["d2h"], steps=r["e2e_steps"],
+                      step_ms_median=r["e2e_step_ms"], cache_hit_rate=es["cache_hits"] / max(es["expansions"], 1)),
+             gpu_launches=r["gpu_launches"], search_stats=st,
+             eval_cache=dict(entries=r["cache"]["entries"], bytes=r["cache"]["bytes"], hit_rate=st["cache_hits"] / max(st["expansions"], 1),
+                             evaluator_rows_per_sim=(st["expansions"] - st["cache_hits"]) / max(st["sims"], 1),
+                             note="MCTS.cache analogue (ai/mcts.py:37-51): hits = leaves answered without an evaluator row"))
+    if "clocks" in r:
+        d["clocks"] = r["clocks"]
+    if "selfplay" in r:
+        d["selfplay"] = r["selfplay"]
+    prof = r.get("profile", {})
+    if prof:
+        rr = dict(r, stats=r["profile_stats"])
+        d["kernel_ms"] = {k: round(v["ms"], 4) for k, v in prof.items()}
+        d["roofline"] = roofline(wl, rr, prof, pk)
+        d["rooflines_all"] = {k: rl for k, rl in ((k, roofline(wl, rr, prof, pk, k)) for k in prof) if rl}
+        pf = r.get("path_flags", 0)
+        d["evaluator_path"] = dict(flags=pf, front_kernel="az_front2_kernel" if pf & 2 else ("az_front_kernel" if pf & 1 else "generic"),
+                                   cls_row_gemm="cta_pair" if pf & 4 else "single_cta", layernorm_fold=bool(pf & 8), head_epilogue=bool(pf & 16))
+    return d
+
+
+def config_of(wl, world):
+    return dict(workload=wl["name"], game=wl["game"], board=f"{wl['rows']}x{7 if wl['game'] == 'connect4' else wl['rows']}",
+                concurrent_games_per_gpu=wl["trees"], sims_per_move=wl["iters"], vl_batch=wl["vl"],
+                net="Net(D=512,patch=5,heads=8,depth=1) random-init, ai/nn.py / main.py:134",
+                steps="successive plies of device-side self-play: games start from synthetic positions of 0..max_plies random plies, "
+                      "finished games restart from the empty board; Dirichlet noise on, moves sampled / first-max as the reference",
+                l2="inputs larger than L2: forest node pools + activations >> 126 MB, every step searches new root positions",
+                parallelism=f"dp{world} (games sharded per GPU; no collective inside a search; selfplay leg: one NCCL all-gather of trajectories)")
 
 
 def main():
@@ -339,47 +499,52 @@ def main():
             wl[k] = getattr(args, k)
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
-    config = dict(workload=wl["name"], game=wl["game"], board=f"{wl['rows']}x{7 if wl['game'] == 'connect4' else wl['rows']}",
-                  concurrent_games_per_gpu=wl["trees"], sims_per_move=wl["iters"], vl_batch=wl["vl"],
-                  net="Net(D=512,patch=5,heads=8,depth=1) random-init, ai/nn.py / main.py:134",
-                  l2="inputs larger than L2: forest node pools + activations >> 126 MB, fresh root positions every step",
-                  parallelism=f"dp{world} (games sharded per GPU, no data-path collective)")
+    other = None if args.no_second_workload else dict(WORKLOADS["gomoku" if wl["game"] == "connect4" else "connect4"])
     base = dict(metric="mcts_simulations_per_second", unit="simulations/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
-                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16", data="synthetic", config=config)
+                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16", data="synthetic", config=config_of(wl, world))
 
     if args.impl == "reference":
         if rank != 0:
             return
-        cb = run_cpu_baseline(wl, args.cpu_seconds, args.cpu_procs or min(os.cpu_count() or 1, 64))
-        line = dict(base, impl="reference", value=cb["value"], ms_per_step=wl["trees"] * wl["iters"] * world / max(cb["value"], 1e-9) * 1e3,
-                    cpu_baseline=cb, e2e=dict(value=cb["value"], unit="simulations/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
-                    gpu_launches=0)
+        secs = args.cpu_seconds or 30.0
+        procs = args.cpu_procs or min(os.cpu_count() or 1, 64)
+        many = run_cpu_baseline(wl, secs, procs)
+        one = run_cpu_baseline(wl, secs, 1)
+        line = dict(base, impl="reference", value=many["value"], ms_per_step=wl["trees"] * wl["iters"] * world / max(many["value"], 1e-9) * 1e3,
+                    cpu_baseline=many, cpu_baseline_1proc=one,
+                    e2e=dict(value=many["value"], unit="simulations/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0,
+                    note="ms_per_step is extrapolated (one step = concurrent games x sims/move simulations); the CPU arm times a bounded sample")
+        if other:
+            line["workloads"] = {other["game"]: dict(workload=other["name"], cpu_baseline=run_cpu_baseline(other, secs, procs),
+                                                     cpu_baseline_1proc=run_cpu_baseline(other, secs, 1))}
         print(json.dumps(line))
         return
 
+    import torch
+    import torch.distributed as dist
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cb = run_cpu_baseline(wl, args.cpu_seconds, args.cpu_procs)
-    r = run_b200(args, wl, rank, world)
+        cb = run_cpu_baseline(wl, args.cpu_seconds or 15.0, args.cpu_procs)
+    r = run_workload(args, wl, rank, world, args.steps, args.warmup, full=True)
+    r2 = None
+    if other:
+        from alpha_zero_b200.ai import MCTS
+        MCTS.release()
+        r2 = run_workload(args, other, rank, world, min(args.steps, 40), min(args.warmup, 3), full=True)
+    if world > 1:
+        dist.destroy_process_group()
     if rank != 0:
         return
     pk = peaks()
-    value = r["sims_per_step"] * args.steps / (r["dev_ms"] / 1e3)
-    e2e = r["sims_per_step"] * args.steps / r["e2e_s"]
-    line = dict(base, impl="b200", value=value, ms_per_step=r["dev_ms"] / args.steps, clocks=r["clocks"],
-                e2e=dict(value=e2e, unit="simulations/s", h2d_bytes_per_step=r["h2d"], d2h_bytes_per_step=r["d2h"],
-                         steps_ms=r["e2e_steps_ms"]),
-                gpu_launches=r["gpu_launches"], search_stats=r["stats"])
-    pf = r.get("path_flags", 0)
-    line["evaluator_path"] = dict(flags=pf, front_kernel="az_front2_kernel" if pf & 2 else ("az_front_kernel" if pf & 1 else "generic"),
-                                  cls_row_gemm="cta_pair" if pf & 4 else "single_cta", layernorm_fold=bool(pf & 8), head_epilogue=bool(pf & 16))
-    prof = r.get("profile", {})
-    if prof:
-        line["kernel_ms"] = {k: round(v["ms"], 4) for k, v in prof.items()}
-        line["roofline"] = roofline(wl, r, prof, pk)
-        line["rooflines_all"] = {k: rl for k, rl in ((k, roofline(wl, r, prof, pk, k)) for k in prof) if rl}
-    if "selfplay" in r:
-        line["selfplay"] = r["selfplay"]
+    line = dict(base, impl="b200")
+    line.update(summarize(args, wl, r, world, pk))
+    line["steps"] = r["steps"]
+    if r2:
+        line["workloads"] = {other["game"]: dict(summarize(args, other, r2, world, pk), config=config_of(other, world))}
     if cb:
         line["cpu_baseline"] = cb
     print(json.dumps(line))
