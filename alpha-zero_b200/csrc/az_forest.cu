@@ -475,7 +475,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     // closes a step after `vl` terminal descents as well.  At vl == 1 nothing is pending when that
     // happens, the next launch resumes the very same sequence and the reference's order is kept;
     // at vl > 1 it is part of the build-defined batching rule (oracle: az_oracle.c azo_search).
-    const unsigned kMaxTerminalPerLaunch = (unsigned)f.vl;
+    const unsigned kMaxTerminalPerLaunch = (unsigned)max(f.vl, f.max_rounds);   // max_rounds > 1 only at vl == 1 with the cache
     AzBoard<NW> kept = rootb;
     int kept_player = 0, flushed = 0;
     uint32_t kept_entry = 0xffffffffu;                        // cache entry of this lane's pending leaf
@@ -1280,7 +1280,11 @@ extern "C" int az_forest_cache_config(az_forest* f, int log2_entries) {
     cudaMemset(epoch, 0, 16);
     cudaMemset(le, 0xff, (size_t)f->d.max_leaves * 4);
     f->d.cache = c;
-    int rounds = 4;                                           // simulations per tree and launch while leaves hit the cache (vl == 1)
+    // Simulations per tree and launch while leaves hit the cache (vl == 1).  Measured on Connect4 4096 x 800 (B200, round 2):
+    // 46.5 / 41.0 / 32.3 / 23.1 / 15.9 M sims/s at 1 / 2 / 4 / 8 / 16 -- the slowest tree still needs ~iters launches per
+    // search (a sampled move into a rarely visited child leaves nothing to reuse) while every launch lasts as long as its
+    // slowest warp's R simulations -- so extra rounds do not pay; the cache's gain is the evaluator rows it removes.
+    int rounds = 1;
     if (const char* e = getenv("AZ_CACHE_ROUNDS")) rounds = std::max(1, std::min(64, atoi(e)));
     f->d.max_rounds = rounds;
     if (cudaDeviceSynchronize() != cudaSuccess) return az_fail(AZ_ECUDA, "cache_config: device error");
@@ -1336,6 +1340,16 @@ extern "C" int az_forest_set_evaluator(az_forest* f, unsigned long long id, void
 }
 
 unsigned long long az_forest_uid(az_forest* f) { return f->uid; }
+// Launches to queue before the next look at the done counter.  vl == 1 with one simulation per launch: every launch
+// retires exactly one simulation per live tree, iters + 1 launches finish the search.  Otherwise a launch retires up to
+// `vl` (or, with the cache at vl == 1, up to max_rounds) simulations per tree: queue the least number that could
+// finish, then poll.
+int az_search_burst(const AzForestDev* d, int iters, int steps_done) {
+    if (d->vl == 1 && d->max_rounds <= 1) return steps_done == 0 ? iters + 1 : (steps_done <= iters ? iters + 1 - steps_done : 4);
+    const int per = d->vl > 1 ? d->vl : d->max_rounds;
+    if (steps_done == 0) return std::max(8, (iters + per - 1) / per + 1);
+    return d->vl > 1 ? 4 : 16;
+}
 double* az_forest_noise_dev(az_forest* f) { return f->noise_dev; }
 int az_forest_use_device_noise(az_forest* f, int on) {
     f->d.use_noise = on ? 1 : 0;
@@ -1533,7 +1547,7 @@ extern "C" int az_forest_search_hash(az_forest* f, int iters, uint64_t seed, int
     // finish the search (the last one only applies results); vl > 1 polls the done counter.
     int done = 0, steps = 0;
     for (;;) {
-        const int burst = steps == 0 ? (f->d.vl == 1 && !f->d.cache.cap ? iters + 1 : std::max(8, iters / f->d.vl / (f->d.cache.cap ? 2 : 1))) : 4;
+        const int burst = az_search_burst(&f->d, iters, steps);
         for (int i = 0; i < burst; ++i) {
             if ((rc = az_forest_advance(f, stream))) return rc;
             if ((rc = az_eval_hash(f, seed, qbits, stream))) return rc;

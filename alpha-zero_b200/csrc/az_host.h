@@ -20,3 +20,4 @@ int az_forest_use_device_noise(az_forest* f, int on);
 // Evaluator identity: cached answers belong to ONE evaluator; a different tag clears the evaluation cache.
 int az_forest_set_eval_tag(az_forest* f, unsigned long long tag, cudaStream_t s);
 int az_forest_check_eval_tag(az_forest* f, unsigned long long tag);
+int az_search_burst(const AzForestDev* d, int iters, int steps_done);   // launches to queue before polling the done counter

@@ -1281,8 +1281,8 @@ extern "C" int az_forest_search_net(az_forest* f, az_net* n, int iters, void* st
     g.last_use = ++g_graph_clock;
     int done = 0;
     for (;;) {
-        const int want = steps <= 1 ? (d->vl == 1 && !cache_on ? iters + 1 - steps : std::max(8, iters / d->vl)) : 4;
-        const int burst = (want + g.steps - 1) / g.steps;
+        const int want = az_search_burst(d, iters, steps);
+        const int burst = std::max(1, (want + g.steps - 1) / g.steps);
         for (int i = 0; i < burst; ++i) {
             AZ_CUDA_OK(cudaGraphLaunch(g.exec, s));
             n->launches += g.kernels;
