@@ -17,6 +17,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
 UNITS = {
     "az_forest.cu": ["-fmad=false"],
     "az_selfplay.cu": ["-fmad=false"],
+    "az_noalloc.cu": ["-fmad=false"],
     "az_net.cu": [],
 }
 

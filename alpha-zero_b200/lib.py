@@ -54,6 +54,7 @@ _SIGS = {
     "az_gemm_bf16": (i32, [vp, i32, vp, vp, vp, i32, vp, i32, i32, i32, i32, i32, vp]),
 }
 _SIGS.update({
+    "az_rules_legal_noalloc": (i32, [i32, i32, i32, i32, vp, vp, vp, vp]),
     "az_forest_cache_config": (i32, [vp, i32]),
     "az_forest_cache_clear": (i32, [vp, vp]),
     "az_forest_cache_info": (i32, [vp, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),

@@ -153,6 +153,16 @@ AZ_API long long az_selfplay_launch_count(az_selfplay* sp);
 /* words_host uint64 [n][2][nw]; out_counts int32 [n]; out_cells uint8 [n][rows*cols]. */
 AZ_API int az_rules_legal(int game, int rows, int cols, int n, const uint64_t* words_host, int32_t* out_counts_host,
                    uint8_t* out_cells_host);
+/* az_rules_legal for callers that may not allocate device memory (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  It has NO counterpart in the reference.
+ * words_dev uint64 [n][2][nw], out_counts_dev int32 [n], out_cells_dev uint8 [n][rows*cols] are DEVICE buffers of the
+ * caller; asynchronous on `stream`; results identical to az_rules_legal.  The kernel's scratch is one static __device__
+ * array of 4 MiB + 2 KiB that every GPU loading the library holds until exit; the call performs no cudaMalloc / cudaFree.
+ * Limit: n * 2 * (set_slots + 1) <= 4 MiB, i.e. at most 16 256 positions of 7x7 Gomoku, 4 088 of 15x15 Gomoku, 2 097 152
+ * of TicTacToe / Connect4 per call; larger n returns AZ_EINVAL with the limit in az_last_error().  All calls share the
+ * array (it keeps the last call's contents; nothing in it needs clearing): calls that overlap on the GPU race. */
+AZ_API int az_rules_legal_noalloc(int game, int rows, int cols, int n, const uint64_t* words_dev, int32_t* out_counts_dev,
+                                  uint8_t* out_cells_dev, void* stream);
 /* After `player` played `cell`: winner id or -1 (check_winner). */
 AZ_API int az_rules_winner(int game, int rows, int cols, int n, const uint64_t* words_host, const int32_t* players_host,
                     const int32_t* cells_host, int32_t* out_winner_host);
