@@ -73,9 +73,9 @@ class MCTS:
     _MAX_FORESTS = 3            # node pools are large (Gomoku 8192 x 800: 10 GB): keep the most recently used few
 
     @staticmethod
-    def _forest_for(Game, n_trees, iters, vl):
+    def _forest_for(Game, n_trees, iters, vl, tag=0):
         spec = _spec_of(Game)
-        key = (spec.name, spec.rows, n_trees, vl)
+        key = (spec.name, spec.rows, n_trees, vl, tag)
         f = MCTS._forests.pop(key, None)
         if f is None or f.max_iters < iters:
             if f is not None:
@@ -176,14 +176,19 @@ class MCTS:
 
     # ---- many positions at once --------------------------------------------------------------------
     @staticmethod
-    def mcts_batch(model, boards, players, move_counts, Game, mcts_iterations, noise=None, vl=1, active=None):
+    def mcts_batch(model, boards, players, move_counts, Game, mcts_iterations, noise=None, vl=1, active=None, forest_tag=0,
+                   return_best=False):
         """boards float32 [n,C,H,W]; noise float64 [n,A] or None.  Returns (visits int32 [n,A],
-        q float64 [n]) -- the visit-count policy numerators and root.value/root.visit."""
+        q float64 [n]) -- the visit-count policy numerators and root.value/root.visit -- and with return_best the cell of
+        root.max_visit_child() per tree (first maximum in child order).  forest_tag selects a separate forest (and
+        evaluation cache) for callers that alternate between evaluators, e.g. the arena."""
         boards = np.asarray(boards, dtype=np.float32)
-        forest = MCTS._forest_for(Game, boards.shape[0], mcts_iterations, vl)
+        forest = MCTS._forest_for(Game, boards.shape[0], mcts_iterations, vl, forest_tag)
         forest.set_roots_planes(boards, players, move_counts)
         forest.set_noise(noise)
         forest.set_active(active)
         MCTS._run(forest, model, mcts_iterations)
         MCTS.mcts_count += mcts_iterations * boards.shape[0]
+        if return_best:
+            return forest.root_visits() + (forest.root_best(),)
         return forest.root_visits()

@@ -937,6 +937,21 @@ __global__ void az_root_visits_kernel(AzForestDev f, int* visits, double* q) {
     if (threadIdx.x == 0 && q) q[tree] = nodes[0].hot.N ? nodes[0].W / (double)nodes[0].hot.N : 0.0;   // gomoku.py:141
 }
 
+// Node.max_visit_child (ai/node.py:76-81) for every root: the FIRST most-visited child in child order, as its cell.
+__global__ void az_root_best_kernel(AzForestDev f, int* cells) {
+    const int tree = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tree >= f.n_trees) return;
+    const AzNode* nodes = f.nodes + (size_t)tree * f.cap;
+    const AzMeta m = nodes[0].meta;
+    int best = -1, cell = -1;
+    if (m.status == AZ_ST_EXPANDED)
+        for (int c = 0; c < m.nchild; ++c) {
+            const int n = nodes[m.child_base + c].hot.N;
+            if (n > best) { best = n; cell = nodes[m.child_base + c].meta.action; }
+        }
+    cells[tree] = cell;
+}
+
 }  // namespace
 
 // ======================================================================================
@@ -1574,6 +1589,17 @@ extern "C" int az_forest_root_visits(az_forest* f, int32_t* visits_host, double*
     AZ_CUDA_OK(cudaStreamSynchronize(s));
     memcpy(visits_host, h_vis, (size_t)n * A * 4);
     if (q_host) memcpy(q_host, h_q, (size_t)n * 8);
+    return AZ_OK;
+}
+
+extern "C" int az_forest_root_best(az_forest* f, int32_t* cells_host, void* stream) {
+    if (!f || !cells_host) return az_fail(AZ_EINVAL, "root_best: null");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int n = f->d.n_trees;
+    az_root_best_kernel<<<(n + 127) / 128, 128, 0, s>>>(f->d, f->vis_dev);
+    AZ_CUDA_OK(cudaMemcpyAsync(f->h_stage, f->vis_dev, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    AZ_CUDA_OK(cudaStreamSynchronize(s));
+    memcpy(cells_host, f->h_stage, (size_t)n * 4);
     return AZ_OK;
 }
 

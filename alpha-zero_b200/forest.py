@@ -169,6 +169,12 @@ class Forest:
         _lib.check(self._L.az_forest_root_visits(self.h, _ptr(vis), _ptr(q), self.stream), "root_visits")
         return vis, q
 
+    def root_best(self):
+        """Cell of root.max_visit_child() for every tree: first maximum in child order (ai/node.py:76-81)."""
+        cells = np.zeros(self.n_trees, np.int32)
+        _lib.check(self._L.az_forest_root_best(self.h, _ptr(cells), self.stream), "root_best")
+        return cells
+
     def root_children(self, tree):
         m = self.g.max_children
         cells = np.zeros(m, np.int32)
