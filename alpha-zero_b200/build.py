@@ -18,6 +18,7 @@ UNITS = {
     "az_forest.cu": ["-fmad=false"],
     "az_selfplay.cu": ["-fmad=false"],
     "az_noalloc.cu": ["-fmad=false"],
+    "az_replay.cu": ["-fmad=false"],
     "az_net.cu": [],
 }
 

@@ -55,6 +55,17 @@ _SIGS = {
 }
 _SIGS.update({
     "az_rules_legal_noalloc": (i32, [i32, i32, i32, i32, vp, vp, vp, vp]),
+    "az_forest_root_best": (i32, [vp, vp, vp]),
+    "az_replay_create": (i32, [i32, i32, i32, C.c_longlong, C.POINTER(vp)]),
+    "az_replay_destroy": (None, [vp]),
+    "az_replay_size": (C.c_longlong, [vp]),
+    "az_replay_entry_bytes": (C.c_longlong, [vp]),
+    "az_replay_clear": (i32, [vp]),
+    "az_replay_add": (C.c_longlong, [vp, i32, i32, vp, vp, vp, vp, vp, vp]),
+    "az_replay_sample": (i32, [vp, i32, u64, u64, vp, vp, vp, vp, vp]),
+    "az_replay_read": (i32, [vp, C.c_longlong, i32, vp, vp, vp, vp]),
+    "az_d4_source_cell": (i32, [i32, i32, i32, i32]),
+    "az_loss_policy_value": (i32, [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp]),
     "az_forest_cache_config": (i32, [vp, i32]),
     "az_forest_cache_clear": (i32, [vp, vp]),
     "az_forest_cache_info": (i32, [vp, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),

@@ -66,3 +66,84 @@ class ReplayBuffer:
             print(f"Replay Buffer loaded from {filename} successfully.")
         except Exception:                               # noqa: BLE001 -- reference behaviour
             print("Failed to load Replay Buffer.")
+
+
+class DeviceReplayBuffer:
+    """The same contract with the entries resident in HBM (csrc/az_replay.cu): a ring of `buffer_size` entries in the
+    reference's order, filled straight from the self-play engine's trajectory arrays (add_trajectories: z assignment,
+    canonicalisation and the 8 dihedral variants of train.save_data_to_buffer run as one kernel), sampled without
+    replacement by a keyed permutation into three float32 CUDA tensors [B,C,H,W], [B,A], [B,1] -- no host copy on either
+    side.  to_host() rebuilds the reference's deque (for save_pickle)."""
+
+    def __init__(self, Game, buffer_size, seed=None):
+        import ctypes as C
+        from . import lib as _lib
+        from .forest import game_spec
+        self._lib, self._C = _lib, C
+        self._L = _lib.load()
+        self.g = game_spec(Game.name, Game.rows)
+        self.buffer_size = int(buffer_size)
+        h = C.c_void_p()
+        _lib.check(self._L.az_replay_create(self.g.gid, self.g.rows, self.g.cols, self.buffer_size, C.byref(h)), "az_replay_create")
+        self.h = h
+        self.seed = int(np.random.randint(0, 2 ** 31 - 1)) if seed is None else int(seed)
+        self.draws = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self._L.az_replay_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def size(self):
+        return int(self._L.az_replay_size(self.h))
+
+    def entry_bytes(self):
+        return int(self._L.az_replay_entry_bytes(self.h))
+
+    def clear(self):
+        self._lib.check(self._L.az_replay_clear(self.h), "az_replay_clear")
+
+    def add_trajectories(self, t):
+        """t: dict with CUDA tensors plies / winner / first (int32 [G]), words (int64 [G,P,2,nw]), visits (int16 [G,P,A]) --
+        selfplay.SelfPlayEngine.device_tensors() or parallel.gather_trajectories(); games are stored in array order.
+        Returns the number of entries appended."""
+        stream = torch.cuda.current_stream().cuda_stream
+        arrs = [t[k].contiguous() for k in ("plies", "winner", "first", "words", "visits")]
+        assert all(a.is_cuda for a in arrs) and arrs[0].dtype == torch.int32
+        n = self._lib.check(self._L.az_replay_add(self.h, int(arrs[0].shape[0]), int(arrs[3].shape[1]), *[a.data_ptr() for a in arrs], stream),
+                            "az_replay_add")
+        return int(n)
+
+    def _out(self, n):
+        g = self.g
+        dev = torch.device("cuda", torch.cuda.current_device())
+        return (torch.empty((n, g.planes, g.rows, g.cols), dtype=torch.float32, device=dev),
+                torch.empty((n, g.action_dim), dtype=torch.float32, device=dev), torch.empty((n, 1), dtype=torch.float32, device=dev))
+
+    def sample(self, batch_size, return_indices=False):
+        s, p, z = self._out(batch_size)
+        idx = torch.empty(batch_size, dtype=torch.int64, device=s.device) if return_indices else None
+        self.draws += 1
+        self._lib.check(self._L.az_replay_sample(self.h, int(batch_size), self._C.c_uint64(self.seed), self._C.c_uint64(self.draws),
+                                                 s.data_ptr(), p.data_ptr(), z.data_ptr(), idx.data_ptr() if return_indices else None,
+                                                 torch.cuda.current_stream().cuda_stream), "az_replay_sample")
+        return (s, p, z, idx) if return_indices else (s, p, z)
+
+    def read(self, start=0, count=None):
+        count = self.size() - start if count is None else count
+        s, p, z = self._out(count)
+        self._lib.check(self._L.az_replay_read(self.h, int(start), int(count), s.data_ptr(), p.data_ptr(), z.data_ptr(),
+                                               torch.cuda.current_stream().cuda_stream), "az_replay_read")
+        return s, p, z
+
+    def to_host(self):
+        """ReplayBuffer holding the same entries.  (The policy comes back as the float32 quotient widened to float64 --
+        the reference's deque holds the float64 quotient; sample() rounds both to the same float32.)"""
+        out = ReplayBuffer(self.buffer_size)
+        if self.size():
+            s, p, z = (x.cpu().numpy() for x in self.read())
+            for i in range(len(s)):
+                out.add(s[i], p[i].astype(np.float64), [int(z[i, 0])])
+        return out

@@ -203,38 +203,118 @@ def collect_data(Game, model, buffer, iterations, mcts_iter, display=False, vl=1
     return results
 
 
+class _PolicyValueLoss(torch.autograd.Function):
+    """train.py:110-112 as ONE kernel (az_loss_policy_value, csrc/az_replay.cu): soft-target cross entropy + MSE, forward
+    and backward together; returns (policy_loss, value_loss) and hands the stored gradients back in backward."""
+
+    @staticmethod
+    def forward(ctx, logits, values, pis, zs):
+        from . import lib as _lib
+        L = _lib.load()
+        logits, values, pis, zs = (t.contiguous().float() for t in (logits, values, pis, zs))
+        B, A = logits.shape
+        dl, dv = torch.empty_like(logits), torch.empty_like(values)
+        out = torch.empty(2, dtype=torch.float32, device=logits.device)
+        _lib.check(L.az_loss_policy_value(logits.data_ptr(), values.data_ptr(), pis.data_ptr(), zs.data_ptr(), int(B), int(A), dl.data_ptr(),
+                                          dv.data_ptr(), out.data_ptr(), torch.cuda.current_stream().cuda_stream), "az_loss_policy_value")
+        ctx.save_for_backward(dl, dv)
+        return out[0], out[1]
+
+    @staticmethod
+    def backward(ctx, g_policy, g_value):
+        dl, dv = ctx.saved_tensors
+        return dl * g_policy, dv * g_value, None, None
+
+
+def policy_value_loss(logits, values, pis, zs):
+    """(policy_loss, value_loss) of train.py:110-112; the fused CUDA kernel for CUDA tensors, the reference's torch ops on CPU."""
+    if logits.is_cuda:
+        return _PolicyValueLoss.apply(logits, values, pis, zs)
+    return (torch.mean(torch.sum(-pis * torch.log_softmax(logits, dim=1), dim=1)), torch.nn.functional.mse_loss(values, zs))
+
+
+class _GradBuckets:
+    """Data-parallel gradient averaging overlapped with backward: every parameter's .grad is a view into one flat buffer
+    cut into buckets (in reverse parameter order = the order backward produces them); when the last gradient of a bucket
+    has been accumulated its all-reduce starts asynchronously (NCCL over NVLink) while backward continues."""
+
+    def __init__(self, model, bucket_bytes=4 << 20):
+        import torch.distributed as dist
+        self.dist, self.world = dist, dist.get_world_size()
+        params = [p for p in model.parameters() if p.requires_grad]
+        self.flat = torch.zeros(sum(p.numel() for p in params), dtype=params[0].dtype, device=params[0].device)
+        off = self.flat.numel()
+        self.buckets, cur, cur_hi = [], [], off                     # bucket = [lo, hi, params, pending]
+        for p in reversed(params):
+            off -= p.numel()
+            p.grad = self.flat[off:off + p.numel()].view_as(p)
+            cur.append(p)
+            if (cur_hi - off) * self.flat.element_size() >= bucket_bytes or off == 0:
+                self.buckets.append(dict(lo=off, hi=cur_hi, params=cur, left=len(cur)))
+                cur, cur_hi = [], off
+        self.of = {id(p): b for b in self.buckets for p in b["params"]}
+        self.work = []
+        self.hooks = [p.register_post_accumulate_grad_hook(self._ready) for p in params]
+
+    def _ready(self, p):
+        b = self.of[id(p)]
+        b["left"] -= 1
+        if b["left"] == 0:
+            self.work.append(self.dist.all_reduce(self.flat[b["lo"]:b["hi"]], async_op=True))
+
+    def zero(self):
+        self.flat.zero_()
+        for b in self.buckets:
+            b["left"] = len(b["params"])
+
+    def finish(self):
+        for w in self.work:
+            w.wait()
+        self.work.clear()
+        self.flat /= self.world
+
+    def close(self):
+        for h in self.hooks:
+            h.remove()
+
+
 def train(model, batch_size, buffer, train_iterations, lr, device):
     """train.py:85-123: fresh Adam, loss = soft-target CE + MSE + 1e-4 * sum(w^2) over every
     parameter whose name has no 'bias' (the 'LayerNorm' filter of train.py:106 never matches,
-    so LayerNorm weights, cls_token and pos_embedding ARE regularised -- kept as is)."""
+    so LayerNorm weights, cls_token and pos_embedding ARE regularised -- kept as is).
+    `buffer` is a ReplayBuffer (host deque, one H2D per step as in the reference, train.py:98-99) or a
+    DeviceReplayBuffer (samples are CUDA tensors already).  Under torch.distributed (world > 1) every rank samples its own
+    batch and the gradients are averaged with bucketed all-reduces overlapped with backward."""
     import torch.distributed as dist
     model.to(device)
     model.train()
     opt = torch.optim.Adam(model.parameters(), lr=lr)
     ddp = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+    buckets = _GradBuckets(model) if ddp else None
+    reg = [p for name, p in model.named_parameters() if "bias" not in name and "LayerNorm" not in name]
     loss = policy_loss = value_loss = l2 = torch.zeros(())
     t0 = time.time()
     for i in range(train_iterations):
-        states, pis, zs = (t.to(device) for t in buffer.sample(batch_size))
-        l2 = sum(torch.sum(p ** 2) for name, p in model.named_parameters() if "bias" not in name and "LayerNorm" not in name)
+        states, pis, zs = (t.to(device, non_blocking=True) for t in buffer.sample(batch_size))
+        l2 = torch.stack([torch.sum(p * p) for p in reg]).sum()
         logits, values = model(states)
-        policy_loss = torch.mean(torch.sum(-pis * torch.log_softmax(logits, dim=1), dim=1))
-        value_loss = torch.nn.functional.mse_loss(values, zs)
+        policy_loss, value_loss = policy_value_loss(logits, values, pis, zs)
         loss = policy_loss + value_loss + 1e-4 * l2
-        opt.zero_grad()
+        if buckets:
+            buckets.zero()
+        else:
+            opt.zero_grad()
         loss.backward()
-        if ddp:                                         # data-parallel ranks: average gradients over NVLink
-            flat = torch.cat([p.grad.reshape(-1) for p in model.parameters()])
-            dist.all_reduce(flat)
-            flat /= dist.get_world_size()
-            off = 0
-            for p in model.parameters():
-                p.grad.copy_(flat[off:off + p.numel()].view_as(p))
-                off += p.numel()
+        if buckets:                                     # data-parallel ranks: average gradients over NVLink
+            buckets.finish()
         opt.step()
         if (i + 1) % 50 == 0:
             now = time.time()
             print("train_iter:", i + 1, "loss:", loss.item(), "policy_loss:", policy_loss.item(), "value_loss:",
                   value_loss.item(), "l2_loss:", l2.item(), "time:", now - t0)
             t0 = now
+    if buckets:
+        buckets.close()
+        for p in model.parameters():                    # leave ordinary, independent .grad tensors behind
+            p.grad = None
     return loss.item(), policy_loss.item(), value_loss.item(), l2.item()

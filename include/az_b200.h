@@ -89,6 +89,9 @@ AZ_API int az_forest_search_hash(az_forest* f, int iters, uint64_t seed, int qbi
  *      root.value/root.visit (gomoku.py:141) and reads of root.children (test.py:44-46) ---- */
 AZ_API int az_forest_root_visits(az_forest* f, int32_t* visits_host /*[n_trees][A]*/, double* q_host /*[n_trees]*/,
                           void* stream);
+/* root.max_visit_child() (ai/node.py:76-81) of every tree: cell of the FIRST most-visited child in child order
+ * (-1 for a root that was not searched); int32 [n_trees]. */
+AZ_API int az_forest_root_best(az_forest* f, int32_t* cells_host, void* stream);
 /* Children of one root in child order: cell = r*cols+c of prevAction. Returns the count. */
 AZ_API int az_forest_root_children(az_forest* f, int tree, int max_children, int32_t* cells_host, int32_t* visits_host,
                             double* values_host, double* priors_host, int32_t* root_visit, double* root_value,
@@ -148,6 +151,36 @@ AZ_API int az_selfplay_read(az_selfplay* sp, int32_t* plies_host, int32_t* winne
                             uint16_t* visits_host, double* q_host, int16_t* action_host, double* u_host, void* stream);
 AZ_API int az_selfplay_read_slots(az_selfplay* sp, int32_t* slot_game_host, double* noise_host, void* stream);
 AZ_API long long az_selfplay_launch_count(az_selfplay* sp);
+
+/* ---- device-resident replay buffer: replaces train.save_data_to_buffer / rotate_data / flip_data (train.py:8-49) and
+ *      ReplayBuffer.add / sample / size (replay_buffer.py:8-25,34-35) ---------------------------------------------------
+ * A ring of `capacity` ENTRIES (the deque's maxlen), one per sample the reference would hold, in its order (game, ply,
+ * variant: rot0, rot0-lr, rot0-tb, rot90, rot90-lr, rot90-tb, rot180, rot270; plies 0 and 1 once; Connect4: identity +
+ * mirror), compact in HBM: canonical transformed side bitboards, u16 visit counts, z. */
+typedef struct az_replay az_replay;
+AZ_API int az_replay_create(int game, int rows, int cols, long long capacity, az_replay** out);
+AZ_API void az_replay_destroy(az_replay* rb);
+AZ_API long long az_replay_size(az_replay* rb);
+AZ_API long long az_replay_entry_bytes(az_replay* rb);
+AZ_API int az_replay_clear(az_replay* rb);
+/* Appends the recorded positions of n_games finished games; device arrays in the layout of az_selfplay_buffers
+ * (plies / winner / first i32[n_games], words u64[n_games][P][2][nw], visits u16[n_games][P][A], P = rows*cols), games
+ * in storage order.  Returns the entries appended (< 0: error). */
+AZ_API long long az_replay_add(az_replay* rb, int n_games, int max_plies, const int32_t* plies_dev, const int32_t* winner_dev,
+                               const int32_t* first_dev, const uint64_t* words_dev, const uint16_t* visits_dev, void* stream);
+/* ReplayBuffer.sample(B): B distinct entries drawn uniformly (a keyed permutation of (seed, counter)) expanded into the
+ * caller's device buffers: states f32 [B][C][rows][cols], policies f32 [B][A] (= (float)(n_a / sum n)), z f32 [B][1];
+ * indices_dev (optional, int64 [B]) receives the entry numbers (0 = oldest). */
+AZ_API int az_replay_sample(az_replay* rb, int B, uint64_t seed, uint64_t counter, float* states_dev, float* policies_dev,
+                            float* z_dev, long long* indices_dev, void* stream);
+/* Entries start .. start+count-1 (oldest first), expanded like a sample. */
+AZ_API int az_replay_read(az_replay* rb, long long start, int count, float* states_dev, float* policies_dev, float* z_dev, void* stream);
+/* Source cell of output cell `cell` under augmentation variant 0..7 (host function; the transform the kernels apply). */
+AZ_API int az_d4_source_cell(int rows, int cols, int variant, int cell);
+/* ---- the loss of train.train (train.py:110-112) for one batch, forward + backward in one kernel: out2 = {mean_b sum_a
+ *      -pi log_softmax(logits), mean_b (v - z)^2}, dlogits [B][A], dvalues [B].  All pointers device memory. */
+AZ_API int az_loss_policy_value(const float* logits_dev, const float* values_dev, const float* pis_dev, const float* zs_dev, int B,
+                                int A, float* dlogits_dev, float* dvalues_dev, float* out2_dev, void* stream);
 
 /* ---- batched rules for differential tests: games/*.py get_valid_moves / check_winner ---- */
 /* words_host uint64 [n][2][nw]; out_counts int32 [n]; out_cells uint8 [n][rows*cols]. */
