@@ -244,6 +244,118 @@ __device__ __noinline__ int az_cache_probe(const AzCacheDev c, uint64_t mine, ui
     return 0;
 }
 
+// ---- vl == 1: backup + cached best child ------------------------------------------------------------------
+// At vl == 1 exactly one simulation of a tree is in flight, so between two visits of a node nothing it scores changes
+// except through the backup of the simulation that passed through it.  The backup therefore also computes, for EVERY
+// path node, the PUCT argmax the NEXT visit of that node will take -- same inputs, same arithmetic, same first-maximum
+// rule as Node.select (ai/node.py:42-47, utils.py:29-44) -- and stores it in the node's V field (unused without
+// virtual loss).  The next descent is then a pointer walk: one uniform 32-byte load per level instead of a scan +
+// scoring + warp reduction per level.  Work split: (1) lane i updates path node i (visit += 1, value += v,
+// node.py:69-72) and publishes the record in shared memory; (2) 8-lane groups score the children of one path node
+// each, four path nodes per pass, one child per lane and pass of 8 -- the scoring stays lane-parallel (issue slots, not
+// memory, bound this kernel) and the child fetches of four levels share one round trip; (3) lane i stores node i.
+// nd0 / nd1: path entries lane and lane + 32; `result` is credited to the last path node, alternating sign upwards;
+// leaf_best: argmax among the fresh children of the last node (0 for a terminal leaf).
+// Returns the root's new best child (all lanes).  *reads += children scored (statistics).
+struct __attribute__((aligned(8))) AzBestRec {   // 32 bytes
+    uint32_t nd;
+    int N;
+    float Q, P;
+    double W;
+    uint32_t cb;
+    uint16_t nc, best;
+};
+#define AZ_BEST_SMEM (64 * 32)
+template <int G>
+__device__ __noinline__ int az_backup_best(AzNode* nodes, uint32_t nd0, uint32_t nd1, int len, double result, int leaf_best,
+                                           const double* root_p64, int lane, unsigned gmask, uint64_t pol, unsigned* reads,
+                                           AzBestRec* rec) {
+    for (int h = 0; h * 32 < len; ++h) {                      // (1) own records
+        const int i = lane + 32 * h;
+        if (i < len) {
+            const uint32_t nd = h ? nd1 : nd0;
+            AzHot hh;
+            ulonglong2 mw;
+            az_load_node(&nodes[nd], pol, hh, mw);
+            const AzMeta m = *reinterpret_cast<const AzMeta*>(&mw.x);
+            const double v = ((len - 1 - i) & 1) ? -result : result;
+            AzBestRec r;
+            r.nd = nd;
+            r.W = __dadd_rn(__longlong_as_double((long long)mw.y), v);
+            r.N = hh.N + 1;
+            r.Q = az_q32(r.W, r.N);
+            r.P = hh.P;
+            r.cb = m.child_base;
+            r.nc = m.nchild;
+            r.best = 0;
+            rec[i] = r;
+        }
+    }
+    __syncwarp(gmask);
+    const int k = lane & 7, grp = lane >> 3;                  // (2) children of path nodes p0 .. p0+3, 8 lanes each
+    const unsigned m8 = 0xffu << (grp * 8);
+    unsigned scored = 0;
+    for (int p0 = 0; p0 < len - 1; p0 += 4) {
+        const int j = p0 + grp;
+        if (j >= len - 1) continue;                           // group-uniform
+        const AzBestRec r = rec[j];
+        const uint32_t x_nd = rec[j + 1].nd;                  // the child on the path: its record in memory is stale
+        const int nc = r.nc;
+        int bi = 0x7fffffff;
+        if (j == 0 && root_p64) {                             // noisy root: f64 priors, f64 scores (utils.py:24-25)
+            const double s = __dsqrt_rn((double)r.N);
+            double best = -1.0 / 0.0;
+            for (int c = k; c < nc; c += 8) {
+                int n;
+                double W;
+                if (r.cb + c == x_nd) {
+                    n = rec[1].N;
+                    W = rec[1].W;
+                } else {
+                    n = (int)az_ldk(reinterpret_cast<const uint32_t*>(&nodes[r.cb + c].hot.N), pol);
+                    W = __longlong_as_double((long long)az_ldk(reinterpret_cast<const uint64_t*>(&nodes[r.cb + c].W), pol));
+                }
+                const double sc = az_puct64(W, root_p64[c], n, s);
+                if (sc > best) { best = sc; bi = c; }
+            }
+            bi = az_group_argmax(m8, best, bi);
+        } else {
+            const float s = __fsqrt_rn((float)r.N);
+            float best = -1.0f / 0.0f;
+            for (int c = k; c < nc; c += 8) {
+                uint32_t cn, cq, cp, unused;
+                asm volatile("ld.global.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+                             : "=r"(cn), "=r"(cq), "=r"(cp), "=r"(unused) : "l"(&nodes[r.cb + c]), "l"(pol) : "memory");
+                if (r.cb + c == x_nd) {
+                    cn = (uint32_t)rec[j + 1].N;
+                    cq = __float_as_uint(rec[j + 1].Q);
+                }
+                const float sc = az_puct32(__uint_as_float(cq), __uint_as_float(cp), (int)cn, s);
+                if (sc > best) { best = sc; bi = c; }
+            }
+            bi = az_group_argmax(m8, best, bi);
+        }
+        if (k == 0) {
+            rec[j].best = (uint16_t)(bi == 0x7fffffff ? 0 : bi);   // all-NaN guard: max() keeps the first
+            scored += (unsigned)nc;
+        }
+    }
+    __syncwarp(gmask);
+    for (int h = 0; h * 32 < len; ++h) {                      // (3) store
+        const int i = lane + 32 * h;
+        if (i < len) {
+            const AzBestRec r = rec[i];
+            const uint32_t best = i == len - 1 ? (uint32_t)leaf_best : (uint32_t)r.best;
+            az_store16_keep(&nodes[r.nd].hot, make_uint4((uint32_t)r.N, __float_as_uint(r.Q), __float_as_uint(r.P), best), pol);
+            az_store8_keep(&nodes[r.nd].W, (unsigned long long)__double_as_longlong(r.W), pol);
+        }
+    }
+    *reads += __reduce_add_sync(gmask, scored);
+    const int root_best = len == 1 ? leaf_best : (int)rec[0].best;
+    __syncwarp(gmask);                                        // rec is reused by the next backup
+    return root_best;
+}
+
 // Expansion of up to AZ_LP pending leaves of a tree runs in parallel (one lane per leaf generates
 // that leaf's legal moves -- for Gomoku the sequential CPython-set emulation -- into its own scratch).
 #define AZ_LP 8
@@ -303,13 +415,14 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     // the root's record is tracked in registers for the whole launch: every backup and every virtual
     // loss passes through it, and a reload after the backup stores would cost a round trip per descent
     AzMeta root_m;
-    int root_nv;
+    int root_nv, root_best;
     {
         AzHot hr;
         ulonglong2 mwr;
         az_load_node(f.nodes + (size_t)tree * f.cap, l2keep, hr, mwr);
         root_m = *reinterpret_cast<const AzMeta*>(&mwr.x);
         root_nv = hr.N + (int)hr.V;
+        root_best = (int)hr.V;                                // vl == 1: V holds the cached best child (az_backup_best)
     }
     if (!is_active || is_done) return;
     AZ_AT(0);                                                 // tree scalars + root words
@@ -321,12 +434,15 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
     const int moves_pad = (g.max_children + 15) & ~15;
     const int lm_bytes = moves_pad + 2 * g.set_slots;           // legal-move scratch of one pending leaf
     uint8_t* s_lm = sm + 4 * f.max_depth;
+    AzBestRec* s_rec = reinterpret_cast<AzBestRec*>(sm + smem_per_group - AZ_BEST_SMEM);   // vl == 1 only (az_forest_create)
 
     AzNode* const nodes = f.nodes + (size_t)tree * f.cap;
     const AzHotView hot{nodes};
     const AzMetaView meta{nodes};
     const AzMeta64View meta64{nodes};
     const bool use_vl = f.vl > 1;
+    // one simulation in flight per tree and PUCT selection: descents follow cached best children (az_backup_best)
+    const bool best_mode = (G == 32) && f.vl == 1 && !f.ucb1 && f.max_depth <= 64 && !f.no_best;
     const int A = g.action_dim;
     const int LP = f.lp;
 
@@ -405,6 +521,9 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             n_nodes += nc;
             const float* pri = priors_of(slot);
             const bool noisy_root = (leaf == 0) && f.use_noise;
+            int leaf_best = 0;                                    // first maximum of the fresh children's scores = of their priors
+            float lb32 = -1.0f / 0.0f;                            // (n = 0, parent visit 1: P * sqrt(1) / 1, utils.py:34)
+            double lb64 = -1.0 / 0.0;
             for (int c0 = 0; c0 < nc; c0 += G) {
                 const int c = c0 + lane;
                 const bool valid = c < nc;
@@ -418,10 +537,26 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
                 } else {
                     p = valid ? pri[ai] : 0.f;
                 }
+                double p64 = 0.0;
+                if (valid && noisy_root)                         // utils.py:24: f32*0.75 + f64 noise*0.25
+                    p64 = __dadd_rn((double)__fmul_rn(0.75f, p), __dmul_rn(0.25, f.root_noise[(size_t)tree * A + ai]));
+                if (best_mode) {                                 // all lanes take part in the reductions
+                    if (noisy_root) {
+                        double sc = -1.0 / 0.0;
+                        if (valid && p64 > sc) sc = p64;
+                        const int bi = az_group_argmax(gmask, sc, valid ? c : 0x7fffffff);
+                        const double top = __shfl_sync(gmask, sc, bi < 0x7fffffff ? (bi - c0) : 0, G);
+                        if (bi < 0x7fffffff && top > lb64) { lb64 = top; leaf_best = bi; }
+                    } else {
+                        float sc = -1.0f / 0.0f;
+                        if (valid && p > sc) sc = p;
+                        const int bi = az_group_argmax(gmask, sc, valid ? c : 0x7fffffff);
+                        const float top = __shfl_sync(gmask, sc, bi < 0x7fffffff ? (bi - c0) : 0, G);
+                        if (bi < 0x7fffffff && top > lb32) { lb32 = top; leaf_best = bi; }
+                    }
+                }
                 if (!valid) continue;
-                if (noisy_root) {                                // utils.py:24: f32*0.75 + f64 noise*0.25
-                    const double p64 = __dadd_rn((double)__fmul_rn(0.75f, p),
-                                                 __dmul_rn(0.25, f.root_noise[(size_t)tree * A + ai]));
+                if (noisy_root) {
                     f.root_prior64[(size_t)tree * g.max_children + c] = p64;
                     p = __double2float_rn(p64);                  // kept for reporting only
                 }
@@ -450,9 +585,14 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             }
             AZ_AT(2);                                             // child block written
             const double result = -(double)val;                   // mcts.py:56
-            for (int i = lane; i < len; i += G) {                 // node.py:69-72
-                const uint32_t nd = pre ? (i < 32 ? q0 : q1) : gpath[i];
-                az_backup_node(nodes, nd, ((len - 1 - i) & 1) ? -result : result, use_vl, l2keep);
+            if (best_mode) {
+                root_best = az_backup_best<G>(nodes, q0, q1, len, result, leaf_best,
+                                              f.use_noise ? f.root_prior64 + (size_t)tree * g.max_children : nullptr, lane, gmask, l2keep, &st_reads, s_rec);
+            } else {
+                for (int i = lane; i < len; i += G) {             // node.py:69-72
+                    const uint32_t nd = pre ? (i < 32 ? q0 : q1) : gpath[i];
+                    az_backup_node(nodes, nd, ((len - 1 - i) & 1) ? -result : result, use_vl, l2keep);
+                }
             }
             root_nv += use_vl ? 0 : 1;                            // the root: N + 1, V - 1 under virtual loss
             __syncwarp(gmask);
@@ -522,6 +662,23 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
         AZ_AT(4);                                             // root record (registers)
         // One memory round trip per level: every lane fetches hot AND meta of its children, the
         // winner's meta / visit count arrive by shuffle (mcts.py:20-23, node.py:42-47).
+        int walk = root_best;
+        while (best_mode && m.status == AZ_ST_EXPANDED) {     // vl == 1: follow the cached best children, one uniform load per level
+            node = m.child_base + (uint32_t)walk;
+            AzHot h;
+            ulonglong2 mw;
+            az_load_node(&nodes[node], l2keep, h, mw);
+            m = *reinterpret_cast<const AzMeta*>(&mw.x);
+            walk = (int)h.V;
+            if (lane == 0) s_path[len] = node;
+            ++len;
+            ++st_sel;
+            b.put(player, m.action);                          // Game.make_move (mcts.py:23)
+            player ^= 1;
+            ++mc;
+            AZ_AT(5);
+            AZ_AT_COUNT(14, 1);
+        }
         while (m.status == AZ_ST_EXPANDED) {
             const int nc = m.nchild;
             const uint32_t cb = m.child_base;
@@ -599,7 +756,12 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
         }
         if (status == AZ_ST_WIN || status == AZ_ST_DRAW) {
             const double v = status == AZ_ST_WIN ? 1.0 : 0.0;
-            for (int i = lane; i < len; i += G) az_backup_node(nodes, s_path[i], ((len - 1 - i) & 1) ? -v : v, false, l2keep);
+            if (best_mode) {
+                root_best = az_backup_best<G>(nodes, lane < len ? s_path[lane] : 0u, lane + 32 < len ? s_path[lane + 32] : 0u, len, v, 0,
+                                              f.use_noise ? f.root_prior64 + (size_t)tree * g.max_children : nullptr, lane, gmask, l2keep, &st_reads, s_rec);
+            } else {
+                for (int i = lane; i < len; i += G) az_backup_node(nodes, s_path[i], ((len - 1 - i) & 1) ? -v : v, false, l2keep);
+            }
             __syncwarp(gmask);
             root_nv += 1;
             ++st_term;
@@ -629,6 +791,7 @@ __global__ void __launch_bounds__(128, 7) az_advance_kernel(AzForestDev f, int s
             if (found) ++st_hit;
             ready_hit = found == 2;
         }
+        AZ_AT(9);                                             // terminal test + path store + cache probe
         if (lane == np - flushed) {
             kept = b;
             kept_player = player;
@@ -1147,6 +1310,7 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     d.log_tab = nullptr;
     d.cache = AzCacheDev{};
     d.max_rounds = 1;
+    d.no_best = getenv("AZ_NO_BEST") ? 1 : 0;
     f->uid = ++g_forest_uid;
     f->max_iters = max_iters;
     // One warp per tree: sub-warp groups (8 lanes for the <= 9-children games) share a warp between
@@ -1161,6 +1325,7 @@ extern "C" int az_forest_create(int game, int rows, int cols, int n_trees, int m
     d.lp = lp;
     size_t per_group = 4 * (size_t)d.max_depth + lp * lm_bytes;
     f->smem_per_group = (int)((per_group + 15) & ~(size_t)15);
+    if (vl_batch == 1) f->smem_per_group += AZ_BEST_SMEM;     // path-node records of az_backup_best
     const size_t nodes = (size_t)n_trees * d.cap;
     const int nw = g.nw;
 #define AZ_ALLOC(ptr, count)                                  \

@@ -96,4 +96,5 @@ struct AzForestDev {
     unsigned long long* stats; // AZ_STAT_*
     AzCacheDev cache;
     int max_rounds;            // vl == 1 with the cache: simulations a tree may run in one launch while its leaves hit the cache
+    int no_best;               // A/B switch (AZ_NO_BEST=1): vl == 1 searches scan and score per level instead of following cached best children
 };

@@ -1,5 +1,5 @@
 """Phase clocks of az_advance_kernel over one whole search (library built with -DAZ_ADV_TRACE as
-tools/libaz_trace.so: nvcc ... -fmad=false -DAZ_ADV_TRACE -c az_forest.cu, linked with az_net.o).  usage: python tools/adv_trace.py [connect4|gomoku] [trees] [iters] [vl]"""
+tools/libaz_trace.so by tools/build_trace.sh).  usage: python tools/adv_trace.py [connect4|gomoku] [trees] [iters] [vl]"""
 import ctypes as C, sys, os
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -27,7 +27,7 @@ L = lib.load()
 L.az_debug_adv_trace.argtypes = [C.c_void_p, C.c_int]
 buf = np.zeros((8192, 16), np.uint64)
 names = ["tree scalars", "pend scalars+legal moves", "child block write", "backup", "root record", "select levels (sum)",
-         "leaf hand-off", "terminal backup", "tail"]
+         "leaf hand-off", "terminal backup", "tail (slot atomic + writes)", "terminal test + path store + cache probe"]
 for rep in range(2):
     planes, players, mcs = random_roots(G, n, 20 if game == "connect4" else 12, rng)
     forest.set_roots_planes(planes, players, mcs)
