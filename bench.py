@@ -60,7 +60,7 @@ def parse():
     ap.add_argument("--no-second-workload", action="store_true", help="skip the workloads.<other> sub-record")
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--no-cache", action="store_true", help="evaluation cache off (A/B)")
-    ap.add_argument("--selfplay-generations", type=float, default=2.0, help="whole games per slot in the self-play leg")
+    ap.add_argument("--selfplay-generations", type=float, default=6.0, help="whole games per slot in the self-play leg")
     return ap.parse_args()
 
 
