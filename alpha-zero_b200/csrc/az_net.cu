@@ -329,6 +329,7 @@ struct az_net {
     // scratch for the stand-alone forward (planes in, logits out)
     uint64_t* in_words = nullptr;
     uint8_t* in_player = nullptr;
+    float* in_planes = nullptr;          // host planes staged on the device (az_net_forward_planes), allocated on first use
     float *out_priors = nullptr, *out_values = nullptr, *out_logits = nullptr;
     unsigned long long launches = 0;     // kernels launched by forward passes
     unsigned long long weights_version = 0;   // changes with every az_net_finalize: tag of the forests' evaluation caches
@@ -438,6 +439,7 @@ extern "C" int az_net_finalize(az_net* n) {
     az_net_invalidate_graphs(n);
     for (void* p : n->allocs) cudaFree(p);
     n->allocs.clear();
+    n->in_planes = nullptr;
     const int D = n->D, T = n->T, C = n->C, P = n->patch, A = n->A, cells = n->rows * n->cols;
     std::string err;
     int rc;
@@ -1155,21 +1157,25 @@ extern "C" int az_net_forward_planes(az_net* n, const float* planes_host, int B,
     if (!n->finalized) return az_fail(AZ_ESTATE, "az_net_forward_planes: call az_net_finalize first");
     cudaStream_t s = (cudaStream_t)stream;
     const int cells = n->rows * n->cols, nw = cells <= 64 ? 1 : AZ_MAX_WORDS;
-    float* pl_dev = nullptr;
-    AZ_CUDA_OK(cudaMalloc(&pl_dev, (size_t)n->chunk * n->C * cells * 4));
+    // staging for the float planes: owned by the net (allocated at the first call, freed with it) -- a cudaMalloc /
+    // cudaFree pair per call synchronises the device and cost more than the forward pass of a small batch
+    if (!n->in_planes) {
+        int rc = az_net_alloc(n, &n->in_planes, (size_t)n->chunk * n->C * cells);
+        if (rc) return rc;
+    }
+    float* pl_dev = n->in_planes;
     for (int off = 0; off < B; off += n->chunk) {
         const int nb = std::min(n->chunk, B - off);
         AZ_CUDA_OK(cudaMemcpyAsync(pl_dev, planes_host + (size_t)off * n->C * cells, (size_t)nb * n->C * cells * 4, cudaMemcpyHostToDevice, s));
         az_planes_to_leaves_kernel<<<(nb * 2 * nw + 127) / 128, 128, 0, s>>>(pl_dev, nb, n->C, cells, nw, n->in_words, n->in_player);
         AzBatch b{nullptr, nb, 0, nb};
         int rc = az_net_forward_chunk(n, b, n->in_words, n->in_player, nw, n->out_priors, n->out_values, n->out_logits, s);
-        if (rc) { cudaFree(pl_dev); return rc; }
+        if (rc) return rc;
         if (logits_host) AZ_CUDA_OK(cudaMemcpyAsync(logits_host + (size_t)off * n->A, n->out_logits, (size_t)nb * n->A * 4, cudaMemcpyDeviceToHost, s));
         if (priors_host) AZ_CUDA_OK(cudaMemcpyAsync(priors_host + (size_t)off * n->A, n->out_priors, (size_t)nb * n->A * 4, cudaMemcpyDeviceToHost, s));
         if (values_host) AZ_CUDA_OK(cudaMemcpyAsync(values_host + off, n->out_values, (size_t)nb * 4, cudaMemcpyDeviceToHost, s));
         AZ_CUDA_OK(cudaStreamSynchronize(s));
     }
-    cudaFree(pl_dev);
     return AZ_OK;
 }
 
