@@ -910,6 +910,8 @@ __global__ void az_cache_publish_kernel(AzForestDev f, unsigned int* ticket) {
     }
 }
 
+__global__ void az_cache_tick_kernel(AzForestDev f) { *f.cache.epoch += 1u; }
+
 // splitmix64 finaliser; the build-defined hash evaluator (oracle/az_oracle.py: hash_eval_*).
 __device__ __forceinline__ uint64_t az_sm64(uint64_t x) {
     x += 0x9E3779B97F4A7C15ull;
@@ -1474,6 +1476,7 @@ extern "C" int az_forest_cache_config(az_forest* f, int log2_entries) {
 // Forget every cached answer (main.py:55-57 clears MCTS.cache after each model update).
 extern "C" int az_forest_cache_clear(az_forest* f, void* stream) {
     if (!f) return az_fail(AZ_EINVAL, "cache_clear: null");
+    f->eval_tag_set = false;                                  // an empty cache belongs to whichever evaluator fills it next
     if (!f->d.cache.cap) return AZ_OK;
     cudaStream_t s = (cudaStream_t)stream;
     if (cudaMemsetAsync(f->d.cache.state, 0, (size_t)f->d.cache.cap * 4, s) != cudaSuccess) return az_fail(AZ_ECUDA, "cache_clear: memset");
@@ -1492,9 +1495,10 @@ extern "C" int az_forest_cache_info(az_forest* f, long long* entries, long long*
 int az_forest_set_eval_tag(az_forest* f, unsigned long long tag, cudaStream_t s) {
     if (f->eval_tag_set && f->eval_tag == tag) return AZ_OK;
     const bool had = f->eval_tag_set;
+    const int rc = had ? az_forest_cache_clear(f, s) : AZ_OK;
     f->eval_tag = tag;
     f->eval_tag_set = true;
-    return had ? az_forest_cache_clear(f, s) : AZ_OK;
+    return rc;
 }
 // Step-by-step searches (az_forest_advance + an evaluator call): the evaluator must be the one the cache was filled by.
 int az_forest_check_eval_tag(az_forest* f, unsigned long long tag) {
@@ -1517,6 +1521,26 @@ unsigned long long az_hash_eval_tag(uint64_t seed, int qbits) {
 extern "C" int az_forest_set_evaluator(az_forest* f, unsigned long long id, void* stream) {
     if (!f) return az_fail(AZ_EINVAL, "set_evaluator: null");
     return az_forest_set_eval_tag(f, id, (cudaStream_t)stream);
+}
+
+int az_forest_cache_tick(az_forest* f, cudaStream_t s) {
+    if (!f->d.cache.cap) return AZ_OK;
+    az_cache_tick_kernel<<<1, 1, 0, s>>>(f->d);
+    return AZ_OK;
+}
+
+// vl == 1 with the cache: up to `rounds` simulations per tree and launch while the leaves hit the cache.  1 for lockstep
+// searches (see az_forest_cache_config); continuous self-play (az_selfplay_run_async_*) gains from more, because there a
+// tree that runs ahead starts its next search instead of waiting for the slowest one.
+extern "C" int az_forest_set_rounds(az_forest* f, int rounds) {
+    if (!f || rounds < 1 || rounds > 64) return az_fail(AZ_EINVAL, "set_rounds: 1 <= rounds <= 64");
+    rounds = (f->d.cache.cap && f->d.vl == 1) ? rounds : 1;
+    if (rounds != f->d.max_rounds) {
+        cudaDeviceSynchronize();
+        az_net_forget_forest(f->uid);                            // step graphs hold the forest's parameters by value
+        f->d.max_rounds = rounds;
+    }
+    return AZ_OK;
 }
 
 unsigned long long az_forest_uid(az_forest* f) { return f->uid; }

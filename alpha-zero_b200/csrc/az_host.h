@@ -21,3 +21,9 @@ int az_forest_use_device_noise(az_forest* f, int on);
 int az_forest_set_eval_tag(az_forest* f, unsigned long long tag, cudaStream_t s);
 int az_forest_check_eval_tag(az_forest* f, unsigned long long tag);
 int az_search_burst(const AzForestDev* d, int iters, int steps_done);   // launches to queue before polling the done counter
+struct az_selfplay;
+int az_selfplay_service(az_selfplay* sp, cudaStream_t s);        // az_selfplay.cu: finished slots move and re-arm (capturable)
+az_forest* az_selfplay_forest(az_selfplay* sp);
+void az_selfplay_count_plies(az_selfplay* sp, long long n);
+int az_forest_cache_tick(az_forest* f, cudaStream_t s);          // one unit of cache age without a synchronised begin_move (continuous plies)
+unsigned long long az_hash_eval_tag(uint64_t seed, int qbits);   // evaluator identity of the hash evaluator (az_eval_hash)

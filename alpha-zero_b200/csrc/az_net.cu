@@ -1301,6 +1301,67 @@ extern "C" int az_forest_search_net(az_forest* f, az_net* n, int iters, void* st
     return AZ_OK;
 }
 
+// Continuous self-play with the built-in net (az_selfplay.cu: az_selfplay_service): one CUDA graph holds `K` search steps
+// (advance + evaluator) followed by the service kernels; it is replayed until every game is over.  No tree waits for
+// another one: a slot whose search is finished moves and starts its next search at the next service point.
+extern "C" int az_selfplay_run_async_net(az_selfplay* sp, az_net* n, int iters, long long max_steps_arg, int resume, void* stream) {
+    if (!sp || !n || iters < 1) return az_fail(AZ_EINVAL, "az_selfplay_run_async_net: bad arguments");
+    if (!n->finalized) return az_fail(AZ_ESTATE, "az_selfplay_run_async_net: call az_net_finalize first");
+    az_forest* f = az_selfplay_forest(sp);
+    AzForestDev* d = az_forest_dev(f);
+    if (iters > d->iters && iters > 0) { /* begin_move below checks against the forest's max_iters */ }
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!s) {
+        if (!g_own_stream) AZ_CUDA_OK(cudaStreamCreateWithFlags(&g_own_stream, cudaStreamNonBlocking));
+        AZ_CUDA_OK(cudaStreamSynchronize(0));
+        s = g_own_stream;
+    }
+    int rc;
+    if (!resume) {                                                       // resume: the slots continue the searches a budgeted call left
+        if ((rc = az_selfplay_prepare(sp, s))) return rc;                // root noise of the first plies (and use_noise before capture)
+        if ((rc = az_forest_set_eval_tag(f, n->weights_version, s))) return rc;
+        if ((rc = az_forest_begin_move(f, iters, s))) return rc;
+    }
+    if ((rc = az_step_eager(n, f, s))) return rc;                        // warm-up outside capture (function attributes)
+    if ((rc = az_selfplay_service(sp, s))) return rc;
+    int K = 4;                                                           // search steps per service point
+    if (const char* e = getenv("AZ_ASYNC_STEPS")) K = std::max(1, std::min(64, atoi(e)));
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    AZ_CUDA_OK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    const unsigned long long before = n->launches;
+    for (int i = 0; i < K && !rc; ++i) rc = az_step_eager(n, f, s);
+    if (!rc) rc = az_selfplay_service(sp, s);
+    const unsigned long long per_graph = n->launches - before;
+    cudaError_t ce = cudaStreamEndCapture(s, &graph);
+    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+    if (ce != cudaSuccess) return az_fail(AZ_ECUDA, std::string("async graph capture: ") + cudaGetErrorString(ce));
+    ce = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ce != cudaSuccess) return az_fail(AZ_ECUDA, std::string("async graph instantiate: ") + cudaGetErrorString(ce));
+    long long steps = 1 + K;
+    int live = 1;
+    const long long max_steps = (long long)d->g.state_dim * (iters + 2) * 64 + 1024;   // per slot generation; the loop also ends on live == 0
+    long long since_tick = steps, guard = 0;
+    while (live > 0) {
+        int burst = std::max(1, 64 / K);                                 // ~64 steps between two looks at the counters
+        if (max_steps_arg > 0) burst = (int)std::max<long long>(1, std::min<long long>(burst, (max_steps_arg - steps + K - 1) / K));
+        for (int i = 0; i < burst; ++i) {
+            ce = cudaGraphLaunch(exec, s);
+            if (ce != cudaSuccess) { cudaGraphExecDestroy(exec); return az_fail(AZ_ECUDA, std::string("async graph launch: ") + cudaGetErrorString(ce)); }
+            n->launches += per_graph;
+            steps += K;
+            since_tick += K;
+            if (since_tick >= iters) { az_forest_cache_tick(f, s); since_tick = 0; }
+        }
+        if (max_steps_arg > 0 && steps >= max_steps_arg) break;          // budgeted run (benchmarks): the caller resumes or reads what is there
+        if ((rc = az_selfplay_status(sp, nullptr, nullptr, &live, nullptr, s))) { cudaGraphExecDestroy(exec); return rc; }
+        if (++guard > max_steps) { cudaGraphExecDestroy(exec); return az_fail(AZ_ESTATE, "az_selfplay_run_async_net: did not converge"); }
+    }
+    cudaGraphExecDestroy(exec);
+    return (int)std::min<long long>(steps, 0x7fffffff);
+}
+
 extern "C" int az_net_invalidate_graphs(az_net* n) {
     auto it = g_graphs.find(n);
     if (it != g_graphs.end()) {

@@ -37,6 +37,7 @@ struct AzSelfplayDev {
     int* g_plies;             // [n_games] plies of the finished game (= stones on its final board), 0 = not finished
     int* g_winner;            // [n_games] 0 / 1, -1 = draw (check_winner's convention), -2 = not finished
     int* g_first;             // [n_games] first recorded ply: 0, or the move count of an adopted root (az_selfplay_begin)
+    uint8_t* need_noise;      // [n_trees] continuous plies: the slot has a new root whose Dirichlet noise is not drawn yet
 };
 
 namespace {
@@ -96,11 +97,8 @@ __global__ void az_selfplay_begin_kernel(AzForestDev f, AzSelfplayDev sp, int ad
 
 // One thread per slot, after a search: record the position, choose and apply the move, finish / refill the slot.
 template <int NW>
-__global__ void az_selfplay_move_kernel(AzForestDev f, AzSelfplayDev sp) {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= f.n_trees) return;
+__device__ __forceinline__ void az_selfplay_move_slot(const AzForestDev& f, const AzSelfplayDev& sp, int s) {
     int k = sp.slot_game[s];
-    if (k < 0) return;
     const AzGame& g = f.g;
     const int A = g.action_dim;
     const AzNode* nodes = f.nodes + (size_t)s * f.cap;
@@ -197,6 +195,39 @@ __global__ void az_selfplay_move_kernel(AzForestDev f, AzSelfplayDev sp) {
     }
 }
 
+// Lockstep plies: every live slot moves (the search of ALL trees has finished).
+template <int NW>
+__global__ void az_selfplay_move_kernel(AzForestDev f, AzSelfplayDev sp) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= f.n_trees || sp.slot_game[s] < 0) return;
+    az_selfplay_move_slot<NW>(f, sp, s);
+}
+
+// Continuous plies: a slot whose search has finished (done_flag, set by az_advance_kernel) moves NOW and starts its next
+// search -- fresh root, no subtree reuse (gomoku.py:134) -- while the other slots keep searching; nobody waits for the
+// slowest tree of a ply.  A game's trajectory does not depend on the schedule: search, noise and move sampling are
+// functions of (game id, ply).  The re-arming is what az_begin_move_kernel does for every tree at once.
+template <int NW>
+__global__ void az_selfplay_service_kernel(AzForestDev f, AzSelfplayDev sp) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= f.n_trees || sp.slot_game[s] < 0 || !f.done_flag[s]) return;
+    az_selfplay_move_slot<NW>(f, sp, s);
+    if (sp.slot_game[s] < 0) return;                              // retired: no game left for this slot
+    AzNode& root = f.nodes[(size_t)s * f.cap];
+    AzHot h;
+    h.N = 0; h.Q = 0.f; h.P = 0.f; h.V = 0;
+    AzMeta m;
+    m.child_base = 0; m.action = 0; m.nchild = 0; m.status = AZ_ST_LEAF;
+    root.hot = h;
+    root.meta = m;
+    root.W = 0.0;
+    f.n_nodes[s] = 1;
+    f.sims_done[s] = 0;
+    f.n_pending[s] = 0;
+    f.done_flag[s] = 0;
+    sp.need_noise[s] = 1;
+}
+
 // Gamma(alpha) for alpha < 1 as Gamma(alpha + 1) * U^(1/alpha) (Marsaglia & Tsang 2000 for the shape >= 1 part).
 // NumPy's legacy generator uses a different algorithm for the same distribution (utils.py:21): statistical parity.
 __device__ double az_gamma_small(uint64_t seed, uint32_t gid, uint32_t ply, uint32_t a, double alpha) {
@@ -221,11 +252,16 @@ __device__ double az_gamma_small(uint64_t seed, uint32_t gid, uint32_t ply, uint
 }
 
 // One warp per slot: noise[a] = g_a / sum g, g_a ~ Gamma(alpha): np.random.dirichlet([alpha] * A) (utils.py:21).
-__global__ void az_selfplay_noise_kernel(AzForestDev f, AzSelfplayDev sp, double* noise, double alpha) {
+__global__ void az_selfplay_noise_kernel(AzForestDev f, AzSelfplayDev sp, double* noise, double alpha, int only_flagged) {
     const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (s >= f.n_trees) return;
     const int k = sp.slot_game[s];
     if (k < 0) return;
+    if (only_flagged) {                                           // continuous plies: only the slots that have just moved
+        if (!sp.need_noise[s]) return;
+        __syncwarp();
+        if (lane == 0) sp.need_noise[s] = 0;
+    }
     const int A = f.g.action_dim;
     const uint32_t gid = (uint32_t)(sp.id_first + k * sp.id_stride);
     const uint32_t ply = f.root_mc[s];
@@ -296,7 +332,7 @@ extern "C" int az_selfplay_create(az_forest* f, int n_games, int id_first, int i
               alloc((void**)&d.t_words, npos * 2 * fd->g.nw * 8) && alloc((void**)&d.t_visits, npos * fd->g.action_dim * 2) &&
               alloc((void**)&d.t_q, npos * 8) && alloc((void**)&d.t_action, npos * 2) && alloc((void**)&d.t_u, npos * 8) &&
               alloc((void**)&d.g_plies, (size_t)n_games * 4) && alloc((void**)&d.g_winner, (size_t)n_games * 4) &&
-              alloc((void**)&d.g_first, (size_t)n_games * 4);
+              alloc((void**)&d.g_first, (size_t)n_games * 4) && alloc((void**)&d.need_noise, (size_t)fd->n_trees);
     if (!ok || cudaMallocHost(&sp->h_counters, 64) != cudaSuccess) {
         cudaGetLastError();
         az_selfplay_destroy(sp);
@@ -304,6 +340,7 @@ extern "C" int az_selfplay_create(az_forest* f, int n_games, int id_first, int i
     }
     cudaMemset(d.counters, 0, 64);
     cudaMemset(d.slot_game, 0xff, (size_t)fd->n_trees * 4);
+    cudaMemset(d.need_noise, 0, (size_t)fd->n_trees);
     *out = sp;
     return AZ_OK;
 }
@@ -337,7 +374,7 @@ extern "C" int az_selfplay_prepare(az_selfplay* sp, void* stream) {
     fd = az_forest_dev(sp->f);
     const int warps_per_block = 4;
     az_selfplay_noise_kernel<<<(fd->n_trees + warps_per_block - 1) / warps_per_block, 32 * warps_per_block, 0, s>>>(
-        *fd, sp->d, az_forest_noise_dev(sp->f), sp->alpha);
+        *fd, sp->d, az_forest_noise_dev(sp->f), sp->alpha, 0);
     AZ_CUDA_OK(cudaGetLastError());
     sp->launches += 1;
     return AZ_OK;
@@ -355,6 +392,23 @@ extern "C" int az_selfplay_move(az_selfplay* sp, void* stream) {
     sp->launches += 1;
     return AZ_OK;
 }
+
+// Continuous plies: finished slots move and start their next search (+ their root noise).  Asynchronous, capturable.
+int az_selfplay_service(az_selfplay* sp, cudaStream_t s) {
+    AzForestDev* fd = az_forest_dev(sp->f);
+    const int n = fd->n_trees;
+    if (fd->g.nw == 1) az_selfplay_service_kernel<1><<<(n + 127) / 128, 128, 0, s>>>(*fd, sp->d);
+    else az_selfplay_service_kernel<AZ_MAX_WORDS><<<(n + 127) / 128, 128, 0, s>>>(*fd, sp->d);
+    sp->launches += 1;
+    if (sp->use_noise) {
+        az_selfplay_noise_kernel<<<(n + 3) / 4, 128, 0, s>>>(*fd, sp->d, az_forest_noise_dev(sp->f), sp->alpha, 1);
+        sp->launches += 1;
+    }
+    AZ_CUDA_OK(cudaGetLastError());
+    return AZ_OK;
+}
+az_forest* az_selfplay_forest(az_selfplay* sp) { return sp->f; }
+void az_selfplay_count_plies(az_selfplay* sp, long long n) { sp->plies_run += n; }
 
 // Synchronises `stream`.  started / finished games, live slots, positions recorded in finished games.
 extern "C" int az_selfplay_status(az_selfplay* sp, int* started, int* finished, int* live, long long* positions, void* stream) {
@@ -403,6 +457,28 @@ extern "C" int az_selfplay_run_net(az_selfplay* sp, az_net* net, int iters, int 
 extern "C" int az_selfplay_run_hash(az_selfplay* sp, int iters, uint64_t seed, int qbits, int max_plies, void* stream) {
     if (!sp) return az_fail(AZ_EINVAL, "az_selfplay_run_hash: null");
     return az_selfplay_run(sp, nullptr, seed, qbits, iters, max_plies, stream);
+}
+
+// Continuous plies with the hash evaluator (parity runs): advance + evaluate + service until every game is over.  Returns
+// the number of steps.  The slots are NOT in lockstep; trajectories equal those of az_selfplay_run_hash.
+extern "C" int az_selfplay_run_async_hash(az_selfplay* sp, int iters, uint64_t seed, int qbits, void* stream) {
+    if (!sp || iters < 1) return az_fail(AZ_EINVAL, "az_selfplay_run_async_hash: bad arguments");
+    int rc, live = 1, steps = 0;
+    if ((rc = az_selfplay_prepare(sp, stream))) return rc;
+    if ((rc = az_forest_set_eval_tag(sp->f, az_hash_eval_tag(seed, qbits), (cudaStream_t)stream))) return rc;
+    if ((rc = az_forest_begin_move(sp->f, iters, stream))) return rc;
+    const long long max_steps = (long long)sp->d.n_games * sp->d.max_plies * (iters + 2) + 64;
+    while (live > 0) {
+        for (int i = 0; i < 32; ++i) {
+            if ((rc = az_forest_advance(sp->f, stream))) return rc;
+            if ((rc = az_eval_hash(sp->f, seed, qbits, stream))) return rc;
+            if ((rc = az_selfplay_service(sp, (cudaStream_t)stream))) return rc;
+            if (++steps % iters == 0) az_forest_cache_tick(sp->f, (cudaStream_t)stream);
+        }
+        if ((rc = az_selfplay_status(sp, nullptr, nullptr, &live, nullptr, stream))) return rc;
+        if (steps > max_steps) return az_fail(AZ_ESTATE, "az_selfplay_run_async_hash: did not converge");
+    }
+    return steps;
 }
 
 // Device pointers of the trajectory store (library-owned, valid until az_selfplay_destroy), for zero-copy consumers

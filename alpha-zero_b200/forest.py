@@ -191,6 +191,10 @@ class Forest:
         """2**log2_entries entries; 0 turns the cache off (boards of <= 64 cells only)."""
         _lib.check(self._L.az_forest_cache_config(self.h, int(log2_entries)), "cache_config")
 
+    def set_rounds(self, rounds):
+        """vl == 1 with the cache: simulations a tree may run per launch while its leaves hit the cache."""
+        _lib.check(self._L.az_forest_set_rounds(self.h, int(rounds)), "set_rounds")
+
     def cache_clear(self):
         _lib.check(self._L.az_forest_cache_clear(self.h, self.stream), "cache_clear")
 

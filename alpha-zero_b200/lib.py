@@ -78,6 +78,9 @@ _SIGS.update({
     "az_selfplay_status": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(C.c_longlong), vp]),
     "az_selfplay_run_net": (i32, [vp, vp, i32, i32, vp]),
     "az_selfplay_run_hash": (i32, [vp, i32, u64, i32, i32, vp]),
+    "az_selfplay_run_async_net": (i32, [vp, vp, i32, C.c_longlong, i32, vp]),
+    "az_selfplay_run_async_hash": (i32, [vp, i32, u64, i32, vp]),
+    "az_forest_set_rounds": (i32, [vp, i32]),
     "az_selfplay_buffers": (i32, [vp, C.POINTER(vp), C.POINTER(i32), C.POINTER(i32)]),
     "az_selfplay_read": (i32, [vp] * 10),
     "az_selfplay_read_slots": (i32, [vp, vp, vp, vp]),

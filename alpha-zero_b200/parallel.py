@@ -122,6 +122,32 @@ def collect_data_distributed(Game, model, buffer, iterations, mcts_iter, vl=1, d
     return store_games(Game, buffer, games)
 
 
+def collect_data_device(Game, model, dbuffer, iterations, mcts_iter, vl=1, dirichlet=True, seed=0, concurrent=None):
+    """train.collect_data with everything resident in HBM: this rank plays its shard of `iterations` games on the device,
+    the compact trajectories are all-gathered over NCCL and appended to a DeviceReplayBuffer (canonicalisation, z and the
+    dihedral variants run as one kernel) in global game order -- no host copy of a position anywhere.  Every rank ends
+    with the same buffer.  Returns [wins of side 0, wins of side 1, draws] as train.collect_data does (train.py:69-73)."""
+    from .forest import game_spec
+    from .selfplay import play_games_device
+    rank, ws = world()
+    ids = shard_games(iterations, rank, ws)
+    g = game_spec(Game.name, Game.rows)
+    sp = None
+    if ids:
+        sp = play_games_device(Game, model, len(ids), mcts_iter, vl=vl, dirichlet=dirichlet, concurrent=concurrent, seed=seed,
+                               id_first=rank, id_stride=ws, return_engine=True)
+        local = sp.device_tensors()
+    else:
+        local = empty_trajectories(g, 0, "cuda")
+    merged = gather_trajectories(local, iterations)
+    dbuffer.add_trajectories(merged)
+    w = merged["winner"]
+    results = [int((w == 0).sum().item()), int((w == 1).sum().item()), int((w == -1).sum().item())]
+    if sp is not None:
+        sp.close()
+    return results
+
+
 def empty_trajectories(g, n, device="cpu"):
     P, A = g.state_dim, g.action_dim
     z = lambda shape, dt: torch.zeros(shape, dtype=dt, device=device)

@@ -66,11 +66,20 @@ class SelfPlayEngine:
                    "az_selfplay_status")
         return dict(started=a.value, finished=b.value, live=c.value, positions=d.value)
 
-    def run(self, model, iters, max_plies=0):
-        """Plays until all games are over (or max_plies searches).  model: ai.nn.B200Net or ai.mcts.HashEvaluator.
-        Returns the number of searches (plies of the longest slot history) run."""
+    def run(self, model, iters, max_plies=0, lockstep=False, max_steps=0, resume=False):
+        """Plays until all games are over.  model: ai.nn.B200Net or ai.mcts.HashEvaluator.
+        Default: continuous plies -- a slot whose search is finished moves and starts its next search at once, nobody waits
+        for the slowest tree (returns the search steps run).  lockstep=True (or max_plies > 0: stop after that many
+        searches) searches all slots together ply by ply (returns the searches run).  Both give the same trajectories."""
         from .ai.mcts import HashEvaluator
         from .ai.nn import B200Net
+        if not lockstep and not max_plies:
+            if isinstance(model, B200Net):
+                return _lib.check(self._L.az_selfplay_run_async_net(self.h, model.h, int(iters), int(max_steps), int(bool(resume)),
+                                                                    self.forest.stream), "az_selfplay_run_async_net")
+            if isinstance(model, HashEvaluator):
+                return _lib.check(self._L.az_selfplay_run_async_hash(self.h, int(iters), C.c_uint64(model.seed), int(model.qbits),
+                                                                     self.forest.stream), "az_selfplay_run_async_hash")
         if isinstance(model, B200Net):
             return _lib.check(self._L.az_selfplay_run_net(self.h, model.h, int(iters), int(max_plies), self.forest.stream), "az_selfplay_run_net")
         if isinstance(model, HashEvaluator):
@@ -167,7 +176,7 @@ def games_from_arrays(g, arr, return_visits=False):
 
 
 def play_games_device(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, concurrent=None, seed=None, id_first=0,
-                      id_stride=1, return_arrays=False, return_engine=False):
+                      id_stride=1, return_arrays=False, return_engine=False, lockstep=False):
     """n_games self-play games on the device, `concurrent` in flight.  model: torch Net / B200Net / HashEvaluator."""
     from .ai.mcts import MCTS, HashEvaluator
     slots = int(min(n_games, concurrent or n_games))
@@ -180,7 +189,7 @@ def play_games_device(Game, model, n_games, mcts_iter, vl=1, dirichlet=True, con
     sp = SelfPlayEngine(forest, n_games, seed, reference_sample_plies(Game, True), noise=dirichlet, id_first=id_first, id_stride=id_stride)
     forest.set_active(None)
     sp.begin()
-    sp.run(eng, mcts_iter)
+    sp.run(eng, mcts_iter, lockstep=lockstep)
     MCTS.mcts_count += mcts_iter * sp.status()["positions"]
     if return_engine:
         return sp

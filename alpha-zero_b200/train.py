@@ -203,6 +203,9 @@ def collect_data(Game, model, buffer, iterations, mcts_iter, display=False, vl=1
     return results
 
 
+last_stats = {}        # filled by train(): iterations, world, gradient bytes, all-reduce time left exposed (bench.py's train leg)
+
+
 class _PolicyValueLoss(torch.autograd.Function):
     """train.py:110-112 as ONE kernel (az_loss_policy_value, csrc/az_replay.cu): soft-target cross entropy + MSE, forward
     and backward together; returns (policy_loss, value_loss) and hands the stored gradients back in backward."""
@@ -254,6 +257,7 @@ class _GradBuckets:
                 cur, cur_hi = [], off
         self.of = {id(p): b for b in self.buckets for p in b["params"]}
         self.work = []
+        self.exposed = []                                 # CUDA event pairs around the waits of finish()
         self.hooks = [p.register_post_accumulate_grad_hook(self._ready) for p in params]
 
     def _ready(self, p):
@@ -268,8 +272,15 @@ class _GradBuckets:
             b["left"] = len(b["params"])
 
     def finish(self):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        timed = self.flat.is_cuda
+        if timed:
+            a.record()
         for w in self.work:
             w.wait()
+        if timed:
+            b.record()                                   # what of the all-reduces backward did not hide
+            self.exposed.append((a, b))
         self.work.clear()
         self.flat /= self.world
 
@@ -313,7 +324,12 @@ def train(model, batch_size, buffer, train_iterations, lr, device):
             print("train_iter:", i + 1, "loss:", loss.item(), "policy_loss:", policy_loss.item(), "value_loss:",
                   value_loss.item(), "l2_loss:", l2.item(), "time:", now - t0)
             t0 = now
+    last_stats.clear()
+    last_stats.update(iterations=train_iterations, batch_size=batch_size, world=dist.get_world_size() if ddp else 1,
+                      grad_bytes=sum(p.numel() * p.element_size() for p in model.parameters()))
     if buckets:
+        torch.cuda.synchronize()
+        last_stats.update(allreduce_exposed_ms=sum(a.elapsed_time(b) for a, b in buckets.exposed), buckets=len(buckets.buckets))
         buckets.close()
         for p in model.parameters():                    # leave ordinary, independent .grad tensors behind
             p.grad = None

@@ -39,6 +39,7 @@ WORKLOADS = {
                    name="gomoku_7x7_8192games_800sims_vl8_net512x1"),
 }
 NET = dict(dim=512, depth=1, patch=5, heads=8)          # main.py:134
+ROUNDS_CONTINUOUS = 4                                   # vl = 1, continuous plies: simulations per tree and launch while leaves hit the cache
 
 
 def parse():
@@ -60,6 +61,10 @@ def parse():
     ap.add_argument("--no-second-workload", action="store_true", help="skip the workloads.<other> sub-record")
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--no-cache", action="store_true", help="evaluation cache off (A/B)")
+    ap.add_argument("--lockstep", action="store_true", help="vl = 1: search all slots together ply by ply (A/B against continuous plies)")
+    ap.add_argument("--rounds", type=int, default=0, help="vl = 1: cached simulations per tree and launch in continuous self-play (0 = default)")
+    ap.add_argument("--no-train", action="store_true", help="skip the training leg (config 5)")
+    ap.add_argument("--train-iters", type=int, default=40, help="timed optimiser steps of the training leg")
     ap.add_argument("--selfplay-generations", type=float, default=6.0, help="whole games per slot in the self-play leg")
     return ap.parse_args()
 
@@ -282,50 +287,66 @@ def run_workload(args, wl, rank, world, steps, warmup, full):
 
     out = dict(workload=wl["name"], cache=forest.cache_info())
     clocks = ClockSampler(local) if full else None
-    # ---- value: device time, everything resident; successive plies of device-side self-play ----------------
+    # ---- value: device time, everything resident; continuous device-side self-play -------------------------
+    # K "steps" = K x iters search passes (one pass = advance + evaluator over all concurrent games); a slot whose
+    # search is finished moves and starts its next search at once, so the simulations done are counted, not assumed.
     total = warmup + steps
     planes, players, mcs = random_roots(G, n, wl["max_plies"], rng)
     forest.set_roots_planes(planes, players, mcs)                     # upload BEFORE the timed region
-    n_games = int(n * min(64, 2 + total // 5))                        # enough games to refill every finished slot
+    continuous = vl == 1 and not args.lockstep                        # measured: continuous plies gain 46 % at vl = 1 and lose 7 % at vl = 8
+    rounds = args.rounds or (ROUNDS_CONTINUOUS if continuous else 1)
+    forest.set_rounds(rounds)
+    n_games = int(n * (4 + total))                                    # enough games to refill every finished slot
     sp = SelfPlayEngine(forest, n_games, 1234, sample_plies, noise=True, id_first=rank, id_stride=world)
     sp.begin(adopt_roots=True)
-    ev, launches0, t_clock0 = [], 0, time.time()
-    i = 0
-    while True:
-        if i == warmup:
-            barrier()
-            forest.stats(reset=True)
-            t_clock0 = time.time()
-            launches0 = eng.launch_count() + sp.launch_count()
-        timed = i >= warmup
-        if timed:
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record(stream)
-        sp.prepare()                                                  # Dirichlet noise of the new roots (device)
-        forest.search_net(eng, iters)                                 # n x iters simulations
-        sp.move()                                                     # record, choose, apply, refill (device)
-        if timed:
-            b.record(stream)
-            ev.append((a, b))
-        i += 1
-        if i >= total:
-            if args.min_seconds <= 0:
-                break
-            torch.cuda.synchronize()
-            if sum(x.elapsed_time(y) for x, y in ev) >= args.min_seconds * 1e3 or i >= 64 * total:
-                break
+    ev, passes = [], 0
+
+    def lockstep_plies(k):                                            # all slots search together, then all move
+        for _ in range(k):
+            sp.prepare()                                              # Dirichlet noise of the new roots (device)
+            forest.search_net(eng, iters)                             # n x iters simulations
+            sp.move()                                                 # record, choose, apply, refill (device)
+    if continuous:
+        sp.run(eng, iters, max_steps=warmup * iters)                  # warm-up: graph capture, caches, clocks
+    else:
+        lockstep_plies(warmup)
     barrier()
-    steps_timed = len(ev)
+    forest.stats(reset=True)
+    t_clock0 = time.time()
+    launches0 = eng.launch_count() + sp.launch_count()
+    while True:
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        if continuous:
+            passes += sp.run(eng, iters, max_steps=steps * iters, resume=True)
+        else:
+            lockstep_plies(steps)
+        b.record(stream)
+        ev.append((a, b))
+        torch.cuda.synchronize()
+        if args.min_seconds <= 0 or sum(x.elapsed_time(y) for x, y in ev) >= args.min_seconds * 1e3 or len(ev) >= 64:
+            break
+    barrier()
+    steps_timed = steps * len(ev)
+    if not continuous:
+        passes = None
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
-    gpu_launches = eng.launch_count() + sp.launch_count() - launches0 + steps_timed     # + begin_move kernels
+    gpu_launches = eng.launch_count() + sp.launch_count() - launches0
     stats = forest.stats(reset=True)
     st = sp.status()
     assert st["live"] == n, f"self-play ran out of games ({st})"
-    assert stats["sims"] == n * iters * steps_timed, (stats["sims"], n * iters * steps_timed)
+    assert stats["sims"] >= 0.5 * n * iters * steps_timed, (stats["sims"], n * iters * steps_timed)
     sp.close()
     dev_ms, = max_over_ranks(dev_ms)
-    out.update(dev_ms=dev_ms, steps=steps_timed, sims_per_step=n * iters * world, gpu_launches=int(gpu_launches), stats=stats,
-               games_finished_in_value_leg=st["finished"])
+    sims_all = float(stats["sims"])
+    if world > 1:
+        tsum = torch.tensor([sims_all], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tsum)
+        sims_all = float(tsum.item())
+    out.update(dev_ms=dev_ms, steps=steps_timed, sims_timed=sims_all, search_passes=passes, rounds=rounds, continuous=continuous,
+               gpu_launches=int(gpu_launches),
+               stats=stats, games_finished_in_value_leg=st["finished"])
+    forest.set_rounds(1)                                              # the per-ply API below searches in lockstep
     # ---- e2e: wall clock through the public API with host buffers --------------------------------------------
     e2e_steps = args.e2e_steps or min(steps, 48)
     pinned = torch.empty((n, G.feature_dim, G.rows, G.cols), dtype=torch.float32).pin_memory()
@@ -361,7 +382,7 @@ def run_workload(args, wl, rank, world, steps, warmup, full):
     e2e_s, = max_over_ranks(e2e_s)
     t_clock1 = time.time()
     med = lambda xs: sorted(xs)[len(xs) // 2] * 1e3
-    out.update(e2e_s=e2e_s, e2e_steps=e2e_steps, h2d=int(pinned.numel() * 4 + n * 8 + n * A * 8), d2h=int(n * A * 4 + n * 8),
+    out.update(e2e_s=e2e_s, e2e_steps=e2e_steps, e2e_sims_per_step=n * iters * world, h2d=int(pinned.numel() * 4 + n * 8 + n * A * 8), d2h=int(n * A * 4 + n * 8),
                e2e_step_ms=dict(upload=round(med([p[0] for p in parts]), 3), search=round(med([p[1] for p in parts]), 3),
                                 readback=round(med([p[2] for p in parts]), 3), host_move=round(med([p[3] for p in parts]), 3)),
                e2e_stats=forest.stats(reset=True))
@@ -372,34 +393,93 @@ def run_workload(args, wl, rank, world, steps, warmup, full):
         per_rank = max(int(n * args.selfplay_generations), 1)
         games_total = per_rank * world
         sp2 = SelfPlayEngine(forest, per_rank, 4321, sample_plies, noise=True, id_first=rank, id_stride=world)
+        forest.set_rounds(rounds)
         forest.stats(reset=True)
+        # host side of the call: the model's weights live in host memory (a torch state_dict), the trajectories end in pinned host arrays
+        host_sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+        g_spec = forest.g
+        P_, A_ = g_spec.state_dim, g_spec.action_dim
+        pinned_out = dict(plies=torch.empty(games_total, dtype=torch.int32).pin_memory(), winner=torch.empty(games_total, dtype=torch.int32).pin_memory(),
+                          first=torch.empty(games_total, dtype=torch.int32).pin_memory(),
+                          words=torch.empty((games_total, P_, 2, g_spec.nw), dtype=torch.int64).pin_memory(),
+                          visits=torch.empty((games_total, P_, A_), dtype=torch.int16).pin_memory(),
+                          q=torch.empty((games_total, P_), dtype=torch.float64).pin_memory(),
+                          action=torch.empty((games_total, P_), dtype=torch.int16).pin_memory())
         barrier()
         t0 = time.perf_counter()
+        eng.load_state_dict(host_sd)                                  # H2D: weights -> tensor-core engine (new weights: cold evaluation cache)
+        tw = time.perf_counter()
         sp2.begin()
-        searches = sp2.run(eng, iters)                                # device-side self-play until every game is over
+        searches = sp2.run(eng, iters, lockstep=not continuous)       # device-side self-play until every game is over
         torch.cuda.synchronize()
         t1 = time.perf_counter()
         merged = parallel.gather_trajectories(sp2.device_tensors(), games_total)     # one all_gather_into_tensor (NCCL)
         torch.cuda.synchronize()
         t2 = time.perf_counter()
+        for k_, dst in pinned_out.items():                            # D2H: every rank reads all games (what fills its replay buffer)
+            dst.copy_(merged[k_], non_blocking=True)
+        torch.cuda.synchronize()
+        t2b = time.perf_counter()
         barrier()
         t3 = time.perf_counter()
         positions = int(merged["plies"].sum().item()) if world > 1 else sp2.status()["positions"]
         assert int((merged["winner"] == -2).sum().item()) == 0, "every gathered game must be finished"
         st2 = forest.stats(reset=True)
-        play_s, gather_s, total_s = max_over_ranks(t1 - t0, t2 - t1, t3 - t0)
-        out["selfplay"] = dict(games=games_total, games_per_rank=per_rank, concurrent_per_gpu=n, positions=positions, searches_per_rank=searches,
+        play_s, gather_s, total_s, upload_s, d2h_s = max_over_ranks(t1 - tw, t2 - t1, t3 - t0, tw - t0, t2b - t2)
+        h2d_bytes = int(sum(v.numel() * v.element_size() for v in host_sd.values()))
+        d2h_bytes = int(sum(v.numel() * v.element_size() for v in pinned_out.values()))
+        forest.set_rounds(1)
+        out["selfplay"] = dict(games=games_total, games_per_rank=per_rank, concurrent_per_gpu=n, positions=positions, search_passes_per_rank=searches,
+                               cached_sims_per_launch=rounds,
                                seconds=total_s, play_seconds=play_s, gather_seconds=gather_s, gather_share=gather_s / total_s,
+                               weight_upload_seconds=upload_s, d2h_seconds=d2h_s, h2d_bytes=h2d_bytes, d2h_bytes=d2h_bytes,
                                gather_bytes_per_rank=int(sum(v.numel() * v.element_size() for k, v in merged.items()) // world),
                                games_per_s=games_total / total_s, positions_per_s=positions / total_s,
                                simulations_per_s=positions * iters / total_s, sims_per_move=iters,
                                cache_hit_rate=st2["cache_hits"] / max(st2["expansions"], 1),
                                evaluator_rows_per_sim=(st2["expansions"] - st2["cache_hits"]) / max(st2["sims"], 1),
                                how="selfplay.SelfPlayEngine: every game from the empty board to its end on the device (Dirichlet noise, "
-                                   "moves sampled / first-max as the reference, slots refilled until all games have started, so the batch "
-                                   "thins out only at the end), then parallel.gather_trajectories: one all_gather_into_tensor of the compact "
+                                   "moves sampled / first-max as the reference; continuous plies: a slot moves when ITS search is finished; "
+                                   "slots refilled until all games have started, so the batch thins out only at the end), then "
+                                   "parallel.gather_trajectories: one all_gather_into_tensor of the compact "
                                    "trajectories; max over ranks")
-        del merged
+        # ---- config 5: the gathered games -> device replay buffer -> train.train with the gradient all-reduce ---------
+        if not args.no_train:
+            import copy
+            from alpha_zero_b200.replay_buffer import DeviceReplayBuffer
+            dbuf = DeviceReplayBuffer(G, 4_000_000, seed=100 + rank)      # every rank draws its own batches
+            torch.cuda.synchronize()
+            ta = time.perf_counter()
+            added = dbuf.add_trajectories(merged)                     # z, canonical boards, dihedral variants: one kernel
+            torch.cuda.synchronize()
+            add_s = time.perf_counter() - ta
+            tmodel = copy.deepcopy(model)
+            B, T = 512, args.train_iters                              # main.py:153 batch, train.py:93 lr below
+            az_train.train(tmodel, B, dbuf, 3, 2.5e-4, "cuda")        # warm-up (cuDNN / cuBLAS plans, NCCL channels)
+            barrier()
+            tb = time.perf_counter()
+            losses = az_train.train(tmodel, B, dbuf, T, 2.5e-4, "cuda")
+            torch.cuda.synchronize()
+            barrier()
+            train_s, = max_over_ranks(time.perf_counter() - tb)
+            ts = dict(az_train.last_stats)
+            tu = time.perf_counter()
+            eng.load_state_dict(tmodel.state_dict())                  # new weights into the inference engine (clears the evaluation cache)
+            torch.cuda.synchronize()
+            upload_s = time.perf_counter() - tu
+            out["train"] = dict(samples_per_s=B * world * T / train_s, iterations=T, batch_per_gpu=B, seconds=train_s,
+                                ms_per_iteration=train_s / T * 1e3, buffer_entries=dbuf.size(), entries_added=added,
+                                entry_bytes=dbuf.entry_bytes(), add_entries_per_s=added / max(add_s, 1e-9),
+                                grad_bytes=ts.get("grad_bytes"), allreduce_buckets=ts.get("buckets", 0),
+                                allreduce_exposed_share=(ts.get("allreduce_exposed_ms", 0.0) / 1e3) / train_s,
+                                weight_upload_s=upload_s, loss=losses[0], policy_loss=losses[1], value_loss=losses[2],
+                                how="replay_buffer.DeviceReplayBuffer.add_trajectories on the all-gathered games, then train.train "
+                                    "(train.py:85-123: Adam lr 2.5e-4, soft-target CE + MSE fused kernel + 1e-4 L2, batch 512 per GPU "
+                                    "sampled on the device, bucketed NCCL all-reduce overlapped with backward), then the weights are "
+                                    "uploaded to the tensor-core engine; torch (cuDNN / cuBLAS) runs the Net's forward and backward")
+            dbuf.close()
+            del tmodel
+        del merged, pinned_out
         sp2.close()
     # ---- per-kernel profile (rank 0): eager steps of one search with CUDA events ------------------------------
     if rank == 0 and full and not args.no_profile:
@@ -408,6 +488,8 @@ def run_workload(args, wl, rank, world, steps, warmup, full):
         forest.set_roots_planes(planes, players, mcs)
         forest.set_noise(None)
         forest.stats(reset=True)
+        forest.cache_clear()                                          # the training leg changed the weights: step-by-step callers say so
+        forest.set_rounds(rounds)                                     # the launches profiled are the launches timed above
         forest.begin_move(iters)
         adv, lv, per_step = [], [], {}
         eng.profile(True)
@@ -455,13 +537,27 @@ def run_workload(args, wl, rank, world, steps, warmup, full):
 
 def summarize(args, wl, r, world, pk):
     """JSON fields of one workload from run_workload's raw numbers."""
-    value = r["sims_per_step"] * r["steps"] / (r["dev_ms"] / 1e3)
-    e2e = r["sims_per_step"] * r["e2e_steps"] / r["e2e_s"]
+    value = r["sims_timed"] / (r["dev_ms"] / 1e3)
+    e2e = r["e2e_sims_per_step"] * r["e2e_steps"] / r["e2e_s"]
     st, es = r["stats"], r["e2e_stats"]
+    per_ply = dict(value=e2e, unit="simulations/s", h2d_bytes_per_step=r["h2d"], d2h_bytes_per_step=r["d2h"], steps=r["e2e_steps"],
+                   step_ms_median=r["e2e_step_ms"], cache_hit_rate=es["cache_hits"] / max(es["expansions"], 1),
+                   how="MCTS.mcts_batch-style use: every ply the caller uploads its float32 root planes + Dirichlet noise from pinned host "
+                       "memory, searches all games in lockstep, reads visit counts + root Q back and applies the moves on the host")
+    if "selfplay" in r:                                               # the call a user of the reference makes: collect_data(model) -> games
+        sp_ = r["selfplay"]
+        e2e_rec = dict(value=sp_["simulations_per_s"], unit="simulations/s", h2d_bytes_per_step=sp_["h2d_bytes"], d2h_bytes_per_step=sp_["d2h_bytes"],
+                       steps=1, games_per_s=sp_["games_per_s"],
+                       how="one call = train.collect_data's work through the public API: the model's state_dict is uploaded from host memory, "
+                           f"{sp_['games']} whole games are played on the device(s), the trajectories are all-gathered and copied to pinned host "
+                           "memory; wall clock over all of it, max over ranks (details under `selfplay`)", per_ply_api=per_ply)
+    else:
+        e2e_rec = per_ply
     d = dict(workload=wl["name"], value=value, unit="simulations/s", ms_per_step=r["dev_ms"] / r["steps"], steps=r["steps"],
-             e2e=dict(value=e2e, unit="simulations/s", h2d_bytes_per_step=r["h2d"], d2h_bytes_per_step=r["d2h"], steps=r["e2e_steps"],
-                      step_ms_median=r["e2e_step_ms"], cache_hit_rate=es["cache_hits"] / max(es["expansions"], 1)),
-             gpu_launches=r["gpu_launches"], search_stats=st,
+             e2e=e2e_rec,
+             gpu_launches=r["gpu_launches"], search_stats=st, search_passes=r["search_passes"], cached_sims_per_launch=r["rounds"],
+             plies="continuous" if r["continuous"] else "lockstep",
+             sims_per_pass_per_game=(st["sims"] / r["search_passes"] / wl["trees"]) if r["search_passes"] else None,
              eval_cache=dict(entries=r["cache"]["entries"], bytes=r["cache"]["bytes"], hit_rate=st["cache_hits"] / max(st["expansions"], 1),
                              evaluator_rows_per_sim=(st["expansions"] - st["cache_hits"]) / max(st["sims"], 1),
                              note="MCTS.cache analogue (ai/mcts.py:37-51): hits = leaves answered without an evaluator row"))
@@ -469,6 +565,8 @@ def summarize(args, wl, r, world, pk):
         d["clocks"] = r["clocks"]
     if "selfplay" in r:
         d["selfplay"] = r["selfplay"]
+    if "train" in r:
+        d["train"] = r["train"]
     prof = r.get("profile", {})
     if prof:
         rr = dict(r, stats=r["profile_stats"])
@@ -485,8 +583,10 @@ def config_of(wl, world):
     return dict(workload=wl["name"], game=wl["game"], board=f"{wl['rows']}x{7 if wl['game'] == 'connect4' else wl['rows']}",
                 concurrent_games_per_gpu=wl["trees"], sims_per_move=wl["iters"], vl_batch=wl["vl"],
                 net="Net(D=512,patch=5,heads=8,depth=1) random-init, ai/nn.py / main.py:134",
-                steps="successive plies of device-side self-play: games start from synthetic positions of 0..max_plies random plies, "
-                      "finished games restart from the empty board; Dirichlet noise on, moves sampled / first-max as the reference",
+                steps="device-side self-play from synthetic positions of 0..max_plies random plies, finished games restart from the empty board, "
+                      "Dirichlet noise on, moves sampled / first-max as the reference.  vl 1: continuous plies, one step = sims_per_move search "
+                      "passes (advance + evaluator over all concurrent games), a slot moves when its own search is finished; vl > 1: lockstep, "
+                      "one step = one ply of every game.  value = simulations completed (device counters) / device time",
                 l2="inputs larger than L2: forest node pools + activations >> 126 MB, every step searches new root positions",
                 parallelism=f"dp{world} (games sharded per GPU; no collective inside a search; selfplay leg: one NCCL all-gather of trajectories)")
 

@@ -112,8 +112,11 @@ AZ_API int az_forest_info(az_forest* f, int* n_trees, int* action_dim, int* plan
  * for a deterministic evaluator (search_stats[7] counts the hits).  On by default for boards of <= 64 cells
  * (AZ_NO_CACHE=1 turns it off); log2_entries = 0 removes it.  Entries unused for 2 searches are recycled. */
 AZ_API int az_forest_cache_config(az_forest* f, int log2_entries);
-AZ_API int az_forest_cache_clear(az_forest* f, void* stream);
+AZ_API int az_forest_cache_clear(az_forest* f, void* stream);   /* also forgets which evaluator filled it */
 AZ_API int az_forest_cache_info(az_forest* f, long long* entries, long long* bytes);
+/* vl_batch == 1 with the cache: up to `rounds` simulations per tree and launch while its leaves hit the cache (default 1:
+ * lockstep searches gain nothing from more; continuous self-play does). */
+AZ_API int az_forest_set_rounds(az_forest* f, int rounds);
 /* Names the evaluator whose answers may be cached from now on (any id that changes with the evaluator or its weights);
  * a different id drops the cached answers.  az_forest_search_{hash,net} do this themselves; step-by-step callers
  * (az_forest_advance + an evaluator) call it before az_forest_begin_move when they switch evaluators. */
@@ -142,6 +145,12 @@ AZ_API int az_selfplay_status(az_selfplay* sp, int* started, int* finished, int*
 /* Plays until every game has finished or max_plies searches were run (0 = no limit); returns the searches run. */
 AZ_API int az_selfplay_run_net(az_selfplay* sp, az_net* net, int iters, int max_plies, void* stream);
 AZ_API int az_selfplay_run_hash(az_selfplay* sp, int iters, uint64_t seed, int qbits, int max_plies, void* stream);
+/* Continuous plies: the same games without lockstep -- a slot whose search is finished moves and starts its next search
+ * while the others keep searching (nobody waits for the slowest tree of a ply).  Trajectories are identical to the
+ * lockstep run (search, noise and move sampling are functions of (game id, ply)).  Returns the search steps run. */
+/* max_steps > 0: return after that many search steps (benchmarks); resume != 0: continue the searches such a call left. */
+AZ_API int az_selfplay_run_async_net(az_selfplay* sp, az_net* net, int iters, long long max_steps, int resume, void* stream);
+AZ_API int az_selfplay_run_async_hash(az_selfplay* sp, int iters, uint64_t seed, int qbits, void* stream);
 /* Trajectories, positions indexed [game][ply] with max_plies = rows*cols per game.  Device pointers (library-owned):
  * out8 = {plies i32[G], winner i32[G] (0/1, -1 draw, -2 unfinished), words u64[G][P][2][nw], visits u16[G][P][A],
  * q f64[G][P], action(cell) i16[G][P], uniform f64[G][P] (-1 = argmax ply), first recorded ply i32[G]}. */

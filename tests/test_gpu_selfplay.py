@@ -257,3 +257,119 @@ def test_nccl_gather_fills_identical_buffers_on_all_gpus():
         h.update(np.ascontiguousarray(p, np.float64).tobytes())
         h.update(np.asarray(z, np.float64).tobytes())
     assert (h.hexdigest(), buf.size(), tuple(res)) == out[0]
+
+
+# ---- NCCL, config 5: device buffer filled from the gathered games, gradient all-reduce keeps the replicas identical ----
+def _device_buffer_digest(dbuf):
+    import hashlib
+    h = hashlib.sha256()
+    for x in dbuf.read():
+        h.update(np.ascontiguousarray(x.cpu().numpy()).tobytes())
+    return h.hexdigest()
+
+
+def _nccl_train_worker(rank, world, port, out):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from alpha_zero_b200 import parallel, train
+    from alpha_zero_b200.ai import HashEvaluator, Net
+    from alpha_zero_b200.games import Gomoku
+    from alpha_zero_b200.replay_buffer import DeviceReplayBuffer
+    dbuf = DeviceReplayBuffer(Gomoku, 100000, seed=50 + rank)         # same content everywhere, different batches per rank
+    res = parallel.collect_data_device(Gomoku, HashEvaluator(4, 12), dbuf, 21, 32, seed=1234, concurrent=4)
+    digest = _device_buffer_digest(dbuf)
+    torch.manual_seed(0)
+    net = Net((7, 7), 3, 64, 49, 8, 1, 2, dropout=0.0)
+    before = torch.cat([p.detach().reshape(-1) for p in net.parameters()]).clone()
+    train.train(net, 32, dbuf, 3, 1e-3, "cuda")
+    flat = torch.cat([p.detach().reshape(-1) for p in net.parameters()])
+    gathered = [torch.empty_like(flat) for _ in range(world)]
+    dist.all_gather(gathered, flat)
+    same = all(torch.equal(gathered[0], t) for t in gathered)
+    moved = not torch.equal(flat.cpu(), before)
+    out[rank] = (digest, dbuf.size(), tuple(res), same, moved, train.last_stats.get("buckets", 0) >= 1)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_nccl_device_buffer_and_gradient_all_reduce():
+    import torch
+    import torch.multiprocessing as mp
+    world = torch.cuda.device_count()
+    if world < 2:
+        pytest.skip("needs >= 2 GPUs")
+    game_cls(orc.GOMOKU)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    out = mp.Manager().dict()
+    mp.spawn(_nccl_train_worker, args=(world, port, out), nprocs=world, join=True)
+    assert len({v[:3] for v in out.values()}) == 1, dict(out)       # identical buffers and results on every rank
+    assert all(v[3] and v[4] and v[5] for v in out.values()), dict(out)   # replicas identical, weights moved, buckets reduced
+    from alpha_zero_b200 import parallel
+    from alpha_zero_b200.ai import HashEvaluator
+    from alpha_zero_b200.games import Gomoku
+    from alpha_zero_b200.replay_buffer import DeviceReplayBuffer
+    dbuf = DeviceReplayBuffer(Gomoku, 100000, seed=1)               # one process, same seed: the same buffer (rank-count independent)
+    res = parallel.collect_data_device(Gomoku, HashEvaluator(4, 12), dbuf, 21, 32, seed=1234, concurrent=4)
+    assert (_device_buffer_digest(dbuf), dbuf.size(), tuple(res)) == out[0][:3]
+    dbuf.close()
+
+
+def test_collect_data_device_single_gpu_matches_host_buffer():
+    """Same games through the host path (collect_data_distributed -> save_data_to_buffer) and the device path."""
+    from alpha_zero_b200 import parallel
+    from alpha_zero_b200.ai import HashEvaluator
+    from alpha_zero_b200.replay_buffer import DeviceReplayBuffer, ReplayBuffer
+    for g in (orc.GOMOKU, orc.CONNECT4):
+        G = game_cls(g)
+        dbuf = DeviceReplayBuffer(G, 100000, seed=1)
+        r1 = parallel.collect_data_device(G, HashEvaluator(7, 10), dbuf, 12, 24, seed=99, concurrent=5)
+        hbuf = ReplayBuffer(100000)
+        r2 = parallel.collect_data_distributed(G, HashEvaluator(7, 10), hbuf, 12, 24, seed=99, concurrent=5)
+        assert list(r1) == list(r2) and dbuf.size() == hbuf.size()
+        s, p, z = (x.cpu().numpy() for x in dbuf.read())
+        assert np.array_equal(s, np.stack([e[0] for e in hbuf.buffer]))
+        assert np.array_equal(p, np.stack([e[1] for e in hbuf.buffer]).astype(np.float32))
+        assert np.array_equal(z[:, 0], np.asarray([e[2][0] for e in hbuf.buffer], np.float32))
+        dbuf.close()
+
+
+@pytest.mark.parametrize("name,vl,rounds", [("connect4", 1, 1), ("connect4", 1, 4), ("gomoku", 1, 3), ("gomoku", 8, 1), ("tictactoe", 1, 2)])
+def test_continuous_plies_give_the_lockstep_trajectories(name, vl, rounds):
+    """az_selfplay_run_async_*: slots move as soon as their own search is finished.  A game's trajectory is a function of
+    (game id, ply) only, so it must equal the lockstep run bit for bit -- with several cached simulations per launch too."""
+    from alpha_zero_b200.ai import HashEvaluator, MCTS
+    from alpha_zero_b200.selfplay import play_games_device
+    g = {"tictactoe": orc.TICTACTOE, "connect4": orc.CONNECT4, "gomoku": orc.GOMOKU}[name]
+    G = game_cls(g)
+    ev = HashEvaluator(13, 10)
+    iters = 48
+    MCTS._forest_for(G, 7, iters, vl).set_rounds(1)
+    lock = play_games_device(G, ev, 30, iters, vl=vl, seed=5, concurrent=7, return_arrays=True, lockstep=True)
+    MCTS._forest_for(G, 7, iters, vl).set_rounds(rounds)
+    cont = play_games_device(G, ev, 30, iters, vl=vl, seed=5, concurrent=7, return_arrays=True)
+    MCTS._forest_for(G, 7, iters, vl).set_rounds(1)
+    for k in ("plies", "winner", "first", "words", "visits", "q", "action"):
+        assert np.array_equal(lock[k], cont[k]), k
+    assert (lock["plies"] > 0).all()
+
+
+def test_continuous_plies_with_the_net_match_lockstep():
+    import torch
+    from alpha_zero_b200.ai import Net, MCTS
+    from alpha_zero_b200.selfplay import play_games_device
+    G = game_cls(orc.CONNECT4)
+    torch.manual_seed(3)
+    net = Net((G.rows, G.cols), 5, 128, G.action_dim, 8, 1, G.feature_dim, dropout=0.0).eval()
+    lock = play_games_device(G, net, 40, 64, seed=8, concurrent=16, return_arrays=True, lockstep=True)
+    MCTS._forest_for(G, 16, 64, 1).set_rounds(4)
+    cont = play_games_device(G, net, 40, 64, seed=8, concurrent=16, return_arrays=True)
+    MCTS._forest_for(G, 16, 64, 1).set_rounds(1)
+    for k in ("plies", "winner", "words", "visits", "q", "action"):
+        assert np.array_equal(lock[k], cont[k]), k
