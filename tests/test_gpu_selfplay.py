@@ -350,11 +350,8 @@ def test_continuous_plies_give_the_lockstep_trajectories(name, vl, rounds):
     G = game_cls(g)
     ev = HashEvaluator(13, 10)
     iters = 48
-    MCTS._forest_for(G, 7, iters, vl).set_rounds(1)
     lock = play_games_device(G, ev, 30, iters, vl=vl, seed=5, concurrent=7, return_arrays=True, lockstep=True)
-    MCTS._forest_for(G, 7, iters, vl).set_rounds(rounds)
-    cont = play_games_device(G, ev, 30, iters, vl=vl, seed=5, concurrent=7, return_arrays=True)
-    MCTS._forest_for(G, 7, iters, vl).set_rounds(1)
+    cont = play_games_device(G, ev, 30, iters, vl=vl, seed=5, concurrent=7, return_arrays=True, rounds=rounds)
     for k in ("plies", "winner", "first", "words", "visits", "q", "action"):
         assert np.array_equal(lock[k], cont[k]), k
     assert (lock["plies"] > 0).all()
@@ -368,8 +365,6 @@ def test_continuous_plies_with_the_net_match_lockstep():
     torch.manual_seed(3)
     net = Net((G.rows, G.cols), 5, 128, G.action_dim, 8, 1, G.feature_dim, dropout=0.0).eval()
     lock = play_games_device(G, net, 40, 64, seed=8, concurrent=16, return_arrays=True, lockstep=True)
-    MCTS._forest_for(G, 16, 64, 1).set_rounds(4)
-    cont = play_games_device(G, net, 40, 64, seed=8, concurrent=16, return_arrays=True)
-    MCTS._forest_for(G, 16, 64, 1).set_rounds(1)
+    cont = play_games_device(G, net, 40, 64, seed=8, concurrent=16, return_arrays=True)          # default: 4 cached simulations per launch
     for k in ("plies", "winner", "words", "visits", "q", "action"):
         assert np.array_equal(lock[k], cont[k]), k
