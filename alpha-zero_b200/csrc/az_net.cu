@@ -260,6 +260,7 @@ extern "C" int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const
 #include "az_embed_mma.cuh"
 #include "az_front.cuh"
 #include "az_front2.cuh"
+#include "az_attn.cuh"
 
 struct AzBlockW {
     float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
@@ -317,6 +318,8 @@ struct az_net {
     // cls-row tail without LayerNorm kernels: row statistics travel between the GEMM epilogues,
     // the final norm + heads + softmax are the epilogue of one N = 64 GEMM (A + 1 <= 64)
     bool tail_fold = false, head_fold = false;
+    bool attn_mma = false;               // all-token attention of the full blocks on tcgen05 (az_attn.cuh)
+    CUtensorMap tm_qkv;
     float *stats1 = nullptr, *stats2 = nullptr;
     bf16* w_head_ln = nullptr;
     float *b_head_ln = nullptr, *cs_head = nullptr;
@@ -792,6 +795,12 @@ extern "C" int az_net_finalize(az_net* n) {
         return rc;
     if (deep && ((rc = az_make_tmap(&n->tm_ao, n->ao, M, D, D, 128)) || (rc = az_make_tmap(&n->tm_hbuf, n->hbuf, M, 4 * D, 4 * D, 128))))
         return rc;
+    if (deep && az_attn_supported(T, D, n->H) && !getenv("AZ_NO_ATTN_MMA")) {
+        // key / value rows past a board's last token are read (and meet probability 0): they have to be finite from the start
+        AZ_CUDA_OK(cudaMemset(n->qkv, 0, M * 3 * D * sizeof(bf16)));
+        if ((rc = az_make_tmap(&n->tm_qkv, n->qkv, M, 3 * D, 3 * D, 64))) return rc;
+        n->attn_mma = true;
+    }
     // CTA-pair kernels for the cls-row GEMMs: measured (tools/gemm_bench.py) 7 % faster on the K = 4D GEMM at 65536 rows, not
     // faster at 4096 rows (one tile per CTA: start-up latency, not L2 traffic, bounds those); AZ_PAIR_MIN_ROWS overrides
     const int pair_min = getenv("AZ_PAIR_MIN_ROWS") ? atoi(getenv("AZ_PAIR_MIN_ROWS")) : 16384;
@@ -1073,9 +1082,29 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         if (l > 0) layernorm(T, n->x, D, n->xn, D, w.ln1_g, w.ln1_b);
         if ((rc = gemm(AZ_K_GEMM_FULL, n->tm_xn, w.tm_in, az_gargs(batch, T, w.b_in, nullptr, 0, n->qkv, 3 * D, 3 * D, D), AZ_EPI_BIAS, (int)max_rows))) return rc;
         const int hd = D / H;
-        const size_t smem = ((size_t)2 * T * (hd + 1) + 4 * T) * sizeof(float);
-        if (smem > 48 * 1024) AZ_CUDA_OK(cudaFuncSetAttribute(az_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        {
+        if (n->attn_mma) {
+            AzAttnArgs aa{};
+            aa.batch = batch; aa.out = n->ao; aa.T = T; aa.D = D; aa.H = H; aa.hd = hd;
+            aa.KT = (T + 63) / 64; aa.Tp = (T + 15) & ~15; aa.groups = D / 64; aa.hpg = 64 / hd; aa.nq = (T + 127) / 128;
+            aa.nbuf = aa.KT <= 2 ? 2 : 1; aa.nstg = aa.nbuf;
+            aa.sl2e = 1.4426950408889634f / sqrtf((float)hd);
+            const size_t smem = az_attn_smem(aa);
+            const int cols = az_attn_tmem_cols(aa);
+            static bool attr_done = false;
+            if (!attr_done) {
+                AZ_CUDA_OK(cudaFuncSetAttribute(az_attn_mma_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+                AZ_CUDA_OK(cudaFuncSetAttribute(az_attn_mma_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+                attr_done = true;
+            }
+            const long long work = (long long)cap * aa.groups;
+            const int per_sm = cols == 256 ? 2 : 1;                // TMEM columns bound the CTAs of one SM
+            const int grid = (int)std::min<long long>(work > 0 ? work : 1, (long long)g_num_sms * per_sm);
+            AzProfScope ps(n, AZ_K_ATT_FULL, s);
+            if (cols == 256) az_attn_mma_kernel<256><<<grid, 160, smem, s>>>(n->tm_qkv, aa);
+            else az_attn_mma_kernel<512><<<grid, 160, smem, s>>>(n->tm_qkv, aa);
+        } else {
+            const size_t smem = ((size_t)2 * T * (hd + 1) + 4 * T) * sizeof(float);
+            if (smem > 48 * 1024) AZ_CUDA_OK(cudaFuncSetAttribute(az_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             AzProfScope ps(n, AZ_K_ATT_FULL, s);
             az_attention_kernel<<<cap * H, 128, smem, s>>>(batch, n->qkv, n->ao, T, D, H);
         }
@@ -1185,7 +1214,8 @@ extern "C" int az_net_proj_width(az_net* n) { return n ? (n->folded ? n->n2 : 2 
 
 extern "C" int az_net_path_flags(az_net* n) {
     if (!n) return 0;
-    return (n->front ? 1 : 0) | (n->front2 ? 2 : 0) | (n->blk[n->L - 1].bn_w1_c >= AZ_PAIR ? 4 : 0) | (n->tail_fold ? 8 : 0) | (n->head_fold ? 16 : 0);
+    return (n->front ? 1 : 0) | (n->front2 ? 2 : 0) | (n->blk[n->L - 1].bn_w1_c >= AZ_PAIR ? 4 : 0) | (n->tail_fold ? 8 : 0) | (n->head_fold ? 16 : 0) |
+           (n->attn_mma ? 32 : 0);
 }
 
 extern "C" long long az_net_launch_count(az_net* n) { return n ? (long long)n->launches : 0; }

@@ -62,7 +62,9 @@ def test_net_matches_reference_goldens():
     (3, 3, 3, 9, 64, 1, 3, 700),          # TicTacToe small net
     (3, 3, 3, 9, 128, 1, 3, 700),         # TicTacToe on the fused front end (8 boards per tile)
     (6, 7, 3, 7, 256, 1, 5, 1111),        # Connect4, two feature blocks, ragged last tile
-    (15, 15, 2, 225, 128, 2, 3, 300),     # 15x15: T = 226 tokens
+    (15, 15, 2, 225, 128, 2, 3, 300),     # 15x15: T = 226 tokens (head dim 16, four key boxes, two query tiles)
+    (7, 7, 2, 49, 512, 2, 5, 700),        # depth 2 at D = 512: head dim 64, one head per column group
+    (9, 9, 2, 81, 256, 3, 3, 500),        # 9x9, depth 3: T = 82 tokens (two key boxes), two full blocks
 ])
 def test_net_matches_torch_fp32(rows, cols, C, A, dim, depth, patch, B):
     import torch
@@ -75,6 +77,7 @@ def test_net_matches_torch_fp32(rows, cols, C, A, dim, depth, patch, B):
         x[:, 2] = rng.integers(0, 2, B).astype(np.float32)[:, None, None]
     x[0] = 0                                                   # empty board
     eng = B200Net(net, max_batch=4096)
+    assert bool(eng.path_flags() & 32) == (depth > 1), "full blocks must run their attention on the tensor cores"
     l, v, p = eng.forward_numpy(x)
     with torch.no_grad():
         rl, rv = net(torch.from_numpy(x[:600]))
@@ -150,3 +153,34 @@ def test_search_with_net_replays_exactly_in_oracle(g, n, iters, vl, dim, depth):
     assert np.array_equal(vis_step, vis_graph) and np.array_equal(q_step, q_graph)
     f.close()
     eng.close()
+
+
+@pytest.mark.parametrize("rows,dim,depth,patch", [(7, 256, 2, 5), (15, 128, 2, 3)])
+def test_full_attention_kernels_agree(rows, dim, depth, patch, monkeypatch):
+    """The tcgen05 all-token attention (az_attn.cuh) against the scalar kernel it replaces (AZ_NO_ATTN_MMA=1), same net,
+    same boards: both must sit inside the torch tolerance and next to each other (P is rounded to bf16 before the P V MMA,
+    the scalar kernel keeps it in fp32)."""
+    import torch
+    from alpha_zero_b200.ai.nn import B200Net
+    A = rows * rows
+    net = make_net(rows, rows, 2, A, dim, depth, patch)
+    rng = np.random.default_rng(4)
+    B = 333
+    x = (rng.random((B, 2, rows, rows)) < 0.3).astype(np.float32)
+    x[:, 1] *= (1 - x[:, 0])
+    eng = B200Net(net, max_batch=512)
+    assert eng.path_flags() & 32
+    l, v, p = eng.forward_numpy(x)
+    eng.close()
+    monkeypatch.setenv("AZ_NO_ATTN_MMA", "1")
+    eng = B200Net(net, max_batch=512)
+    assert not eng.path_flags() & 32
+    l0, v0, p0 = eng.forward_numpy(x)
+    eng.close()
+    with torch.no_grad():
+        rl, rv = net(torch.from_numpy(x))
+    check_close(l, v, p, rl.numpy(), rv.numpy())
+    check_close(l0, v0, p0, rl.numpy(), rv.numpy())
+    err_new, err_old = np.abs(l - rl.numpy()).max(), np.abs(l0 - rl.numpy()).max()
+    print(f"\nlogit error vs torch fp32: tcgen05 attention {err_new:.4f}, scalar attention {err_old:.4f}; between them {np.abs(l - l0).max():.4f}")
+    assert np.abs(l - l0).max() <= 0.05
