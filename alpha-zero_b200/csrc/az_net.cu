@@ -1085,23 +1085,21 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         if (n->attn_mma) {
             AzAttnArgs aa{};
             aa.batch = batch; aa.out = n->ao; aa.T = T; aa.D = D; aa.H = H; aa.hd = hd;
-            aa.KT = (T + 63) / 64; aa.Tp = (T + 15) & ~15; aa.groups = D / 64; aa.hpg = 64 / hd; aa.nq = (T + 127) / 128;
-            aa.nbuf = aa.KT <= 2 ? 2 : 1; aa.nstg = aa.nbuf;
+            aa.pack = T <= 64 ? 1 : 0;
+            aa.KT = aa.pack ? 2 : (T + 63) / 64; aa.Tp = (T + 15) & ~15; aa.NS = aa.pack ? 128 : aa.Tp;
+            aa.groups = D / 64; aa.hpg = 64 / hd; aa.hpg_log2 = hd == 64 ? 0 : (hd == 32 ? 1 : 2); aa.nq = (T + 127) / 128;
+            aa.nbuf = aa.KT <= 2 ? 2 : 1; aa.nstg = aa.pack ? 3 : aa.nbuf;
             aa.sl2e = 1.4426950408889634f / sqrtf((float)hd);
             const size_t smem = az_attn_smem(aa);
-            const int cols = az_attn_tmem_cols(aa);
             static bool attr_done = false;
             if (!attr_done) {
-                AZ_CUDA_OK(cudaFuncSetAttribute(az_attn_mma_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-                AZ_CUDA_OK(cudaFuncSetAttribute(az_attn_mma_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+                AZ_CUDA_OK(cudaFuncSetAttribute(az_attn_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
                 attr_done = true;
             }
-            const long long work = (long long)cap * aa.groups;
-            const int per_sm = cols == 256 ? 2 : 1;                // TMEM columns bound the CTAs of one SM
-            const int grid = (int)std::min<long long>(work > 0 ? work : 1, (long long)g_num_sms * per_sm);
+            const long long work = (long long)(aa.pack ? (cap + 1) / 2 : cap) * aa.groups;
+            const int grid = (int)std::min<long long>(work > 0 ? work : 1, (long long)g_num_sms);     // one CTA per SM (TMEM, shared memory)
             AzProfScope ps(n, AZ_K_ATT_FULL, s);
-            if (cols == 256) az_attn_mma_kernel<256><<<grid, 160, smem, s>>>(n->tm_qkv, aa);
-            else az_attn_mma_kernel<512><<<grid, 160, smem, s>>>(n->tm_qkv, aa);
+            az_attn_mma_kernel<<<grid, AZ_ATTN_THREADS, smem, s>>>(n->tm_qkv, aa);
         } else {
             const size_t smem = ((size_t)2 * T * (hd + 1) + 4 * T) * sizeof(float);
             if (smem > 48 * 1024) AZ_CUDA_OK(cudaFuncSetAttribute(az_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
