@@ -261,6 +261,7 @@ extern "C" int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const
 #include "az_front.cuh"
 #include "az_front2.cuh"
 #include "az_attn.cuh"
+#include "az_tail.cuh"
 
 struct AzBlockW {
     float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
@@ -320,6 +321,8 @@ struct az_net {
     bool tail_fold = false, head_fold = false;
     bool attn_mma = false;               // all-token attention of the full blocks on tcgen05 (az_attn.cuh)
     CUtensorMap tm_qkv;
+    bool fused_tail = false;             // out-proj .. heads of the cls rows in one cluster kernel (az_tail.cuh), small batches
+    CUtensorMap tm_t_u, tm_t_wo, tm_t_w1, tm_t_w2;
     float *stats1 = nullptr, *stats2 = nullptr;
     bf16* w_head_ln = nullptr;
     float *b_head_ln = nullptr, *cs_head = nullptr;
@@ -345,9 +348,9 @@ struct az_net {
     double prof_units[16] = {0};         // flops (GEMMs) or bytes (others) of the profiled launches
 };
 
-enum { AZ_K_EMBED = 0, AZ_K_GEMM_KV, AZ_K_GEMM_CLS, AZ_K_CLS_ATT, AZ_K_LN, AZ_K_HEAD, AZ_K_GEMM_FULL, AZ_K_ATT_FULL, AZ_K_FRONT, AZ_K_COUNT };
+enum { AZ_K_EMBED = 0, AZ_K_GEMM_KV, AZ_K_GEMM_CLS, AZ_K_CLS_ATT, AZ_K_LN, AZ_K_HEAD, AZ_K_GEMM_FULL, AZ_K_ATT_FULL, AZ_K_FRONT, AZ_K_TAIL, AZ_K_COUNT };
 static const char* const AZ_K_NAMES[AZ_K_COUNT] = {"embed_ln", "gemm_kv", "gemm_cls_rows", "cls_attention", "layernorm",
-                                                   "head_softmax", "gemm_full_block", "attention_full", "front_fused"};
+                                                   "head_softmax", "gemm_full_block", "attention_full", "front_fused", "tail_fused"};
 
 struct AzProfScope {
     az_net* n; cudaStream_t s; int idx = -1;
@@ -850,6 +853,21 @@ extern "C" int az_net_finalize(az_net* n) {
             (rc = az_upload_f32(n, &n->cs_head, cs)) || (rc = az_make_tmap(&n->tm_whead_ln, n->w_head_ln, 64, D, D, 64)))
             return rc;
     }
+    {   // fused cls-row tail (az_tail.cuh): one cluster kernel instead of four GEMM launches for evaluation batches of up to
+        // AZ_TAIL_MAX_ROWS boards.  Opt-in (AZ_FUSED_TAIL=1): measured on B200 it is 58 us per pass against 70 us for the chain
+        // timed kernel by kernel, but inside the search graph (PDL, back to back) the chain is the faster one: Connect4
+        // 66.6 M simulations/s with the chain, 64.1 M with this kernel.
+        const int tail_max = getenv("AZ_TAIL_MAX_ROWS") ? atoi(getenv("AZ_TAIL_MAX_ROWS")) : 4096;
+        const bool want = getenv("AZ_FUSED_TAIL") && atoi(getenv("AZ_FUSED_TAIL")) != 0;
+        if (want && n->front2 && n->tail_fold && n->head_fold && D % 128 == 0 && D <= 512 && n->chunk <= tail_max) {
+            AzBlockW& w = n->blk[n->L - 1];
+            const int K2 = n->H * 128;
+            if ((rc = az_make_tmap(&n->tm_t_u, n->uc, B, K2, K2, 64)) || (rc = az_make_tmap(&n->tm_t_wo, n->w_out2, D, K2, K2, 128)) ||
+                (rc = az_make_tmap(&n->tm_t_w1, w.w1_ln, 4 * D, D, D, 128)) || (rc = az_make_tmap(&n->tm_t_w2, w.w2, D, 4 * D, 4 * D, 128)))
+                return rc;
+            n->fused_tail = true;
+        }
+    }
     n->head_gemm = false;
     if (!n->head_fold && A + 1 > 32 && A + 1 <= 64 && !getenv("AZ_NO_HEAD_GEMM")) {   // heads as one N = 64 tensor-core GEMM
         std::vector<float> wh((size_t)64 * D, 0.f), bh(64, 0.f);
@@ -1035,6 +1053,41 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         }
         AZ_CUDA_OK(cudaGetLastError());
         ++n->launches;
+        if (n->fused_tail) {
+            AzTailArgs ta{};
+            ta.batch = batch; ta.D = D; ta.K2 = n->H * 128; ta.A = A; ta.C = D / 128;
+            ta.b_out = n->b_out2; ta.b1 = w.b1_ln; ta.cs1 = w.cs1; ta.b2 = w.b2; ta.b_head = n->b_head_ln; ta.cs_head = n->cs_head;
+            ta.priors = priors; ta.values = values; ta.logits = logits; ta.ln_eps = 1e-5f;
+            static bool attr_done = false;
+            if (!attr_done) {
+                AZ_CUDA_OK(cudaFuncSetAttribute(az_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AZ_TAIL_SMEM));
+                attr_done = true;
+            }
+            const int tiles = (cap + AZ_TAIL_ROWS - 1) / AZ_TAIL_ROWS;
+            const int clusters = std::max(1, std::min(tiles, g_num_sms / ta.C));
+            static const bool pdl = !getenv("AZ_NO_PDL");
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned)(clusters * ta.C));
+            cfg.blockDim = dim3(AZ_TAIL_THREADS);
+            cfg.dynamicSmemBytes = AZ_TAIL_SMEM;
+            cfg.stream = s;
+            cudaLaunchAttribute attr[2];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = (unsigned)ta.C;
+            attr[0].val.clusterDim.y = 1;
+            attr[0].val.clusterDim.z = 1;
+            attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[1].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = pdl ? 2 : 1;
+            {
+                AzProfScope ps(n, AZ_K_TAIL, s);
+                AZ_CUDA_OK(cudaLaunchKernelEx(&cfg, az_tail_kernel, n->tm_t_u, n->tm_t_wo, n->tm_t_w1, n->tm_t_w2, n->tm_whead_ln, ta));
+            }
+            AZ_CUDA_OK(cudaGetLastError());
+            ++n->launches;
+            return AZ_OK;
+        }
         if (n->front2) {
             if ((rc = cls_tail(w, az_gargs(batch, 1, n->b_out2, nullptr, 0, n->xc, D, D, n->H * 128), AZ_EPI_BIAS, true))) return rc;
             return heads(n->xc2);
@@ -1213,7 +1266,7 @@ extern "C" int az_net_proj_width(az_net* n) { return n ? (n->folded ? n->n2 : 2 
 extern "C" int az_net_path_flags(az_net* n) {
     if (!n) return 0;
     return (n->front ? 1 : 0) | (n->front2 ? 2 : 0) | (n->blk[n->L - 1].bn_w1_c >= AZ_PAIR ? 4 : 0) | (n->tail_fold ? 8 : 0) | (n->head_fold ? 16 : 0) |
-           (n->attn_mma ? 32 : 0);
+           (n->attn_mma ? 32 : 0) | (n->fused_tail ? 64 : 0);
 }
 
 extern "C" long long az_net_launch_count(az_net* n) { return n ? (long long)n->launches : 0; }

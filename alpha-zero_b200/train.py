@@ -328,7 +328,8 @@ def train(model, batch_size, buffer, train_iterations, lr, device):
     last_stats.update(iterations=train_iterations, batch_size=batch_size, world=dist.get_world_size() if ddp else 1,
                       grad_bytes=sum(p.numel() * p.element_size() for p in model.parameters()))
     if buckets:
-        torch.cuda.synchronize()
+        if buckets.flat.is_cuda:
+            torch.cuda.synchronize()
         last_stats.update(allreduce_exposed_ms=sum(a.elapsed_time(b) for a, b in buckets.exposed), buckets=len(buckets.buckets))
         buckets.close()
         for p in model.parameters():                    # leave ordinary, independent .grad tensors behind

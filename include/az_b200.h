@@ -235,7 +235,9 @@ AZ_API long long az_net_launch_count(az_net* n);
 AZ_API int az_net_proj_width(az_net* n);   /* N of the all-token projection GEMM of the last block */
 /* Which kernels this net runs (for reports): bit 0 fused front end (az_front.cuh), bit 1 its reassociated form
  * (az_front2.cuh: U vectors, out-proj over K = heads*128), bit 2 CTA-pair tiles for the cls-row GEMMs (az_gemm2.cuh),
- * bit 3 LayerNorm folded around the cls-row GEMMs, bit 4 heads + softmax as a GEMM epilogue. */
+ * bit 3 LayerNorm folded around the cls-row GEMMs, bit 4 heads + softmax as a GEMM epilogue, bit 5 all-token attention of
+ * the full blocks on tcgen05 (az_attn.cuh; off: the scalar kernel, AZ_NO_ATTN_MMA=1 or an unsupported head dim), bit 6 the
+ * cls-row tail fused into one cluster kernel (az_tail.cuh; opt-in, AZ_FUSED_TAIL=1). */
 AZ_API int az_net_path_flags(az_net* n);
 /* MCTS.mcts with the built-in net for every tree of the forest: `iters` simulations per tree,
  * one CUDA graph per step (advance + net), no per-node host work. */

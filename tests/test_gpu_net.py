@@ -184,3 +184,48 @@ def test_full_attention_kernels_agree(rows, dim, depth, patch, monkeypatch):
     err_new, err_old = np.abs(l - rl.numpy()).max(), np.abs(l0 - rl.numpy()).max()
     print(f"\nlogit error vs torch fp32: tcgen05 attention {err_new:.4f}, scalar attention {err_old:.4f}; between them {np.abs(l - l0).max():.4f}")
     assert np.abs(l - l0).max() <= 0.05
+
+
+@pytest.mark.parametrize("rows,cols,C,A,dim,patch", [
+    (6, 7, 3, 7, 512, 5),          # Connect4, BASELINE configs[1]: cluster of 4
+    (7, 7, 2, 49, 512, 5),         # Gomoku 7x7: 49 policy outputs + value in the 64-wide head tile
+    (6, 7, 3, 7, 256, 5),          # cluster of 2
+    (6, 7, 3, 7, 128, 5),          # one CTA per tile
+])
+def test_fused_tail_matches_gemm_chain(rows, cols, C, A, dim, patch, monkeypatch):
+    """az_tail_kernel (out-proj .. heads of the cls rows in one cluster kernel; opt-in with AZ_FUSED_TAIL=1)
+    against the four-GEMM chain and against torch fp32, at batch sizes around the 64-row tile and at more tiles than clusters;
+    and a row's answer must not depend on its position in the batch."""
+    import torch
+    from alpha_zero_b200.ai.nn import B200Net
+    net = make_net(rows, cols, C, A, dim, 1, patch)
+    rng = np.random.default_rng(9)
+    B = 4096
+    x = (rng.random((B, C, rows, cols)) < 0.3).astype(np.float32)
+    x[:, 1] *= (1 - x[:, 0])
+    if C == 3:
+        x[:, 2] = rng.integers(0, 2, B).astype(np.float32)[:, None, None]
+    monkeypatch.setenv("AZ_FUSED_TAIL", "1")
+    eng = B200Net(net, max_batch=4096)
+    if not eng.path_flags() & 2:
+        eng.close()
+        pytest.skip("this shape does not run the reassociated front kernel the fused tail follows")
+    assert eng.path_flags() & 64, "the fused tail must be the path that runs"
+    l, v, p = eng.forward_numpy(x)
+    for nb in (1, 63, 64, 65, 129, 1111):
+        ls, vs, ps = eng.forward_numpy(x[:nb])
+        assert np.array_equal(ls, l[:nb]) and np.array_equal(vs, v[:nb]) and np.array_equal(ps, p[:nb]), f"batch of {nb}"
+    l2, v2, _ = eng.forward_numpy(x[-77:])
+    assert np.array_equal(l2, l[-77:]) and np.array_equal(v2, v[-77:])
+    eng.close()
+    monkeypatch.delenv("AZ_FUSED_TAIL")
+    eng = B200Net(net, max_batch=4096)
+    assert not eng.path_flags() & 64
+    l0, v0, p0 = eng.forward_numpy(x)
+    eng.close()
+    with torch.no_grad():
+        rl, rv = net(torch.from_numpy(x[:600]))
+    check_close(l[:600], v[:600], p[:600], rl.numpy(), rv.numpy())
+    d = np.abs(l - l0).max()
+    print(f"\nfused tail vs GEMM chain: max |dlogit| {d:.5f}, max |dvalue| {np.abs(v - v0).max():.5f}; vs torch fp32: fused {np.abs(l[:600] - rl.numpy()).max():.4f}, chain {np.abs(l0[:600] - rl.numpy()).max():.4f}")
+    assert d <= 0.03 and np.abs(p - p0).max() <= 0.01
