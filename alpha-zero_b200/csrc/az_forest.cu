@@ -1167,6 +1167,16 @@ int az_make_game(int game, int rows, int cols, AzGame* out) {
             }
         g.set_slots = size;
     }
+    for (int d = 0; d < 4; ++d) g.win_start[d] = 0;
+    if (g.nw == 1) {
+        const int dcs[4] = {1, 0, 1, -1};
+        for (int d = 0; d < 4; ++d)
+            for (int r = 0; r < rows; ++r)
+                for (int c = 0; c < cols; ++c) {
+                    const int last = c + dcs[d] * (g.k - 1);                 // column of the run's last stone
+                    if (last >= 0 && last < cols) g.win_start[d] |= 1ull << (r * cols + c);
+                }
+    }
     *out = g;
     return AZ_OK;
 }

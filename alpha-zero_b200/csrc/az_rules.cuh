@@ -79,12 +79,43 @@ __host__ __device__ __forceinline__ int az_run_length(const AzGame& g, const AzB
     return n;
 }
 
-// true iff player p, who just played `cell`, has a run >= k through it (overlines count).
+// true iff player p, who just played `cell`, has a run >= k through it (overlines count): walking the four lines.
 template <int NW>
-__host__ __device__ __forceinline__ bool az_is_win(const AzGame& g, const AzBoard<NW>& b, int p, int cell) {
+__host__ __device__ __forceinline__ bool az_is_win_walk(const AzGame& g, const AzBoard<NW>& b, int p, int cell) {
     const int r = cell / g.cols, c = cell - r * g.cols;
     return az_run_length(g, b, p, r, c, 0, 1) >= g.k || az_run_length(g, b, p, r, c, 1, 0) >= g.k ||
            az_run_length(g, b, p, r, c, 1, 1) >= g.k || az_run_length(g, b, p, r, c, 1, -1) >= g.k;
+}
+
+// The same predicate on a one-word board by shift and mask.  Along a direction with bit shift s, bit x of
+//     t = m & (m >> s) & ... & (m >> (k-1) s)
+// says that k stones of p sit at x, x + s, ...; win_start drops the x whose run would wrap into the next row, and `th` keeps
+// the runs that contain `cell` (start = cell - i s, i < k; a start that wrapped is not in win_start either).  Same answer as
+// the walk for EVERY position, also ones that already hold a run elsewhere (the reference only looks through the last move:
+// games/connect4.py:72-98 and the two other check_winner).
+__host__ __device__ __forceinline__ bool az_is_win_bits(const AzGame& g, uint64_t m, int cell) {
+    const uint64_t bitc = 1ull << cell;
+    const int sh[4] = {1, g.cols, g.cols + 1, g.cols - 1};
+    bool win = false;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        uint64_t t = m, th = bitc;
+#pragma unroll
+        for (int i = 1; i < 5; ++i) {
+            if (i < g.k) {
+                t &= m >> (i * sh[d]);
+                th |= bitc >> (i * sh[d]);
+            }
+        }
+        win = win || (t & th & g.win_start[d]) != 0ull;
+    }
+    return win;
+}
+
+template <int NW>
+__host__ __device__ __forceinline__ bool az_is_win(const AzGame& g, const AzBoard<NW>& b, int p, int cell) {
+    if (NW == 1) return az_is_win_bits(g, p ? b.w[1][0] : b.w[0][0], cell);
+    return az_is_win_walk(g, b, p, cell);
 }
 
 // Index into the policy vector of a move stored as a cell: games/*: get_action_idx.

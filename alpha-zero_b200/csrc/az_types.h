@@ -28,6 +28,9 @@ struct AzGame {
     int nw;           // 64-bit words per side bitboard
     int max_children; // upper bound on legal moves of a node
     int set_slots;    // largest CPython-set table the Gomoku legal-move emulation can reach
+    // boards of one word: cells a run of k stones may START at along (0,1), (1,0), (1,1), (1,-1) without leaving its rows
+    // (column bounds only: bits beyond the board are never set), for the shift-and-mask win test of az_rules.cuh
+    uint64_t win_start[4];
 };
 
 // Hot per-node record: everything PUCT reads for one child, one 16-byte load.
