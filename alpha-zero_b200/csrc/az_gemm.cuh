@@ -7,7 +7,10 @@
 //   warp 1   MMA issuer: one lane issues tcgen05.mma (M=128, N=BN, K=16) with the fp32
 //            accumulator in TMEM; tcgen05.commit releases ring slots / publishes the tile;
 //   warps 2-9 epilogue: tcgen05.ld the accumulator (each warp its 32-lane quarter and one half of the
-//            tile's columns), add bias (+ erf GELU | + residual), convert to bf16, 64-byte row stores.
+//            tile's columns), add bias (+ erf GELU | + residual), convert to bf16; tiles of 128 / 256 columns
+//            stage 32 rows x 64 columns per warp in shared memory (128-byte swizzle, conflict-free 16-byte
+//            writes) and store them with cp.async.bulk.tensor (TMA store: one instruction instead of 128
+//            16-byte global stores at a row stride); narrower tiles and fp32 side outputs store directly.
 // Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
 //
 // LayerNorm around a GEMM never runs as its own kernel on the cls-row path.  The GEMM that PRODUCES a
@@ -30,6 +33,8 @@
 #define AZ_STATS_LD 64          // floats per row of a statistics buffer: up to 32 (sum, sum of squares) partials
 #define AZ_GEMM_THREADS 320
 #define AZ_HEAD_STAGE_BYTES (4 * 32 * 64 * 4)
+#define AZ_OUT_STAGE_BYTES (8 * 4096)   // one 32 x 64 bf16 tile per epilogue warp
+#define AZ_BAR_BYTES 1024               // barriers + TMEM slot, keeps what follows 1024-byte aligned
 
 struct AzGemmArgs {
     const float* bias;          // [N] fp32
@@ -56,6 +61,7 @@ struct AzGemmArgs {
     int w_early;                // the first W tiles are requested BEFORE griddepcontrol.wait (weights do not depend on the predecessor;
                                 // only where the row counter was written at least two kernels upstream)
     int l2_hints;               // A loads evict_first, W loads evict_last (the cls-row chain inside the search step)
+    int stage_out;              // 1: bf16 tiles leave through shared memory + TMA stores (tm_o describes `out`, box 64 columns x 32 rows)
     int dbg;                    // experiments (tools/gemm_bench.py): bit 0 no MMA, bit 1 no W loads, bit 2 no A loads (results are garbage)
 };
 
@@ -96,7 +102,7 @@ struct AzGemmCfg {
     static constexpr int STAGES = BN >= 192 ? 4 : 6;
     static constexpr int TMEM_COLS = 2 * BN <= 32 ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
     static constexpr int ACC_STRIDE = TMEM_COLS / 2;          // TMEM columns between the two accumulator stages
-    static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;   // + barriers + align slack
+    static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + AZ_BAR_BYTES + (BN == 128 || BN == 256 ? AZ_OUT_STAGE_BYTES : 0) + 1024;   // + align slack
 };
 
 // nn.GELU() default (erf form): 0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz & Stegun 7.1.25
@@ -114,9 +120,12 @@ __device__ __forceinline__ float az_gelu_erf(float x) {
 // Epilogue of one accumulator tile for one thread (= one output row): BN/2 columns starting at
 // column half*BN/2 of the tile, bias (+ LayerNorm fold) (+ GELU | + residual), bf16 row stores,
 // optional row statistics.  Shared by the single-CTA and the CTA-pair kernels.
+// stg: this warp's 4 KB staging tile (nullptr: direct stores); row_w0: first row of the warp's 32 rows.
 template <int BN, int EPI>
 __device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uint32_t tacc, int row, bool live, int n_blk, int half,
-                                                     float rstd, float nmr) {
+                                                     float rstd, float nmr, unsigned char* stg = nullptr, const CUtensorMap* tm_o = nullptr,
+                                                     int row_w0 = 0) {
+    const int lane_ = threadIdx.x & 31;
     constexpr int CPW = BN / 64;                               // 32-column chunks per warp
     float st1 = 0.f, st2 = 0.f;
 #ifndef AZ_NO_EPI_PREFETCH                                          // the next chunk's tcgen05.ld runs under this chunk's arithmetic
@@ -137,7 +146,9 @@ __device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uin
         azptx::tmem_ld_wait();
 #endif
         const int col0 = n_blk * BN + c * 32;
-        if (live && args.out_f32 && col0 >= args.f32_col0) {      // fp32 side output (attention scores)
+        const bool f32_chunk = args.out_f32 && col0 >= args.f32_col0;   // warp-uniform: the staged path below synchronises the warp
+        if (f32_chunk) {                                          // fp32 side output (attention scores)
+            if (!live) continue;
             const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
             float4* op = reinterpret_cast<float4*>(args.out_f32 + (size_t)row * 64 + (col0 - args.f32_col0));
 #pragma unroll
@@ -146,11 +157,11 @@ __device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uin
                 op[i] = make_float4(__uint_as_float(r[4 * i + 0]) + bb.x, __uint_as_float(r[4 * i + 1]) + bb.y,
                                     __uint_as_float(r[4 * i + 2]) + bb.z, __uint_as_float(r[4 * i + 3]) + bb.w);
             }
-        } else if (live) {
+        } else if (live || stg) {
             const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
             const float4* c4 = reinterpret_cast<const float4*>(args.colsum + col0);
             uint4 rv[4];
-            if (EPI == AZ_EPI_RESID) {
+            if (EPI == AZ_EPI_RESID && live) {
                 const uint4* rp = reinterpret_cast<const uint4*>(args.resid + (size_t)row * args.ldr + col0);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) rv[i] = rp[i];
@@ -194,12 +205,31 @@ __device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uin
                 ow[0] = *reinterpret_cast<uint32_t*>(&o01);
                 ow[1] = *reinterpret_cast<uint32_t*>(&o23);
             }
-            uint4* op = reinterpret_cast<uint4*>(args.out + (size_t)row * args.ldo + col0);
 #ifdef AZ_EPI_EXPERIMENT
             if ((args.dbg & 8) && ov[0].x != 0x7fc07fc1u) continue;   // value-dependent, so the arithmetic is not eliminated
 #endif
+            if (stg) {
+                // 32 rows x 128 bytes, 16-byte chunks swizzled by the row: a 64-column pair of chunks is one TMA store
+                if ((cc & 1) == 0) {
+                    if (lane_ == 0) azptx::bulk_wait_read0();        // the previous store has read the tile
+                    __syncwarp();
+                }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) op[i] = ov[i];
+                for (int i = 0; i < 4; ++i)
+                    *reinterpret_cast<uint4*>(stg + lane_ * 128 + ((((cc & 1) * 4 + i) ^ (lane_ & 7)) << 4)) = live ? ov[i] : make_uint4(0u, 0u, 0u, 0u);
+                if (cc & 1) {
+                    azptx::fence_proxy_async();
+                    __syncwarp();
+                    if (lane_ == 0) {
+                        azptx::tma_store_2d(tm_o, stg, col0 - 32, row_w0);
+                        azptx::bulk_commit();
+                    }
+                }
+            } else {
+                uint4* op = reinterpret_cast<uint4*>(args.out + (size_t)row * args.ldo + col0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) op[i] = ov[i];
+            }
         }
     }
     if (args.stats_out && live)
@@ -208,7 +238,8 @@ __device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uin
 
 template <int BN, int EPI>
 __global__ void __launch_bounds__(AZ_GEMM_THREADS, 1)
-az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, AzGemmArgs args) {
+az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, const __grid_constant__ CUtensorMap tm_o,
+               AzGemmArgs args) {
     using Cfg = AzGemmCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ unsigned char smem_dyn[];
@@ -368,7 +399,7 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                     }
                 }
                 const int A = args.head_A;
-                float* hs = reinterpret_cast<float*>(smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES) + 256) + q * 32 * 64;
+                float* hs = reinterpret_cast<float*>(smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES) + AZ_BAR_BYTES) + q * 32 * 64;
                 const int r0w = m_blk * Cfg::BM + q * 32;     // first row of this warp
                 const int nlive = min(max(M - r0w, 0), 32);
                 const size_t obase = (size_t)(args.m_item_offset + r0w);
@@ -401,13 +432,16 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 __syncwarp();
                 if (live) args.values[obase + lane] = tanhf(val);
             } else {
-                az_gemm_epilogue_row<BN, EPI>(args, tacc, row, live, n_blk, half, rstd, nmr);
+                unsigned char* stg = (BN == 128 || BN == 256) && args.stage_out
+                                         ? smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES) + AZ_BAR_BYTES + (warp - 2) * 4096 : nullptr;
+                az_gemm_epilogue_row<BN, EPI>(args, tacc, row, live, n_blk, half, rstd, nmr, stg, &tm_o, m_blk * Cfg::BM + q * 32);
             }
             azptx::tc_fence_before();
             azptx::mbar_arrive(&tempty[as]);
             as ^= 1;
             if (as == 0) aphase ^= 1;
         }
+        if (lane == 0) azptx::bulk_wait0();                    // this warp's TMA stores have landed before the CTA retires
     }
     azptx::tc_fence_before();
     __syncthreads();

@@ -74,12 +74,13 @@ struct AzGemm2Cfg {
     static constexpr int STAGES = BN >= 256 ? 6 : 8;
     static constexpr int TMEM_COLS = 2 * BN <= 256 ? 256 : 512;
     static constexpr int ACC_STRIDE = TMEM_COLS / 2;
-    static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 256 + 1024;
+    static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + AZ_BAR_BYTES + AZ_OUT_STAGE_BYTES + 1024;
 };
 
 template <int BN, int EPI>
 __global__ void __launch_bounds__(AZ_GEMM_THREADS, 1)
-az_gemm2_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, AzGemmArgs args) {
+az_gemm2_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, const __grid_constant__ CUtensorMap tm_o,
+                AzGemmArgs args) {
     using Cfg = AzGemm2Cfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ unsigned char smem_dyn[];
@@ -194,13 +195,16 @@ az_gemm2_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
             }
             const float nmr = -mean * rstd;
             const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * Cfg::ACC_STRIDE;
-            az_gemm_epilogue_row<BN, EPI>(args, tacc, row, live, n_blk, half, rstd, nmr);
+            unsigned char* stg = args.stage_out ? smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES) + AZ_BAR_BYTES + (warp - 2) * 4096 : nullptr;
+            az_gemm_epilogue_row<BN, EPI>(args, tacc, row, live, n_blk, half, rstd, nmr, stg, &tm_o,
+                                          m_blk * 2 * Cfg::BM + (int)rank * Cfg::BM + q * 32);
             azptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) azptx::mbar_arrive_cluster(ltempty0 + as * 8);
             as ^= 1;
             if (as == 0) aphase ^= 1;
         }
+        if (lane == 0) azptx::bulk_wait0();
     }
     azptx::tc_fence_before();
     __syncthreads();

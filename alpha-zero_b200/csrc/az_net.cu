@@ -14,6 +14,8 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <mutex>
+#include <tuple>
 #include <string>
 #include <vector>
 #include "az_gemm.cuh"
@@ -130,6 +132,35 @@ static cudaError_t az_launch_pdl(void (*kernel)(KArgs...), int grid, int block, 
     return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
+// Output tensor map of a GEMM whose bf16 tiles leave through shared memory + TMA stores (az_gemm.cuh): box = 64 columns x 32
+// rows (one epilogue warp), rows beyond max_rows are clipped by the hardware.  Encoded maps are cached per (pointer, shape).
+template <int BN, int EPI>
+static int az_gemm_out_map(AzGemmArgs* a, CUtensorMap* to, int max_rows) {
+    static const bool off = getenv("AZ_NO_TMA_STORE") != nullptr;
+    a->stage_out = 0;
+    if (off || !(BN == 128 || BN == 256) || EPI == AZ_EPI_HEAD || !a->out || a->ldo % 8 || (reinterpret_cast<uintptr_t>(a->out) & 15) || max_rows < 1)
+        return AZ_OK;
+    struct Key {
+        const void* p; int rows, n, ld;
+        bool operator<(const Key& o) const { return std::tie(p, rows, n, ld) < std::tie(o.p, o.rows, o.n, o.ld); }
+    };
+    static std::map<Key, CUtensorMap> cache;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lk(mu);
+    const Key k{a->out, max_rows, a->N, a->ldo};
+    auto it = cache.find(k);
+    if (it == cache.end()) {
+        CUtensorMap m;
+        int rc = az_make_tmap(&m, a->out, (uint64_t)max_rows, (uint64_t)a->N, (uint64_t)a->ldo, 32);
+        if (rc) return rc;
+        if (cache.size() > 256) cache.clear();
+        it = cache.emplace(k, m).first;
+    }
+    *to = it->second;
+    a->stage_out = 1;
+    return AZ_OK;
+}
+
 template <int BN, int EPI>
 static int az_launch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const AzGemmArgs& a, int max_rows, cudaStream_t s) {
     constexpr int smem = AzGemmCfg<BN>::SMEM + (EPI == AZ_EPI_HEAD ? AZ_HEAD_STAGE_BYTES : 0);
@@ -145,7 +176,11 @@ static int az_launch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const 
     }
     const int tiles = ((max_rows + 127) / 128) * (a.N / BN);
     const int grid = tiles < g_num_sms ? (tiles > 0 ? tiles : 1) : g_num_sms;
-    AZ_CUDA_OK(az_launch_pdl(az_gemm_kernel<BN, EPI>, grid, AZ_GEMM_THREADS, smem, s, ta, tb, a));
+    AzGemmArgs a2 = a;
+    CUtensorMap to = ta;                                       // placeholder when the tile does not go through TMA stores
+    int rc_o = az_gemm_out_map<BN, EPI>(&a2, &to, max_rows);
+    if (rc_o) return rc_o;
+    AZ_CUDA_OK(az_launch_pdl(az_gemm_kernel<BN, EPI>, grid, AZ_GEMM_THREADS, smem, s, ta, tb, to, a2));
     AZ_CUDA_OK(cudaGetLastError());
     return AZ_OK;
 }
@@ -180,7 +215,11 @@ static int az_launch_gemm2_t(const CUtensorMap& ta, const CUtensorMap& tb, const
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 2 : 1;
-    AZ_CUDA_OK(cudaLaunchKernelEx(&cfg, az_gemm2_kernel<BN, EPI>, ta, tb, a));
+    AzGemmArgs a2 = a;
+    CUtensorMap to = ta;
+    int rc_o = az_gemm_out_map<BN, EPI>(&a2, &to, max_rows);
+    if (rc_o) return rc_o;
+    AZ_CUDA_OK(cudaLaunchKernelEx(&cfg, az_gemm2_kernel<BN, EPI>, ta, tb, to, a2));
     AZ_CUDA_OK(cudaGetLastError());
     return AZ_OK;
 }

@@ -9,7 +9,8 @@ import torch
 import alpha_zero_b200 as az
 L = az.lib.load()
 shapes = [("out-proj", 4096, 512, 1024, 0), ("mlp1", 4096, 2048, 512, 1), ("mlp2", 4096, 512, 2048, 2), ("head-like", 4096, 64, 512, 0),
-          ("mlp1 big", 65536, 2048, 512, 1), ("mlp2 big", 65536, 512, 2048, 2)]
+          ("mlp1 big", 65536, 2048, 512, 1), ("mlp2 big", 65536, 512, 2048, 2), ("mlp1 mid", 32768, 2048, 512, 1), ("out-proj mid", 32768, 512, 1024, 0),
+          ("qkv full", 204800, 768, 256, 0), ("mlp1 full", 204800, 1024, 256, 1)]
 import subprocess
 if len(sys.argv) == 1:                                   # driver: one subprocess per (shape, tile) so a failing tile is isolated
     for i, (name, M, N, K, epi) in enumerate(shapes):
