@@ -1305,7 +1305,7 @@ extern "C" int az_net_proj_width(az_net* n) { return n ? (n->folded ? n->n2 : 2 
 extern "C" int az_net_path_flags(az_net* n) {
     if (!n) return 0;
     return (n->front ? 1 : 0) | (n->front2 ? 2 : 0) | (n->blk[n->L - 1].bn_w1_c >= AZ_PAIR ? 4 : 0) | (n->tail_fold ? 8 : 0) | (n->head_fold ? 16 : 0) |
-           (n->attn_mma ? 32 : 0) | (n->fused_tail ? 64 : 0);
+           (n->attn_mma ? 32 : 0) | (n->fused_tail ? 64 : 0) | (getenv("AZ_NO_TMA_STORE") ? 0 : 128);
 }
 
 extern "C" long long az_net_launch_count(az_net* n) { return n ? (long long)n->launches : 0; }

@@ -195,6 +195,9 @@ def roofline(wl, r, prof, pk, kind=None):
         kout = H * 128 if front2 else D
         flops, name = 2.0 * leaves * (kout * D + 8 * D * D) / 3.0, "az_gemm_kernel (cls-row out_proj / MLP GEMMs, tcgen05; average of the 3 launches)"
         ref_flops = 2.0 * leaves * (D * D + 8 * D * D) / 3.0          # the reference's graph: out-proj over K = D
+    elif kind == "tail_fused":      # AZ_FUSED_TAIL=1: the three cls-row GEMMs + the head GEMM in one cluster kernel
+        kout = H * 128 if front2 else D
+        flops, name = 2.0 * leaves * (kout * D + 8 * D * D + 64 * D), "az_tail_kernel (out-proj + MLP + heads of the cls rows, one cluster kernel, tcgen05)"
     elif kind == "embed_ln":
         flops, name = 2.0 * leaves * T * 128 * D, "az_embed_mma_kernel (im2col embedding + LN, tcgen05)"
     if flops is not None:
@@ -575,7 +578,8 @@ def summarize(args, wl, r, world, pk):
         d["rooflines_all"] = {k: rl for k, rl in ((k, roofline(wl, rr, prof, pk, k)) for k in prof) if rl}
         pf = r.get("path_flags", 0)
         d["evaluator_path"] = dict(flags=pf, front_kernel="az_front2_kernel" if pf & 2 else ("az_front_kernel" if pf & 1 else "generic"),
-                                   cls_row_gemm="cta_pair" if pf & 4 else "single_cta", layernorm_fold=bool(pf & 8), head_epilogue=bool(pf & 16))
+                                   cls_row_gemm="cta_pair" if pf & 4 else "single_cta", layernorm_fold=bool(pf & 8), head_epilogue=bool(pf & 16),
+                                   gemm_stores="tma_store" if pf & 128 else "per_thread", fused_tail=bool(pf & 64))
     return d
 
 
