@@ -959,35 +959,28 @@ __device__ int az_rollout(const AzGame& g, AzBoard<NW> b, uint64_t rng) {
 #pragma unroll
     for (int i = 0; i < NW; ++i) mc += __popcll(b.w[0][i]) + __popcll(b.w[1][i]);
     int player = 0;
+    if (NW == 1) {
+        // One-word boards: the legal set by shift and mask (az_rules.cuh; same sets, same k-th-lowest-cell draw and the same
+        // random stream as the cell walk below, hence the same playouts; tests/native/legal_set_test.cu compares the two forms)
+        const AzRolloutMasks m = az_rollout_masks(g);
+        while (mc < g.state_dim) {
+            uint64_t legal = az_rollout_legal_bits(g, m, b.w[0][0] | b.w[1][0], mc);
+            const int n = __popcll(legal);
+            if (n == 0) return 0;
+            rng = az_sm64(rng);
+            const int k = (int)((rng >> 11) % (uint64_t)n);
+            for (int j = 0; j < k; ++j) legal &= legal - 1;
+            const int cell = __ffsll((long long)legal) - 1;
+            b.put(player, cell);
+            ++mc;
+            if (az_is_win(g, b, player, cell)) return player == 0 ? 1 : -1;
+            player ^= 1;
+        }
+        return 0;
+    }
     while (mc < g.state_dim) {
         uint64_t legal[NW];
-#pragma unroll
-        for (int i = 0; i < NW; ++i) legal[i] = 0ull;
-        int n = 0;
-        for (int cell = 0; cell < g.state_dim; ++cell) {
-            if (!b.empty(cell)) continue;
-            bool ok;
-            if (g.gid == AZ_GAME_TICTACTOE) {
-                ok = true;
-            } else if (g.gid == AZ_GAME_CONNECT4) {
-                ok = cell + g.cols >= g.state_dim || !b.empty(cell + g.cols);
-            } else {
-                ok = false;
-                const int r = cell / g.cols, c = cell - r * g.cols;
-                for (int dr = -1; dr <= 1 && !ok; ++dr)
-                    for (int dc = -1; dc <= 1; ++dc) {
-                        const int rr = r + dr, cc = c + dc;
-                        if ((dr || dc) && rr >= 0 && rr < g.rows && cc >= 0 && cc < g.cols && !b.empty(rr * g.cols + cc)) { ok = true; break; }
-                    }
-                if (mc == 0) ok = cell == (g.rows / 2) * g.cols + g.cols / 2;
-            }
-            if (ok) {
-#pragma unroll
-                for (int i = 0; i < NW; ++i)
-                    if (NW == 1 || i == (cell >> 6)) legal[i] |= 1ull << (cell & 63);
-                ++n;
-            }
-        }
+        const int n = az_rollout_legal_walk<NW>(g, b, mc, legal);
         if (n == 0) return 0;
         rng = az_sm64(rng);
         int k = (int)((rng >> 11) % (uint64_t)n);

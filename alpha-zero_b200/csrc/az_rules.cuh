@@ -118,6 +118,65 @@ __host__ __device__ __forceinline__ bool az_is_win(const AzGame& g, const AzBoar
     return az_is_win_walk(g, b, p, cell);
 }
 
+// ---- legal SETS for the random rollouts of vanilla mode (ai/mcts.py:62-79; the order of the moves does not matter under a
+// uniform draw): TicTacToe empty cells, Connect4 the lowest empty cell of every open column, Gomoku empty 8-neighbours of
+// stones (the centre on an empty board).  Two forms: the cell walk (any board size) and shift-and-mask (one-word boards).
+template <int NW>
+__host__ __device__ inline int az_rollout_legal_walk(const AzGame& g, const AzBoard<NW>& b, int mc, uint64_t (&legal)[NW]) {
+#pragma unroll
+    for (int i = 0; i < NW; ++i) legal[i] = 0ull;
+    int n = 0;
+    for (int cell = 0; cell < g.state_dim; ++cell) {
+        if (!b.empty(cell)) continue;
+        bool ok;
+        if (g.gid == AZ_GAME_TICTACTOE) {
+            ok = true;
+        } else if (g.gid == AZ_GAME_CONNECT4) {
+            ok = cell + g.cols >= g.state_dim || !b.empty(cell + g.cols);
+        } else {
+            ok = false;
+            const int r = cell / g.cols, c = cell - r * g.cols;
+            for (int dr = -1; dr <= 1 && !ok; ++dr)
+                for (int dc = -1; dc <= 1; ++dc) {
+                    const int rr = r + dr, cc = c + dc;
+                    if ((dr || dc) && rr >= 0 && rr < g.rows && cc >= 0 && cc < g.cols && !b.empty(rr * g.cols + cc)) { ok = true; break; }
+                }
+            if (mc == 0) ok = cell == (g.rows / 2) * g.cols + g.cols / 2;
+        }
+        if (ok) {
+#pragma unroll
+            for (int i = 0; i < NW; ++i)
+                if (NW == 1 || i == (cell >> 6)) legal[i] |= 1ull << (cell & 63);
+            ++n;
+        }
+    }
+    return n;
+}
+
+struct AzRolloutMasks {
+    uint64_t board, col0, coll, floor_row;
+    int centre;
+};
+__host__ __device__ inline AzRolloutMasks az_rollout_masks(const AzGame& g) {
+    AzRolloutMasks m{0ull, 0ull, 0ull, 0ull, 0};
+    const uint64_t row = g.cols >= 64 ? ~0ull : (1ull << g.cols) - 1ull;
+    for (int r = 0; r < g.rows; ++r) {
+        m.board |= row << (r * g.cols);
+        m.col0 |= 1ull << (r * g.cols);
+        m.coll |= 1ull << (r * g.cols + g.cols - 1);
+    }
+    m.floor_row = row << ((g.rows - 1) * g.cols);
+    m.centre = (g.rows / 2) * g.cols + g.cols / 2;
+    return m;
+}
+__host__ __device__ __forceinline__ uint64_t az_rollout_legal_bits(const AzGame& g, const AzRolloutMasks& m, uint64_t occ, int mc) {
+    if (g.gid == AZ_GAME_TICTACTOE) return ~occ & m.board;
+    if (g.gid == AZ_GAME_CONNECT4) return ~occ & m.board & ((occ >> g.cols) | m.floor_row);
+    if (mc == 0) return 1ull << m.centre;
+    const uint64_t h = (occ | ((occ << 1) & ~m.col0) | ((occ >> 1) & ~m.coll)) & m.board;   // a bit past the last cell must not come back down
+    return (h | (h << g.cols) | (h >> g.cols)) & ~occ & m.board;
+}
+
 // Index into the policy vector of a move stored as a cell: games/*: get_action_idx.
 __host__ __device__ __forceinline__ int az_action_index(const AzGame& g, int cell) {
     return g.gid == AZ_GAME_CONNECT4 ? cell % g.cols : cell;
