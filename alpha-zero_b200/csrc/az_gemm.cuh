@@ -236,6 +236,55 @@ __device__ __forceinline__ void az_gemm_epilogue_row(const AzGemmArgs& args, uin
         *reinterpret_cast<float2*>(args.stats_out + (size_t)row * AZ_STATS_LD + (n_blk * 2 + half) * 2) = make_float2(st1, st2);
 }
 
+// Head epilogue (BN = 64: one thread owns all head outputs of its row): final-norm fold, softmax over the policy logits,
+// tanh of the value (ai/nn.py:78-83, ai/mcts.py:49).  hs: 32 x 64 floats of staging for this warp; r0w: the warp's first row.
+__device__ __forceinline__ void az_gemm_epilogue_head(const AzGemmArgs& args, uint32_t tacc, float* hs, int r0w, int lane, bool live, int M,
+                                                      float rstd, float nmr) {
+    float l[64];
+    {
+        uint32_t r0[32], r1[32];
+        azptx::tmem_ld32(tacc, r0);
+        azptx::tmem_ld32(tacc + 32, r1);
+        azptx::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            l[i] = fmaf(rstd, __uint_as_float(r0[i]), fmaf(nmr, __ldg(args.colsum + i), __ldg(args.bias + i)));
+            l[32 + i] = fmaf(rstd, __uint_as_float(r1[i]), fmaf(nmr, __ldg(args.colsum + 32 + i), __ldg(args.bias + 32 + i)));
+        }
+    }
+    const int A = args.head_A;
+    const int nlive = min(max(M - r0w, 0), 32);
+    const size_t obase = (size_t)(args.m_item_offset + r0w);
+    float mx = -3.0e38f, val = 0.f;
+#pragma unroll
+    for (int o = 0; o < 64; ++o) {
+        if (o < A) mx = fmaxf(mx, l[o]);
+        if (o == A) val = l[o];
+    }
+    if (args.logits) {
+#pragma unroll
+        for (int o = 0; o < 64; ++o) if (o < A && live) hs[lane * A + o] = l[o];
+        __syncwarp();
+        for (int i = lane; i < nlive * A; i += 32) args.logits[obase * A + i] = hs[i];
+        __syncwarp();
+    }
+    float sum = 0.f;
+#pragma unroll
+    for (int o = 0; o < 64; ++o) {
+        if (o < A) {
+            l[o] = expf(l[o] - mx);
+            sum += l[o];
+        }
+    }
+    const float inv = 1.0f / sum;
+#pragma unroll
+    for (int o = 0; o < 64; ++o) if (o < A && live) hs[lane * A + o] = l[o] * inv;
+    __syncwarp();
+    for (int i = lane; i < nlive * A; i += 32) args.priors[obase * A + i] = hs[i];
+    __syncwarp();
+    if (live) args.values[obase + lane] = tanhf(val);
+}
+
 template <int BN, int EPI>
 __global__ void __launch_bounds__(AZ_GEMM_THREADS, 1)
 az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, const __grid_constant__ CUtensorMap tm_o,
@@ -366,10 +415,20 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         uint32_t aphase = 0;
         for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
             const int m_blk = tile / n_tiles, n_blk = tile - m_blk * n_tiles;
-            azptx::mbar_wait(&tfull[as], aphase);
-            azptx::tc_fence_after();
             const int row = m_blk * Cfg::BM + q * 32 + lane;
             const bool live = row < M;
+            // Everything the epilogue reads besides the accumulator is requested while the mainloop still runs: on a grid of one
+            // tile per CTA (the cls-row GEMMs) these round trips to L2 would otherwise start when the accumulator is ready.
+            if (EPI != AZ_EPI_HEAD) {
+                const int c0 = n_blk * BN + half * (BN / 2);
+                if (lane * 32 < BN / 2) {
+                    azptx::prefetch_l1(args.bias + c0 + lane * 32);
+                    if (args.stats_in) azptx::prefetch_l1(args.colsum + c0 + lane * 32);
+                }
+                if (EPI == AZ_EPI_RESID && live) {
+                    for (int b = 0; b < BN; b += 128) azptx::prefetch_l1(args.resid + (size_t)row * args.ldr + c0 + b / 2);
+                }
+            }
             float mean = 0.f, rstd = 1.f;
             if (args.stats_in && live) {                      // LayerNorm statistics of this A row
                 const float2* sp = reinterpret_cast<const float2*>(args.stats_in + (size_t)row * AZ_STATS_LD);
@@ -383,54 +442,13 @@ az_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 rstd = rsqrtf(fmaxf(s2 * args.ln_inv_k - mean * mean, 0.f) + args.ln_eps);
             }
             const float nmr = -mean * rstd;                   // out = rstd*acc + nmr*colsum + bias
+            azptx::mbar_wait(&tfull[as], aphase);
+            azptx::tc_fence_after();
             const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * Cfg::ACC_STRIDE;
             if constexpr (EPI == AZ_EPI_HEAD) {
                 static_assert(EPI != AZ_EPI_HEAD || BN == 64, "head epilogue: one 64-column tile per row");
-                float l[64];
-                {
-                    uint32_t r0[32], r1[32];
-                    azptx::tmem_ld32(tacc, r0);
-                    azptx::tmem_ld32(tacc + 32, r1);
-                    azptx::tmem_ld_wait();
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        l[i] = fmaf(rstd, __uint_as_float(r0[i]), fmaf(nmr, __ldg(args.colsum + i), __ldg(args.bias + i)));
-                        l[32 + i] = fmaf(rstd, __uint_as_float(r1[i]), fmaf(nmr, __ldg(args.colsum + 32 + i), __ldg(args.bias + 32 + i)));
-                    }
-                }
-                const int A = args.head_A;
                 float* hs = reinterpret_cast<float*>(smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES) + AZ_BAR_BYTES) + q * 32 * 64;
-                const int r0w = m_blk * Cfg::BM + q * 32;     // first row of this warp
-                const int nlive = min(max(M - r0w, 0), 32);
-                const size_t obase = (size_t)(args.m_item_offset + r0w);
-                float mx = -3.0e38f, val = 0.f;
-#pragma unroll
-                for (int o = 0; o < 64; ++o) {
-                    if (o < A) mx = fmaxf(mx, l[o]);
-                    if (o == A) val = l[o];
-                }
-                if (args.logits) {
-#pragma unroll
-                    for (int o = 0; o < 64; ++o) if (o < A && live) hs[lane * A + o] = l[o];
-                    __syncwarp();
-                    for (int i = lane; i < nlive * A; i += 32) args.logits[obase * A + i] = hs[i];
-                    __syncwarp();
-                }
-                float sum = 0.f;
-#pragma unroll
-                for (int o = 0; o < 64; ++o) {
-                    if (o < A) {
-                        l[o] = expf(l[o] - mx);
-                        sum += l[o];
-                    }
-                }
-                const float inv = 1.0f / sum;
-#pragma unroll
-                for (int o = 0; o < 64; ++o) if (o < A && live) hs[lane * A + o] = l[o] * inv;
-                __syncwarp();
-                for (int i = lane; i < nlive * A; i += 32) args.priors[obase * A + i] = hs[i];
-                __syncwarp();
-                if (live) args.values[obase + lane] = tanhf(val);
+                az_gemm_epilogue_head(args, tacc, hs, m_blk * Cfg::BM + q * 32, lane, live, M, rstd, nmr);
             } else {
                 unsigned char* stg = (BN == 128 || BN == 256) && args.stage_out
                                          ? smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES) + AZ_BAR_BYTES + (warp - 2) * 4096 : nullptr;

@@ -71,6 +71,10 @@ static int az_pick_bn(int N) { return N % 256 == 0 ? 256 : (N % 192 == 0 ? 192 :
 // Column-tile width for a GEMM with few row tiles (the cls-row GEMMs: M = boards): the widest tile
 // is not the best one when it leaves SMs idle.  cost ~ waves x bytes staged per k-block.
 static int az_pick_bn_small_m(int N, int max_rows) {
+    if (const char* e = getenv("AZ_SMALL_M_ROWS")) {          // experiments: choose the tile for this many live rows instead of the capacity
+        const int r = atoi(e);
+        if (r > 0 && r < max_rows) max_rows = r;
+    }
     if (!g_num_sms) {
         int dev = 0;
         cudaGetDevice(&dev);
@@ -301,6 +305,7 @@ extern "C" int az_gemm_bf16(const void* a_dev, int lda, const void* w_dev, const
 #include "az_front2.cuh"
 #include "az_attn.cuh"
 #include "az_tail.cuh"
+#include "az_chain.cuh"
 
 struct AzBlockW {
     float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
@@ -361,6 +366,8 @@ struct az_net {
     bool attn_mma = false;               // all-token attention of the full blocks on tcgen05 (az_attn.cuh)
     CUtensorMap tm_qkv;
     bool fused_tail = false;             // out-proj .. heads of the cls rows in one cluster kernel (az_tail.cuh), small batches
+    bool chain = false;                  // ... as one persistent kernel running the four GEMMs back to back (az_chain.cuh)
+    unsigned int* chain_sync = nullptr;
     CUtensorMap tm_t_u, tm_t_wo, tm_t_w1, tm_t_w2;
     float *stats1 = nullptr, *stats2 = nullptr;
     bf16* w_head_ln = nullptr;
@@ -907,6 +914,21 @@ extern "C" int az_net_finalize(az_net* n) {
             n->fused_tail = true;
         }
     }
+    {   // the four cls-row GEMMs as one persistent kernel (az_chain.cuh) for evaluation batches of up to AZ_CHAIN_MAX_ROWS boards.
+        // Opt-in (AZ_CHAIN=1): bit-identical to the four launches and 64 us against 70 us when the kernels are timed one by one,
+        // but slower inside the search graph (Connect4 62.9 M simulations/s against 66.8 M): a layer still costs ~16 us without
+        // its launch and prologue, and the grid-wide barriers give up the overlap programmatic dependent launch provides.
+        AzBlockW& w = n->blk[n->L - 1];
+        const int chain_max = getenv("AZ_CHAIN_MAX_ROWS") ? atoi(getenv("AZ_CHAIN_MAX_ROWS")) : 8192;
+        auto ok_bn = [](int bn) { return bn == 128 || bn == 256; };
+        const bool want = getenv("AZ_CHAIN") && atoi(getenv("AZ_CHAIN")) != 0;
+        if (want && n->front2 && n->tail_fold && n->head_fold && !n->fused_tail && n->chunk <= chain_max && ok_bn(n->bn_out2) && ok_bn(w.bn_w1_c) &&
+            ok_bn(w.bn_w2_c)) {
+            if ((rc = az_net_alloc(n, &n->chain_sync, 2))) return rc;
+            AZ_CUDA_OK(cudaMemset(n->chain_sync, 0, 2 * sizeof(unsigned int)));
+            n->chain = true;
+        }
+    }
     n->head_gemm = false;
     if (!n->head_fold && A + 1 > 32 && A + 1 <= 64 && !getenv("AZ_NO_HEAD_GEMM")) {   // heads as one N = 64 tensor-core GEMM
         std::vector<float> wh((size_t)64 * D, 0.f), bh(64, 0.f);
@@ -1127,6 +1149,54 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
             ++n->launches;
             return AZ_OK;
         }
+        if (n->chain) {
+            AzChainMaps cm;
+            AzChainArgs ca{};
+            // the same arguments cls_tail() and heads() give the four separate launches
+            ca.g[0] = az_gargs(batch, 1, n->b_out2, nullptr, 0, n->xc, D, D, n->H * 128);
+            ca.g[0].stats_out = n->stats1;
+            ca.g[1] = az_gargs(batch, 1, w.b1_ln, nullptr, 0, n->hc, 4 * D, 4 * D, D);
+            ca.g[1].stats_in = n->stats1;
+            ca.g[1].stats_parts = 2 * (D / n->bn_out2);
+            ca.g[1].colsum = w.cs1;
+            ca.g[1].ln_inv_k = 1.0f / (float)D;
+            ca.g[1].ln_eps = 1e-5f;
+            ca.g[2] = az_gargs(batch, 1, w.b2, n->xc, D, n->xc2, D, D, 4 * D);
+            ca.g[2].stats_out = n->stats2;
+            ca.g[3] = az_gargs(batch, 1, n->b_head_ln, nullptr, 0, nullptr, 64, 64, D);
+            ca.g[3].stats_in = n->stats2;
+            ca.g[3].stats_parts = 2 * (D / w.bn_w2_c);
+            ca.g[3].colsum = n->cs_head;
+            ca.g[3].ln_inv_k = 1.0f / (float)D;
+            ca.g[3].ln_eps = 1e-5f;
+            ca.g[3].head_A = A;
+            ca.g[3].priors = priors; ca.g[3].values = values; ca.g[3].logits = logits;
+            ca.bn[0] = n->bn_out2; ca.bn[1] = w.bn_w1_c; ca.bn[2] = w.bn_w2_c; ca.bn[3] = 64;
+            ca.sync = n->chain_sync;
+            cm.a[0] = n->tm_uc; cm.a[1] = n->tm_xc; cm.a[2] = n->tm_hc; cm.a[3] = n->tm_xc2;
+            cm.b[0] = n->tm_wout2; cm.b[1] = w.tm_w1_ln_c; cm.b[2] = w.tm_w2_c; cm.b[3] = n->tm_whead_ln;
+            int tiles_max = 1;
+            for (int l = 0; l < 3; ++l) {
+                ca.g[l].l2_hints = 1;
+                cm.o[l] = cm.a[l];
+                if ((rc = az_gemm_out_map<256, AZ_EPI_BIAS>(&ca.g[l], &cm.o[l], cap))) return rc;       // box 64 x 32 whatever the tile width
+                tiles_max = std::max(tiles_max, ((cap + 127) / 128) * (ca.g[l].N / ca.bn[l]));
+            }
+            cm.o[3] = cm.a[3];
+            static bool attr_done = false;
+            if (!attr_done) {
+                AZ_CUDA_OK(cudaFuncSetAttribute(az_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AZ_CHAIN_SMEM));
+                attr_done = true;
+            }
+            const int grid = std::min(tiles_max, g_num_sms);
+            {
+                AzProfScope ps(n, AZ_K_TAIL, s);
+                AZ_CUDA_OK(az_launch_pdl(az_chain_kernel, grid, AZ_GEMM_THREADS, (size_t)AZ_CHAIN_SMEM, s, cm, ca));
+            }
+            AZ_CUDA_OK(cudaGetLastError());
+            ++n->launches;
+            return AZ_OK;
+        }
         if (n->front2) {
             if ((rc = cls_tail(w, az_gargs(batch, 1, n->b_out2, nullptr, 0, n->xc, D, D, n->H * 128), AZ_EPI_BIAS, true))) return rc;
             return heads(n->xc2);
@@ -1305,7 +1375,7 @@ extern "C" int az_net_proj_width(az_net* n) { return n ? (n->folded ? n->n2 : 2 
 extern "C" int az_net_path_flags(az_net* n) {
     if (!n) return 0;
     return (n->front ? 1 : 0) | (n->front2 ? 2 : 0) | (n->blk[n->L - 1].bn_w1_c >= AZ_PAIR ? 4 : 0) | (n->tail_fold ? 8 : 0) | (n->head_fold ? 16 : 0) |
-           (n->attn_mma ? 32 : 0) | (n->fused_tail ? 64 : 0) | (getenv("AZ_NO_TMA_STORE") ? 0 : 128);
+           (n->attn_mma ? 32 : 0) | (n->fused_tail ? 64 : 0) | (getenv("AZ_NO_TMA_STORE") ? 0 : 128) | (n->chain ? 256 : 0);
 }
 
 extern "C" long long az_net_launch_count(az_net* n) { return n ? (long long)n->launches : 0; }

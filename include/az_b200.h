@@ -238,7 +238,8 @@ AZ_API int az_net_proj_width(az_net* n);   /* N of the all-token projection GEMM
  * bit 3 LayerNorm folded around the cls-row GEMMs, bit 4 heads + softmax as a GEMM epilogue, bit 5 all-token attention of
  * the full blocks on tcgen05 (az_attn.cuh; off: the scalar kernel, AZ_NO_ATTN_MMA=1 or an unsupported head dim), bit 6 the
  * cls-row tail fused into one cluster kernel (az_tail.cuh; opt-in, AZ_FUSED_TAIL=1), bit 7 bf16 GEMM tiles of 128 / 256
- * columns leave through shared memory + TMA stores (az_gemm.cuh; AZ_NO_TMA_STORE=1 restores per-thread row stores). */
+ * columns leave through shared memory + TMA stores (az_gemm.cuh; AZ_NO_TMA_STORE=1 restores per-thread row stores), bit 8
+ * the four cls-row GEMMs as one persistent kernel (az_chain.cuh; opt-in, AZ_CHAIN=1). */
 AZ_API int az_net_path_flags(az_net* n);
 /* MCTS.mcts with the built-in net for every tree of the forest: `iters` simulations per tree,
  * one CUDA graph per step (advance + net), no per-node host work. */

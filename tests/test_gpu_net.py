@@ -229,3 +229,40 @@ def test_fused_tail_matches_gemm_chain(rows, cols, C, A, dim, patch, monkeypatch
     d = np.abs(l - l0).max()
     print(f"\nfused tail vs GEMM chain: max |dlogit| {d:.5f}, max |dvalue| {np.abs(v - v0).max():.5f}; vs torch fp32: fused {np.abs(l[:600] - rl.numpy()).max():.4f}, chain {np.abs(l0[:600] - rl.numpy()).max():.4f}")
     assert d <= 0.03 and np.abs(p - p0).max() <= 0.01
+
+
+@pytest.mark.parametrize("rows,cols,C,A,dim,patch", [(6, 7, 3, 7, 512, 5), (7, 7, 2, 49, 512, 5), (6, 7, 3, 7, 256, 5)])
+def test_chain_kernel_is_bit_identical_to_separate_launches(rows, cols, C, A, dim, patch, monkeypatch):
+    """az_chain_kernel (csrc/az_chain.cuh) runs the four cls-row GEMMs of small evaluation batches back to back in one
+    persistent kernel with grid-wide barriers between the layers: same tiles, same epilogues, so logits, values and priors
+    must equal those of the four separate launches bit for bit, at every batch size and on repeated calls (the barrier
+    counters are reset by the last CTA of each launch).  Opt-in with AZ_CHAIN=1: slower inside the search graph."""
+    from alpha_zero_b200.ai.nn import B200Net
+    net = make_net(rows, cols, C, A, dim, 1, patch)
+    rng = np.random.default_rng(11)
+    B = 4096
+    x = (rng.random((B, C, rows, cols)) < 0.3).astype(np.float32)
+    x[:, 1] *= (1 - x[:, 0])
+    if C == 3:
+        x[:, 2] = rng.integers(0, 2, B).astype(np.float32)[:, None, None]
+    monkeypatch.setenv("AZ_CHAIN", "1")
+    eng = B200Net(net, max_batch=4096)
+    if not eng.path_flags() & 2:
+        eng.close()
+        pytest.skip("this shape does not run the reassociated front kernel")
+    if dim == 512:
+        assert eng.path_flags() & 256, "the chain kernel must be the path that runs"
+    elif not eng.path_flags() & 256:
+        eng.close()
+        pytest.skip("tiles of 64 columns were chosen for this width: separate launches")
+    outs = {}
+    for nb in (1, 127, 128, 129, 1111, 1792, 4096, 1792, 5):
+        outs[nb] = eng.forward_numpy(x[:nb])
+    eng.close()
+    monkeypatch.delenv("AZ_CHAIN")
+    eng = B200Net(net, max_batch=4096)
+    assert not eng.path_flags() & 256
+    for nb, (l, v, p) in outs.items():
+        l0, v0, p0 = eng.forward_numpy(x[:nb])
+        assert np.array_equal(l, l0) and np.array_equal(v, v0) and np.array_equal(p, p0), f"batch of {nb}"
+    eng.close()

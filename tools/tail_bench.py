@@ -1,5 +1,5 @@
-"""Per-kernel time of the cls-row evaluator at small batches with the fused tail (az_tail.cuh, AZ_FUSED_TAIL=1) and with the
-four-GEMM chain (default).  usage: python tools/tail_bench.py [connect4|gomoku] [boards ...]"""
+"""Per-kernel time of the cls-row evaluator at small batches: four separate GEMM launches (default), the chain kernel
+(az_chain.cuh, AZ_CHAIN=1) and the feature-split cluster kernel (az_tail.cuh, AZ_FUSED_TAIL=1).  usage: python tools/tail_bench.py [connect4|gomoku] [boards ...]"""
 import os, sys, subprocess
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -34,7 +34,7 @@ if __name__ == "__main__":
     else:
         game = a[0] if a else "connect4"
         sizes = a[1:] or ["256", "1024", "1792", "4096"]
-        for env in ({"AZ_FUSED_TAIL": "1"}, {}):
-            print("==", env or "GEMM chain")
+        for env in ({}, {"AZ_CHAIN": "1"}, {"AZ_FUSED_TAIL": "1"}):
+            print("==", env or "four launches (default)")
             sys.stdout.flush()
             subprocess.check_call([sys.executable, __file__, "--child", game] + sizes, env={**os.environ, **env})
