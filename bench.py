@@ -37,6 +37,10 @@ WORKLOADS = {
                      name="connect4_6x7_4096games_800sims_vl1_net512x1"),
     "gomoku": dict(game="gomoku", rows=7, trees=8192, iters=800, vl=8, max_plies=12,
                    name="gomoku_7x7_8192games_800sims_vl8_net512x1"),
+    # the reference's other network (main.py:187-188: D = 256, depth 2): the generic evaluator path (all-token tcgen05 attention,
+    # full-block GEMMs); not part of the default run, `--workload gomoku_depth2`
+    "gomoku_depth2": dict(game="gomoku", rows=7, trees=4096, iters=800, vl=8, max_plies=12, net=dict(dim=256, depth=2, patch=5, heads=8),
+                          name="gomoku_7x7_4096games_800sims_vl8_net256x2"),
 }
 NET = dict(dim=512, depth=1, patch=5, heads=8)          # main.py:134
 ROUNDS_CONTINUOUS = 4                                   # vl = 1, continuous plies: simulations per tree and launch while leaves hit the cache
@@ -82,7 +86,8 @@ def run_cpu_baseline(wl, seconds, procs, kind="auto"):
     if kind == "auto":
         kind = "reference" if (wl["game"] == "gomoku" and wl["rows"] == 7 and have_ref()) else "port"
     cmd = [sys.executable, os.path.join(ROOT, "oracle", "cpu_baseline.py"), "--kind", kind, "--game", wl["game"], "--rows", str(wl["rows"]),
-           "--dim", str(NET["dim"]), "--depth", str(NET["depth"]), "--patch", str(NET["patch"]), "--heads", str(NET["heads"]),
+           "--dim", str(wl.get("net", NET)["dim"]), "--depth", str(wl.get("net", NET)["depth"]), "--patch", str(wl.get("net", NET)["patch"]),
+           "--heads", str(wl.get("net", NET)["heads"]),
            "--iters", str(wl["iters"]), "--seconds", str(seconds)]
     env = dict(os.environ, OMP_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
     t0 = time.time()
@@ -171,7 +176,8 @@ def roofline(wl, r, prof, pk, kind=None):
     launches form one kind).  Algorithmic work per launch = per-leaf (or per-simulation) figure of DESIGN.md section 4 x
     the units of one launch; duration = CUDA-event average over the profiled launches."""
     G = game_class(wl)
-    D, H, P = NET["dim"], NET["heads"], NET["patch"]
+    net = wl.get("net", NET)
+    D, H, P = net["dim"], net["heads"], net["patch"]
     T = G.rows * G.cols + 1
     kused = G.feature_dim * P * P + T
     leaves = r["leaves_per_step"]
@@ -185,26 +191,34 @@ def roofline(wl, r, prof, pk, kind=None):
     share = per_step[kind] / sum(per_step.values())
     flops, ref_flops = None, None
     front2 = bool(r.get("path_flags", 0) & 2)
+    depth = net["depth"]
+    lps = max(prof[kind]["launches"] / adv_n, 1e-9)       # launches of this kind per search pass (the generic path evaluates in chunks of 4096 boards)
     if kind == "front_fused" and front2:   # statistics (H scores + K Cholesky columns) per token + U = A^T w: H columns per token
         flops, name = 2.0 * leaves * T * kused * (H + kused + H), "az_front2_kernel (embedding+LN1+score projection+cls softmax+U=A^T w, tcgen05)"
     elif kind == "front_fused":     # one contraction over the K binary inputs per token: D value + H score + K Gram columns
         flops, name = 2.0 * leaves * T * kused * (D + H + kused), "az_front_kernel (embedding+LN1+V/score projection+cls attention, tcgen05)"
     elif kind == "gemm_kv":
-        flops, name = 2.0 * leaves * T * D * r["proj_width"], f"az_gemm_kernel (all-token projection, N={r['proj_width']}, tcgen05)"
+        flops, name = 2.0 * leaves * T * D * r["proj_width"] / lps, f"az_gemm_kernel (all-token projection, N={r['proj_width']}, tcgen05)"
     elif kind == "gemm_cls_rows":   # out_proj D*D (D x H*128 after the front-kernel reassociation), mlp D*4D, 4D*D over 3 launches -> average launch
         kout = H * 128 if front2 else D
-        flops, name = 2.0 * leaves * (kout * D + 8 * D * D) / 3.0, "az_gemm_kernel (cls-row out_proj / MLP GEMMs, tcgen05; average of the 3 launches)"
-        ref_flops = 2.0 * leaves * (D * D + 8 * D * D) / 3.0          # the reference's graph: out-proj over K = D
+        qproj = 0 if r.get("path_flags", 0) & 3 else D * D        # generic path: the cls query projection is a fourth launch
+        flops, name = 2.0 * leaves * (kout * D + 8 * D * D + qproj) / lps, "az_gemm_kernel (cls-row out_proj / MLP GEMMs, tcgen05; average over the launches of a pass)"
+        ref_flops = 2.0 * leaves * (D * D + 8 * D * D + qproj) / lps          # the reference's graph: out-proj over K = D
     elif kind == "tail_fused":      # AZ_FUSED_TAIL=1: the three cls-row GEMMs + the head GEMM in one cluster kernel
         kout = H * 128 if front2 else D
         flops, name = 2.0 * leaves * (kout * D + 8 * D * D + 64 * D), "az_tail_kernel (out-proj + MLP + heads of the cls rows, one cluster kernel, tcgen05)"
     elif kind == "embed_ln":
-        flops, name = 2.0 * leaves * T * 128 * D, "az_embed_mma_kernel (im2col embedding + LN, tcgen05)"
+        flops, name = 2.0 * leaves * T * 128 * D / lps, "az_embed_mma_kernel (im2col embedding + LN, tcgen05)"
+    elif kind == "gemm_full_block":  # per full block: in-proj D x 3D, out-proj D x D, mlp D x 4D and 4D x D over all tokens
+        flops, name = 2.0 * leaves * T * 12 * D * D * (depth - 1) / lps, "az_gemm_kernel (full-block GEMMs over all tokens, tcgen05 + TMA stores; average over the launches of a pass)"
+    elif kind == "attention_full":   # S = Q K^T and O = P V per head: 2 x 2 T^2 hd per head
+        flops, name = 4.0 * leaves * T * T * D * (depth - 1) / lps, "az_attn_mma_kernel (all-token attention of a full block, tcgen05)"
     if flops is not None:
         ach = flops / (ms / 1e3) / 1e12
         d = dict(kernel=name, bound="tensor", achieved=ach, peak=pk["tflops"], unit="TFLOP/s", frac=ach / pk["tflops"],
                  traffic=traffic, peak_source=pk["src_tensor"], flops_per_launch=flops, ms_per_launch=ms, share_of_step=share,
-                 rows_per_launch=leaves)
+                 rows_per_launch=leaves / max(lps / {"gemm_cls_rows": 3.0 if r.get("path_flags", 0) & 3 else 4.0, "gemm_full_block": 4.0 * max(depth - 1, 1),
+                                                     "attention_full": float(max(depth - 1, 1))}.get(kind, 1.0), 1.0))
         if ref_flops is not None:
             d["reference_graph"] = dict(flops_per_launch=ref_flops, achieved=ref_flops / (ms / 1e3) / 1e12,
                                         frac=ref_flops / (ms / 1e3) / 1e12 / pk["tflops"],
@@ -266,7 +280,8 @@ def run_workload(args, wl, rank, world, steps, warmup, full):
     n, iters, vl = wl["trees"], wl["iters"], wl["vl"]
     A = G.action_dim
     torch.manual_seed(0)                                              # identical random-init weights on every rank
-    model = Net((G.rows, G.cols), NET["patch"], NET["dim"], A, NET["heads"], NET["depth"], G.feature_dim, dropout=0.1).eval()
+    net = wl.get("net", NET)
+    model = Net((G.rows, G.cols), net["patch"], net["dim"], A, net["heads"], net["depth"], G.feature_dim, dropout=0.1).eval()
     stream = torch.cuda.Stream()
     eng = B200Net(model, max_batch=n * vl)
     forest = az.Forest(az.game_spec(wl["game"], wl["rows"]), n, iters, vl=vl, stream=stream.cuda_stream)
@@ -586,7 +601,8 @@ def summarize(args, wl, r, world, pk):
 def config_of(wl, world):
     return dict(workload=wl["name"], game=wl["game"], board=f"{wl['rows']}x{7 if wl['game'] == 'connect4' else wl['rows']}",
                 concurrent_games_per_gpu=wl["trees"], sims_per_move=wl["iters"], vl_batch=wl["vl"],
-                net="Net(D=512,patch=5,heads=8,depth=1) random-init, ai/nn.py / main.py:134",
+                net=("Net(D=512,patch=5,heads=8,depth=1) random-init, ai/nn.py / main.py:134" if "net" not in wl else
+                     f"Net(D={wl['net']['dim']},patch={wl['net']['patch']},heads={wl['net']['heads']},depth={wl['net']['depth']}) random-init, ai/nn.py / main.py:187"),
                 steps="device-side self-play from synthetic positions of 0..max_plies random plies, finished games restart from the empty board, "
                       "Dirichlet noise on, moves sampled / first-max as the reference.  vl 1: continuous plies, one step = sims_per_move search "
                       "passes (advance + evaluator over all concurrent games), a slot moves when its own search is finished; vl > 1: lockstep, "
