@@ -1296,7 +1296,15 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         if ((rc = gemm(AZ_K_GEMM_CLS, n->tm_xn_cls, w.tm_q, az_gargs(batch, 1, w.b_in, nullptr, 0, n->qc, D, D, D), AZ_EPI_BIAS, cap))) return rc;
         {
             AzProfScope ps(n, AZ_K_CLS_ATT, s);
-            az_cls_attention_kernel<<<(cap * H + 3) / 4, 128, 0, s>>>(batch, n->qc, n->qkv, n->oc, T, D, H);
+            const int hd = D / H;
+            static const bool old_kernel = getenv("AZ_NO_CLS_ATT2") != nullptr;
+            const int grid = (cap * H + 3) / 4;
+            if (!old_kernel && hd == 32 && T <= 64) az_cls_attention2_kernel<32, 2><<<grid, 128, 0, s>>>(batch, n->qc, n->qkv, n->oc, T, D, H);
+            else if (!old_kernel && hd == 64 && T <= 64) az_cls_attention2_kernel<64, 2><<<grid, 128, 0, s>>>(batch, n->qc, n->qkv, n->oc, T, D, H);
+            else if (!old_kernel && hd == 16 && T <= 64) az_cls_attention2_kernel<16, 2><<<grid, 128, 0, s>>>(batch, n->qc, n->qkv, n->oc, T, D, H);
+            else if (!old_kernel && hd == 32 && T <= 128) az_cls_attention2_kernel<32, 4><<<grid, 128, 0, s>>>(batch, n->qc, n->qkv, n->oc, T, D, H);
+            else if (!old_kernel && hd == 16 && T <= 256) az_cls_attention2_kernel<16, 8><<<grid, 128, 0, s>>>(batch, n->qc, n->qkv, n->oc, T, D, H);
+            else az_cls_attention_kernel<<<grid, 128, 0, s>>>(batch, n->qc, n->qkv, n->oc, T, D, H);
         }
         AZ_CUDA_OK(cudaGetLastError());
         }

@@ -322,6 +322,115 @@ __global__ void __launch_bounds__(128) az_cls_attention_kernel(AzBatch batch, co
     }
 }
 
+// The same attention with every load issued up front: lane t owns tokens t, t + 32, ... (at most TPL of them) and reads BOTH
+// their K and V slices (HD bf16 each, 16-byte loads, independent of one another) before any arithmetic; scores, warp softmax,
+// then each lane scales its V slices by its probabilities and the HD partial outputs are summed across the 32 lanes by a
+// halving butterfly (HD - HD/32 shuffles: lane d ends with dims d, d + 32).  One memory round trip instead of one per four
+// tokens of the V phase.  HD in {16, 32, 64}, T <= 32 * TPL.
+template <int HD, int TPL>
+__global__ void __launch_bounds__(128) az_cls_attention2_kernel(AzBatch batch, const bf16* __restrict__ qc, const bf16* __restrict__ kv,
+                                                                bf16* __restrict__ oc, int T, int D, int H) {
+    const int items = az_batch_items(batch);
+    const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int w = blockIdx.x * (blockDim.x >> 5) + wib;
+    const int b = w / H, h = w - b * H;
+    if (b >= items) return;
+    constexpr int C8 = HD / 8;
+    const bf16* kb = kv + (size_t)b * T * 2 * D + h * HD;
+    uint4 kq[TPL][C8], vq[TPL][C8];
+#pragma unroll
+    for (int j = 0; j < TPL; ++j) {
+        const int t = j * 32 + lane;
+        const uint4* kr = reinterpret_cast<const uint4*>(kb + (size_t)(t < T ? t : 0) * 2 * D);
+#pragma unroll
+        for (int c = 0; c < C8; ++c) {
+            kq[j][c] = __ldg(kr + c);
+            vq[j][c] = __ldg(kr + D / 8 + c);
+        }
+    }
+    __shared__ float s_q2[4][HD];
+    float* q = s_q2[wib];
+    for (int d = lane; d < HD; d += 32) q[d] = __bfloat162float(qc[(size_t)b * D + h * HD + d]);
+    __syncwarp();
+    const float scale = rsqrtf((float)HD);
+    float s[TPL];
+    float mx = -1e30f;
+#pragma unroll
+    for (int j = 0; j < TPL; ++j) {
+        float acc = 0.f;
+#pragma unroll
+        for (int c = 0; c < C8; ++c) {
+            float f[8];
+            az_unpack8(kq[j][c], f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc += f[e] * q[c * 8 + e];
+        }
+        s[j] = (j * 32 + lane < T) ? acc * scale : -1e30f;
+        mx = fmaxf(mx, s[j]);
+    }
+    mx = az_warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < TPL; ++j) {
+        s[j] = (j * 32 + lane < T) ? __expf(s[j] - mx) : 0.f;
+        sum += s[j];
+    }
+    const float inv = 1.0f / az_warp_sum(sum);
+    float o[HD];
+#pragma unroll
+    for (int d = 0; d < HD; ++d) o[d] = 0.f;
+#pragma unroll
+    for (int j = 0; j < TPL; ++j) {
+#pragma unroll
+        for (int c = 0; c < C8; ++c) {
+            float f[8];
+            az_unpack8(vq[j][c], f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[c * 8 + e] = fmaf(s[j], f[e], o[c * 8 + e]);
+        }
+    }
+    // sum over the 32 lanes, halving the values a lane carries at every step: after the step with offset `off` a lane keeps the
+    // dims whose bit `off` (of dim mod 32) equals its own lane bit
+#pragma unroll
+    for (int off = 16, n = HD; off >= 1; off >>= 1) {
+        n >>= 1;
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < n; ++i) {
+            const float send = up ? o[i] : o[i + n];            // the half this lane gives away
+            const float keep = up ? o[i + n] : o[i];
+            o[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+        if (n == 1 && off > 1) {                                  // HD < 32: fewer dims than lanes, finish by plain reductions
+#pragma unroll
+            for (int o2 = off >> 1; o2 >= 1; o2 >>= 1) o[0] += __shfl_xor_sync(0xffffffffu, o[0], o2);
+            break;
+        }
+    }
+    // which dim did this lane end up with?  step k (offset 16 >> k) splits the current range in two and an `up` lane takes the
+    // upper half: dims = bit-reversed picture of the lane id, computed the same way
+    if (HD >= 32) {
+        int base = 0, span = HD;
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+            span >>= 1;
+            if (lane & off) base += span;
+        }
+        // span == HD / 32 values left: o[0 .. span)
+#pragma unroll
+        for (int i = 0; i < HD / 32; ++i) oc[(size_t)b * D + h * HD + base + i] = __float2bfloat16(o[i] * inv);
+    } else {
+        // HD = 16: after the offsets 16, 8, 4, 2 a lane holds one dim (the last reductions summed the remaining lane pairs)
+        int base = 0, span = HD;
+#pragma unroll
+        for (int off = 16; off >= 2; off >>= 1) {
+            span >>= 1;
+            if (lane & off) base += span;
+        }
+        if ((lane & 1) == 0) oc[(size_t)b * D + h * HD + base] = __float2bfloat16(o[0] * inv);
+    }
+}
+
 struct AzHeadArgs {
     AzBatch batch;
     const bf16* xc;       // [items][D] cls rows after the last block
