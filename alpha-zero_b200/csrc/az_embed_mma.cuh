@@ -8,7 +8,10 @@
 // Per 128-token tile:
 //   warps 4-7  build the A tile in shared memory in the 128B-swizzled K-major layout
 //   warp  8    one lane issues tcgen05.mma (M128, N<=256 per instruction, accumulator = whole row in TMEM)
-//   warps 0-3  read the accumulator twice (tcgen05.ld): row mean / variance, then normalise -> bf16
+//   warps 0-3  read the accumulator twice (tcgen05.ld): row mean / variance, then normalise -> bf16; both outputs leave
+//              through shared memory + TMA stores (32 rows x 64 columns per warp and store): per-thread 16-byte row
+//              stores at a 2 D-byte stride were 4096 LSU transactions per warp and tile and made this kernel 5x its
+//              HBM time
 // Wemb stays resident in shared memory (TMA, once per CTA); the LayerNorm affine is folded into
 // the weights of the following projections at load time, so the epilogue writes (x-mean)*rstd.
 #pragma once
@@ -27,20 +30,24 @@ struct AzEmbedMmaArgs {
     bf16* x;                      // residual stream (raw embedding), may be written for cls rows only
     bf16* xn;                     // (x - mean) * rstd
     int write_all_x;
+    int tma_out;                  // 1: tm_x / tm_xn describe x / xn (box 64 columns x 32 rows): staged TMA stores
 };
 
-static inline size_t az_embed_mma_smem(int D, int kblocks, int T, int pp) {
-    return 1024 + (size_t)kblocks * D * 128 + 2 * (size_t)kblocks * 16384 + ((size_t)T * pp + 15) / 16 * 16 + 128;
+#define AZ_EMBED_STAGE_BYTES (4 * 2 * 2 * 4096)     // per epilogue warp: two buffers of (xn | x) tiles, 32 rows x 128 bytes each
+static inline size_t az_embed_mma_smem(int D, int kblocks, int T, int pp, bool staged) {
+    return 1024 + (size_t)kblocks * D * 128 + 2 * (size_t)kblocks * 16384 + (staged ? AZ_EMBED_STAGE_BYTES : 0) + ((size_t)T * pp + 15) / 16 * 16 + 128;
 }
 
 template <int TMEM_COLS>
-__global__ void __launch_bounds__(288, 1) az_embed_mma_kernel(const __grid_constant__ CUtensorMap tm_w, AzEmbedMmaArgs a) {
+__global__ void __launch_bounds__(288, 1) az_embed_mma_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
+                                                              const __grid_constant__ CUtensorMap tm_xn, AzEmbedMmaArgs a) {
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
     const int KB = a.kblocks, D = a.D, T = a.T, pp = a.patch * a.patch;
     unsigned char* s_w = smem;                                   // [KB][D rows][128 B]
     unsigned char* s_a = s_w + (size_t)KB * D * 128;             // [2 stages][KB][128 rows][128 B]
-    uint8_t* s_tap = s_a + 2 * (size_t)KB * 16384;               // [T][pp] source cell of each tap, 0xFF = outside
+    unsigned char* s_out = s_a + 2 * (size_t)KB * 16384;         // [4 warps][2 buffers][xn | x][32 rows][128 B] staging of the TMA stores
+    uint8_t* s_tap = s_out + (a.tma_out ? AZ_EMBED_STAGE_BYTES : 0);   // [T][pp] source cell of each tap, 0xFF = outside
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_tap + ((size_t)T * pp + 15) / 16 * 16);
     uint64_t* w_full = bars;          // 1
     uint64_t* a_full = bars + 1;      // 2
@@ -192,20 +199,50 @@ __global__ void __launch_bounds__(288, 1) az_embed_mma_kernel(const __grid_const
             const float mean = s / (float)D;
             const float rstd = rsqrtf(fmaxf(ss / (float)D - mean * mean, 0.f) + 1e-5f);
             const bool want_x = live && (a.write_all_x || (row % T) == 0);
+            const bool stage = a.tma_out != 0;                   // warp-uniform
+            const bool stage_x = stage && a.write_all_x;
+            const int row_w0 = tile * 128 + q * 32;
             for (int c = 0; c < D / 32; ++c) {
                 uint32_t v[32];
                 azptx::tmem_ld32(tq + c * 32, v);
                 azptx::tmem_ld_wait();
-                if (live) {
-                    uint4 o[4], xr[4];
+                uint4 o[4], xr[4];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const float f0 = __uint_as_float(v[2 * i]), f1 = __uint_as_float(v[2 * i + 1]);
-                        __nv_bfloat162 n2 = __floats2bfloat162_rn((f0 - mean) * rstd, (f1 - mean) * rstd);
-                        __nv_bfloat162 x2 = __floats2bfloat162_rn(f0, f1);
-                        reinterpret_cast<uint32_t*>(o)[i] = *reinterpret_cast<uint32_t*>(&n2);
-                        reinterpret_cast<uint32_t*>(xr)[i] = *reinterpret_cast<uint32_t*>(&x2);
+                for (int i = 0; i < 16; ++i) {
+                    const float f0 = __uint_as_float(v[2 * i]), f1 = __uint_as_float(v[2 * i + 1]);
+                    __nv_bfloat162 n2 = __floats2bfloat162_rn((f0 - mean) * rstd, (f1 - mean) * rstd);
+                    __nv_bfloat162 x2 = __floats2bfloat162_rn(f0, f1);
+                    reinterpret_cast<uint32_t*>(o)[i] = live ? *reinterpret_cast<uint32_t*>(&n2) : 0u;
+                    reinterpret_cast<uint32_t*>(xr)[i] = live ? *reinterpret_cast<uint32_t*>(&x2) : 0u;
+                }
+                unsigned char* stg_n = s_out + ((size_t)q * 2 + ((c >> 1) & 1)) * 2 * 4096;   // pairs of chunks alternate between two buffers
+                unsigned char* stg_x = stg_n + 4096;
+                if (stage) {
+                    if ((c & 1) == 0) {
+                        if (lane == 0) azptx::bulk_wait_read1();     // the stores issued two pairs ago have read this buffer
+                        __syncwarp();
                     }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const uint32_t off = (uint32_t)lane * 128u + (((uint32_t)((c & 1) * 4 + i) ^ ((uint32_t)lane & 7u)) << 4);
+                        *reinterpret_cast<uint4*>(stg_n + off) = o[i];
+                        if (stage_x) *reinterpret_cast<uint4*>(stg_x + off) = xr[i];
+                    }
+                    if (c & 1) {
+                        azptx::fence_proxy_async();
+                        __syncwarp();
+                        if (lane == 0) {
+                            azptx::tma_store_2d(&tm_xn, stg_n, (c - 1) * 32, row_w0);
+                            if (stage_x) azptx::tma_store_2d(&tm_x, stg_x, (c - 1) * 32, row_w0);
+                            azptx::bulk_commit();
+                        }
+                    }
+                    if (!stage_x && want_x) {
+                        uint4* dx = reinterpret_cast<uint4*>(a.x + (size_t)row * D + c * 32);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) dx[i] = xr[i];
+                    }
+                } else if (live) {
                     uint4* dst = reinterpret_cast<uint4*>(a.xn + (size_t)row * D + c * 32);
 #pragma unroll
                     for (int i = 0; i < 4; ++i) dst[i] = o[i];
@@ -219,6 +256,7 @@ __global__ void __launch_bounds__(288, 1) az_embed_mma_kernel(const __grid_const
             azptx::tc_fence_before();
             azptx::mbar_arrive(acc_empty);
         }
+        if (lane == 0) azptx::bulk_wait0();                     // this warp's TMA stores are complete before the CTA retires
     }
     azptx::tc_fence_before();
     __syncthreads();

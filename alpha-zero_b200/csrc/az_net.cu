@@ -333,7 +333,8 @@ struct az_net {
     float* posb = nullptr;
     bf16* w_emb_mma = nullptr;           // [D][kpad]: conv taps | pos-emb rows (tensor-core embedding)
     int emb_kc = 0, emb_kblocks = 0;     // 0 kblocks: shape not supported, CUDA-core embedding is used
-    CUtensorMap tm_emb;
+    CUtensorMap tm_emb, tm_x_st, tm_xn_st;   // embedding weights; x / xn as TMA-store targets (box 64 x 32)
+    bool emb_tma_out = false;
     float *ones = nullptr, *zeros = nullptr;
     // depth-1 nets: cls query folded into the projection (V + 64 score columns), see az_cls_attention_folded_kernel
     bool folded = false;
@@ -844,6 +845,13 @@ extern "C" int az_net_finalize(az_net* n) {
         return rc;
     if (deep && ((rc = az_make_tmap(&n->tm_ao, n->ao, M, D, D, 128)) || (rc = az_make_tmap(&n->tm_hbuf, n->hbuf, M, 4 * D, 4 * D, 128))))
         return rc;
+    n->tm_x_st = n->tm_xn;                                    // placeholders unless the embedding kernel stores through TMA
+    n->tm_xn_st = n->tm_xn;
+    if (!n->front && n->emb_kblocks && D % 64 == 0 && !getenv("AZ_NO_TMA_STORE") &&
+        az_embed_mma_smem(D, n->emb_kblocks, T, n->patch * n->patch, true) <= 200 * 1024) {
+        if ((rc = az_make_tmap(&n->tm_x_st, n->x, M, D, D, 32)) || (rc = az_make_tmap(&n->tm_xn_st, n->xn, M, D, D, 32))) return rc;
+        n->emb_tma_out = true;
+    }
     if (deep && az_attn_supported(T, D, n->H) && !getenv("AZ_NO_ATTN_MMA")) {
         // key / value rows past a board's last token are read (and meet probability 0): they have to be finite from the start
         AZ_CUDA_OK(cudaMemset(n->qkv, 0, M * 3 * D * sizeof(bf16)));
@@ -1211,7 +1219,8 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
         ma.batch = batch; ma.leaf_words = words; ma.leaf_player = players; ma.nw = nw;
         ma.rows = n->rows; ma.cols = n->cols; ma.planes = n->C; ma.patch = n->patch; ma.D = D; ma.T = T;
         ma.kc = n->emb_kc; ma.kblocks = n->emb_kblocks; ma.x = n->x; ma.xn = n->xn; ma.write_all_x = L > 1;
-        const size_t smem = az_embed_mma_smem(D, n->emb_kblocks, T, n->patch * n->patch);
+        ma.tma_out = n->emb_tma_out ? 1 : 0;
+        const size_t smem = az_embed_mma_smem(D, n->emb_kblocks, T, n->patch * n->patch, n->emb_tma_out);
         const int tiles = (int)((max_rows + 127) / 128);
         const int grid = tiles < g_num_sms ? (tiles > 0 ? tiles : 1) : g_num_sms;
 #define AZ_EMB(COLS)                                                                                                  \
@@ -1221,7 +1230,7 @@ static int az_net_forward_chunk(az_net* n, AzBatch batch, const uint64_t* words,
             AZ_CUDA_OK(cudaFuncSetAttribute(az_embed_mma_kernel<COLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
             done = true;                                                                                              \
         }                                                                                                             \
-        az_embed_mma_kernel<COLS><<<grid, 288, smem, s>>>(n->tm_emb, ma);                                             \
+        az_embed_mma_kernel<COLS><<<grid, 288, smem, s>>>(n->tm_emb, n->tm_x_st, n->tm_xn_st, ma);                     \
     }
         if (D <= 64) AZ_EMB(64) else if (D <= 128) AZ_EMB(128) else if (D <= 256) AZ_EMB(256) else AZ_EMB(512)
 #undef AZ_EMB
